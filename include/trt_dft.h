@@ -1,0 +1,103 @@
+/*
+ * trt_dft.h -- C ABI of the B200-native DFT kernel library inside libtrt_dft_plugins.so.
+ *
+ * The reference exports no C symbols at all: its API is "dlopen the .so and the two plugin
+ * creators register themselves" (/root/reference/src/dft_plugins/dft_plugins.cpp:575-576,
+ * /root/reference/src/trt_dft_plugins/__init__.py:26-32).  Its hot path is the pair of
+ * library calls made from enqueue.  Each entry point below replaces one of those call sites,
+ * so that the plugin shell's enqueue is a few lines over this ABI and so that the path can be
+ * driven (ctypes, cgo, JNI, ...) and tested without TensorRT.
+ *
+ * Conventions: plain pointers and sizes only; every function returns an int status
+ * (TRT_DFT_OK == 0) unless noted; nothing throws, nothing synchronises the device unless the
+ * comment says so; all device work is enqueued on the caller's stream.
+ * Layouts are the plugin's: fp32, C-contiguous ("kLINEAR"), complex = trailing dim of 2
+ * (re, im interleaved), one-sided in the last signal dim, leading dims folded into `batch`
+ * (splitSignalDims, dft_plugins.cpp:250-266).
+ */
+#ifndef TRT_DFT_H_
+#define TRT_DFT_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define TRT_DFT_OK 0
+#define TRT_DFT_ERR_INVALID_ARG 1   /* bad direction / rank / dims / null pointer            */
+#define TRT_DFT_ERR_CUDA 2          /* a CUDA runtime call or kernel launch failed            */
+#define TRT_DFT_ERR_ALLOC 3         /* host or device allocation failed                       */
+#define TRT_DFT_ERR_WORKSPACE 4     /* plan needs workspace and none (or misaligned) was given */
+#define TRT_DFT_ERR_UNSUPPORTED 5   /* size outside what this build handles                   */
+
+#define TRT_DFT_FORWARD 0           /* R2C, unnormalised      (CUFFT_FORWARD, dft_plugins.cpp:346) */
+#define TRT_DFT_INVERSE 1           /* C2R, scaled by 1/prod(dims) (CUFFT_INVERSE + scal, :400,:457-468) */
+
+typedef struct trt_dft_plan_s* trt_dft_plan_t;
+
+/* Library version string, e.g. "b200-dft 0.1 (sm_100a)".  Never NULL. */
+const char* trt_dft_version(void);
+
+/* Human-readable text for a status code.  Never NULL. */
+const char* trt_dft_error_string(int status);
+
+/*
+ * Replaces cufftCreate + cufftSetAutoAllocation + cufftXtMakePlanMany
+ * (dft_plugins.cpp:161-176, called from configurePlugin :131-178).
+ *   direction : TRT_DFT_FORWARD or TRT_DFT_INVERSE
+ *   rank      : signal_ndim, 1..3                                   (dft_plugins.cpp:57)
+ *   dims      : the LOGICAL REAL signal size, rank entries -- the input's trailing dims for
+ *               Rfft (:396), the output's trailing dims for Irfft (:488); any length >= 1
+ *   batch     : product of all leading dims (:260-263), >= 0
+ * Builds the radix schedule, uploads twiddle / permutation tables to the current device
+ * (cudaMalloc + synchronous cudaMemcpy: call it at configure time, not inside a stream
+ * capture) and picks the kernels.  The plan is immutable afterwards and may be used from
+ * several streams at once.
+ */
+int trt_dft_plan_create(trt_dft_plan_t* plan, int direction, int rank, const int64_t* dims, int64_t batch);
+
+/* Replaces the workSize out-parameter of cufftXtMakePlanMany (dft_plugins.cpp:175) that
+ * getWorkspaceSize reports (:114-129).  0 for every single-kernel plan. */
+size_t trt_dft_workspace_bytes(trt_dft_plan_t plan);
+
+/*
+ * Replaces cufftSetStream + cufftSetWorkArea + cufftXtExec (+ cublasSetStream + cublasScalEx
+ * for the inverse): dft_plugins.cpp:185-195 and :454-468.
+ *   in, out   : device pointers (out-of-place; `in` is never written -- the reference
+ *               const_casts it for cuFFT, :193)
+ *   workspace : device pointer to >= trt_dft_workspace_bytes(plan) bytes, 16-byte aligned;
+ *               may be NULL when that is 0
+ *   stream    : a cudaStream_t (0 = legacy default stream)
+ * Asynchronous; no allocation, no synchronisation, no host<->device copy.
+ */
+int trt_dft_exec(trt_dft_plan_t plan, const void* in, void* out, void* workspace, void* stream);
+
+/* Replaces cufftDestroy / cublasDestroy (dft_plugins.cpp:277-303).  Frees the plan's device
+ * tables (synchronises the device, like cudaFree does).  NULL is accepted. */
+int trt_dft_plan_destroy(trt_dft_plan_t plan);
+
+/*
+ * Host-buffer convenience used by tests and bench.py's end-to-end number: what
+ * tests/test_dft.py:104-115 (run_trt_inference) does around the engine -- device buffers,
+ * host->device copy of `host_in`, exec, device->host copy into `host_out`, stream
+ * synchronise.  `host_in` / `host_out` are ordinary or pinned host memory.  Allocates and
+ * frees its own device buffers and workspace.  Synchronous.
+ */
+int trt_dft_exec_host(trt_dft_plan_t plan, const void* host_in, void* host_out);
+
+/* Introspection for tests and DESIGN.md: fills `buf` (size `len`) with a one-line description
+ * of the kernels the plan runs, e.g. "fused2d<90,180> tiles=6144 threads=256 smem=64816".
+ * Returns the number of kernel launches one trt_dft_exec issues (> 0), or -1. */
+int trt_dft_plan_describe(trt_dft_plan_t plan, char* buf, size_t len);
+
+/* Number of elements (floats) of the input / output tensors of a plan, for callers that
+ * size buffers from the plan instead of recomputing the shape rules. */
+int64_t trt_dft_plan_input_floats(trt_dft_plan_t plan);
+int64_t trt_dft_plan_output_floats(trt_dft_plan_t plan);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* TRT_DFT_H_ */

@@ -1,0 +1,172 @@
+// dft_phases.cuh -- the per-tile phases of the shared-memory FFT engine.
+//
+// A tile (one or more images / rows / a column chunk) sits in shared memory as complex
+// float2 values with pitch P.  Every phase is written as "thread tid of nthr does its share";
+// phases are separated by a CTA barrier in the kernels (dft_kernels.cu).  The same functions
+// compile for the host (tests/emu) where the "threads" of a phase run one after another --
+// legal because no phase has an intra-phase dependency between threads.
+//
+// All FFT steps are forward (w = exp(-2*pi*i/n)), in place, decimation in frequency; the
+// digit-reversed result order and the inverse transform's index reversal are resolved by the
+// perm tables when the result leaves shared memory.
+#pragma once
+#include <math.h>
+
+#include "dft_butterflies.cuh"
+#include "dft_types.h"
+
+#if defined(__CUDA_ARCH__)
+#define DFT_LDG(ptr) __ldg(ptr)
+#else
+#define DFT_LDG(ptr) (*(ptr))
+#endif
+
+namespace dft {
+
+// ---- one radix-R step over all lines of the tile -------------------------------------------
+// ROWS (COLS=false): line l, element e at buf[l*pitch + e].
+// COLS (COLS=true) : line = (img, col) with ncols columns per image; element e at
+//                    buf[img*img_stride + e*pitch + col]; consecutive threads take
+//                    consecutive columns (bank-conflict free, stride 1).
+template <int R, bool COLS>
+DFT_HD void fft_step(float2* buf, int nlines, int pitch, int N, int L, const float2* tw, int ncols,
+                     int img_stride, int tid, int nthr)
+{
+    const int m = L / R;         // element stride inside the butterfly
+    const int bpl = N / R;       // butterflies per line
+    const int tws = N / L;       // twiddle table stride: w_L^x = w_N^(x*tws)
+    const int total = nlines * bpl;
+    for (int t = tid; t < total; t += nthr) {
+        int line, u;
+        if (COLS) {
+            u = t / nlines;
+            line = t - u * nlines;
+        } else {
+            line = t / bpl;
+            u = t - line * bpl;
+        }
+        int blk, b;
+        if (m == 1) {
+            blk = u;
+            b = 0;
+        } else {
+            blk = u / m;
+            b = u - blk * m;
+        }
+        const int e0 = blk * L + b;
+        float2* p;
+        int es;
+        if (COLS) {
+            int base = line;
+            if (ncols != nlines) {  // more than one image in the tile
+                const int img = line / ncols;
+                base = img * img_stride + (line - img * ncols);
+            }
+            p = buf + base + e0 * pitch;
+            es = m * pitch;
+        } else {
+            p = buf + line * pitch + e0;
+            es = m;
+        }
+        float2 v[R];
+        static_for<0, R>([&](auto ac) {
+            constexpr int a = decltype(ac)::value;
+            v[a] = p[a * es];
+        });
+        dft_reg<R>(v);
+        if (m > 1) {
+            static_for<1, R>([&](auto cc) {
+                constexpr int c = decltype(cc)::value;
+                const float2 w = DFT_LDG(tw + (long long)b * c * tws);
+                v[c] = cmul(v[c], w);
+            });
+        }
+        static_for<0, R>([&](auto cc) {
+            constexpr int c = decltype(cc)::value;
+            p[c * es] = v[c];
+        });
+    }
+}
+
+template <bool COLS>
+DFT_HD void fft_step_dispatch(int radix, float2* buf, int nlines, int pitch, int N, int L,
+                              const float2* tw, int ncols, int img_stride, int tid, int nthr)
+{
+    switch (radix) {
+#define DFT_CASE(R)                                                                     \
+    case R:                                                                             \
+        fft_step<R, COLS>(buf, nlines, pitch, N, L, tw, ncols, img_stride, tid, nthr);  \
+        break;
+        DFT_CASE(2)
+        DFT_CASE(3)
+        DFT_CASE(4)
+        DFT_CASE(5)
+        DFT_CASE(6)
+        DFT_CASE(7)
+        DFT_CASE(8)
+        DFT_CASE(9)
+        DFT_CASE(10)
+        DFT_CASE(11)
+        DFT_CASE(13)
+        DFT_CASE(16)
+#undef DFT_CASE
+        default:
+            break;
+    }
+}
+
+// ---- forward real-FFT split ("untangle") ----------------------------------------------------
+// x real of length W = 2M, z[n] = x[2n] + i x[2n+1], Z = FFT_M(z):
+//   X[k] = (Z[k] + conj Z[M-k])/2 - (i/2) w_W^k (Z[k] - conj Z[M-k]),   k = 0..M  (indices mod M)
+// In 2-D the same formula holds after the column FFT with the partner taken at row (H-q) mod H.
+DFT_HD float2 untangle(float2 z1, float2 z2, float2 w)
+{
+    // e = (z1 + conj z2)/2 ; o = (z1 - conj z2)/2 ; X = e - i*w*o
+    const float ex = 0.5f * (z1.x + z2.x), ey = 0.5f * (z1.y - z2.y);
+    const float ox = 0.5f * (z1.x - z2.x), oy = 0.5f * (z1.y + z2.y);
+    // w*o
+    const float tx = w.x * ox - w.y * oy, ty = w.x * oy + w.y * ox;
+    // -i*(tx + i ty) = ty - i tx
+    return float2{ex + ty, ey - tx};
+}
+
+// ---- inverse real-FFT merge (in place, per row) -----------------------------------------------
+// From the one-sided row T[0..M] build Z'[k] = (T[k] + conj T[M-k]) + i conj(w_W^k)(T[k] - conj T[M-k]),
+// k = 0..M-1, whose (unnormalised) inverse M-point FFT is W*x packed as x[2n] + i x[2n+1].
+// The imaginary parts of T[0] and T[M] are ignored (C2R semantics).
+DFT_HD void merge_rows(float2* buf, int nrows, int pitch, int M, const float2* tw_unt, int tid, int nthr)
+{
+    const int half = M / 2;                  // pairs k = 0..half  (k and M-k)
+    const int per_row = half + 1;
+    const int total = nrows * per_row;
+    for (int t = tid; t < total; t += nthr) {
+        const int r = t / per_row;
+        const int k = t - r * per_row;
+        float2* row = buf + r * pitch;
+        if (k == 0) {
+            const float a = row[0].x, b = row[M].x;
+            row[0] = float2{a + b, a - b};
+            continue;
+        }
+        const int k2 = M - k;
+        if (k2 < k) continue;                // only when M is odd and k == half+... (never for k<=half) guard
+        const float2 a = row[k], b = row[k2];
+        const float2 w = DFT_LDG(tw_unt + k);  // (c, s) = exp(-2 pi i k / W)
+        // Z'[k]   = (a + conj b) + i*conj(w)*(a - conj b)
+        // Z'[M-k] = (b + conj a) - i*w*(b - conj a)
+        const float sx = a.x + b.x, sy = a.y - b.y;   // a + conj b
+        const float dx = a.x - b.x, dy = a.y + b.y;   // a - conj b
+        // conj(w)*(d) = (c - i s)(dx + i dy) = (c dx + s dy) + i(c dy - s dx)
+        const float ux = w.x * dx + w.y * dy, uy = w.x * dy - w.y * dx;
+        // i*u = (-uy, ux)
+        row[k] = float2{sx - uy, sy + ux};
+        if (k2 != k) {
+            // b + conj a = (sx, -sy) ; b - conj a = (-dx, dy)
+            // w*(b - conj a) = (c + i s)(-dx + i dy) = (-c dx - s dy) + i(c dy - s dx) = (-ux, uy)
+            // -i*(-ux + i uy) = (uy, ux)
+            row[k2] = float2{sx + uy, -sy + ux};
+        }
+    }
+}
+
+}  // namespace dft

@@ -1,0 +1,399 @@
+// dft_planner.h -- host-side planner: radix schedules, twiddle / permutation tables and the list
+// of kernel launches for one (direction, rank, dims, batch).  Header-only; used by the CUDA
+// executor (dft_kernels.cu) and by the test-only host emulator (tests/emu/dft_emu.cpp).
+//
+// This is the replacement for what cufftXtMakePlanMany does for the reference
+// (/root/reference/src/dft_plugins/dft_plugins.cpp:171-176).
+#pragma once
+#include <math.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <string.h>
+
+#include <algorithm>
+#include <string>
+#include <vector>
+
+#include "dft_types.h"
+
+namespace dft {
+
+constexpr int kSmemMax = 227 * 1024 - 64;   // usable dynamic shared memory per CTA (bytes)
+constexpr int kBarrierBytes = 16;           // mbarrier slot appended after the tile
+constexpr int kThreads = 256;
+
+enum BufSel : int { BUF_IN = 0, BUF_OUT = 1, BUF_WS = 2, BUF_WS1 = 3 };
+
+struct Launch {
+    KParams kp;            // pointers left null; resolved by the executor from the ids below
+    int src, dst;          // BufSel
+    int tw_row_id = -1, tw_col_id = -1, tw_unt_id = -1;
+    int perm_row_id = -1, perm_col_id = -1;
+    std::string name;
+};
+
+struct PlanDesc {
+    int direction = 0, rank = 0;
+    int64_t dims[3] = {1, 1, 1};
+    int64_t batch = 0;
+    int64_t in_floats = 0, out_floats = 0;
+    size_t ws_bytes = 0;
+    size_t ws1_offset = 0;   // start of the second workspace half (BUF_WS + 1), naive inverse only
+    std::vector<Launch> launches;
+    std::vector<std::vector<float2>> tw_tables;
+    std::vector<std::vector<int>> perm_tables;
+    std::string description;
+};
+
+// ---- radix schedule --------------------------------------------------------------------------
+static const int kRadices[] = {16, 13, 11, 10, 9, 8, 7, 6, 5, 4, 3, 2};
+
+inline void factor_search(int n, int start, std::vector<int>& cur, std::vector<int>& best)
+{
+    if (n == 1) {
+        bool better = best.empty() || cur.size() < best.size();
+        if (!better && cur.size() == best.size()) {
+            const int mc = *std::max_element(cur.begin(), cur.end());
+            const int mb = *std::max_element(best.begin(), best.end());
+            better = mc < mb;
+        }
+        if (better) best = cur;
+        return;
+    }
+    if (!best.empty() && cur.size() + 1 > best.size()) return;
+    for (int i = start; i < (int)(sizeof(kRadices) / sizeof(int)); ++i) {
+        const int r = kRadices[i];
+        if (n % r) continue;
+        cur.push_back(r);
+        factor_search(n / r, i, cur, best);
+        cur.pop_back();
+    }
+}
+
+// false when n has a prime factor outside {2,3,5,7,11,13} or needs too many steps.
+inline bool make_line_fft(int n, bool rows, LineFFT* f)
+{
+    memset(f, 0, sizeof(*f));
+    f->n = n;
+    if (n < 1) return false;
+    if (n == 1) return true;
+    int m = n;
+    for (int p : {2, 3, 5, 7, 11, 13})
+        while (m % p == 0) m /= p;
+    if (m != 1) return false;
+    std::vector<int> cur, best;
+    factor_search(n, 0, cur, best);
+    if (best.empty() || (int)best.size() > kMaxSteps) return false;
+    std::sort(best.begin(), best.end(), [](int a, int b) { return a > b; });
+    if (rows) {
+        // the last row step reads r contiguous elements per thread; an odd radix makes the
+        // lane stride odd in 8-byte units, i.e. shared-memory bank-conflict free
+        int pick = -1;
+        for (int i = 0; i < (int)best.size(); ++i)
+            if (best[i] % 2 == 1) { pick = i; break; }
+        if (pick >= 0) {
+            const int r = best[pick];
+            best.erase(best.begin() + pick);
+            best.push_back(r);
+        }
+    }
+    f->nsteps = (int)best.size();
+    for (int i = 0; i < f->nsteps; ++i) f->radix[i] = best[i];
+    return true;
+}
+
+// position (in the in-place DIF result) of frequency k
+inline int dif_position(const LineFFT& f, int k)
+{
+    int L = f.n, pos = 0;
+    for (int s = 0; s < f.nsteps; ++s) {
+        const int r = f.radix[s];
+        const int m = L / r;
+        pos += (k % r) * m;
+        k /= r;
+        L = m;
+    }
+    return pos;
+}
+
+inline std::vector<int> make_perm(const LineFFT& f, bool inverse)
+{
+    std::vector<int> p(f.n);
+    for (int i = 0; i < f.n; ++i) p[i] = dif_position(f, inverse ? (f.n - i) % f.n : i);
+    return p;
+}
+
+// w_n^j = exp(-2 pi i j / n), j in [0, count)
+inline std::vector<float2> make_twiddles(int n, int count)
+{
+    std::vector<float2> t(count);
+    for (int j = 0; j < count; ++j) {
+        const double a = 2.0 * 3.14159265358979323846264338327950288 * (double)(j % n) / (double)n;
+        t[j] = float2{(float)cos(a), (float)(-sin(a))};
+    }
+    return t;
+}
+
+// ---- plan -------------------------------------------------------------------------------------
+struct Planner {
+    PlanDesc* pd;
+    int add_tw(std::vector<float2> t) { pd->tw_tables.push_back(std::move(t)); return (int)pd->tw_tables.size() - 1; }
+    int add_perm(std::vector<int> t) { pd->perm_tables.push_back(std::move(t)); return (int)pd->perm_tables.size() - 1; }
+
+    static KParams base(int mode)
+    {
+        KParams k;
+        memset(&k, 0, sizeof(k));
+        k.mode = mode;
+        k.threads = kThreads;
+        k.scale = 1.0f;
+        k.G = 1;
+        return k;
+    }
+
+    static int pick_group(long long nunits, long long unit_bytes, long long target_bytes)
+    {
+        long long g = target_bytes / std::max<long long>(unit_bytes, 1);
+        const long long spread = (nunits + 148 * 4 - 1) / (148 * 4);   // keep >= ~4 tiles per SM
+        g = std::min(g, spread);
+        g = std::min<long long>(g, (long long)kSmemMax / std::max<long long>(unit_bytes, 1));
+        return (int)std::max<long long>(g, 1);
+    }
+
+    // rows pass (1-D R2C / C2R over `nrows` rows of real length W)
+    void add_rows(bool inverse, long long nrows, int W, int src, int dst, float scale)
+    {
+        const bool even = (W % 2 == 0);
+        const int M = even ? W / 2 : W;
+        KParams k = base(inverse ? (even ? MODE_I1D : MODE_I1D_ODD) : (even ? MODE_F1D : MODE_F1D_ODD));
+        k.W = W;
+        k.M = M;
+        k.H = 1;
+        k.P = (inverse && even) ? M + 1 : M;
+        make_line_fft(M, true, &k.row);
+        k.nunits = nrows;
+        k.G = pick_group(nrows, (long long)k.P * 8, 32 * 1024);
+        k.ntiles = (nrows + k.G - 1) / k.G;
+        k.smem_bytes = k.G * k.P * 8 + kBarrierBytes;
+        k.scale = scale;
+        Launch l;
+        l.kp = k;
+        l.src = src;
+        l.dst = dst;
+        l.tw_row_id = add_tw(make_twiddles(M, M));
+        l.perm_row_id = add_perm(make_perm(k.row, inverse));
+        if (even) l.tw_unt_id = add_tw(make_twiddles(W, M + 1));
+        char nm[128];
+        snprintf(nm, sizeof nm, "%s<W=%d> rows=%lld G=%d smem=%d", inverse ? (even ? "rows_c2r" : "rows_c2r_odd") : (even ? "rows_r2c" : "rows_r2c_odd"),
+                 W, nrows, k.G, k.smem_bytes);
+        l.name = nm;
+        pd->launches.push_back(l);
+    }
+
+    // complex FFT of length N along a strided axis of data[outer][N][inner]
+    void add_cols(bool inverse, long long outer, int N, long long inner, int src, int dst, float scale)
+    {
+        if (N == 1 && src == dst && scale == 1.0f) return;   // identity
+        KParams k = base(MODE_C2C_COLS);
+        k.H = N;
+        make_line_fft(N, false, &k.col);
+        const long long maxfit = std::max<long long>(1, (long long)(kSmemMax - kBarrierBytes) / ((long long)N * 8));
+        long long tm = std::max(std::min<long long>(16, maxfit), std::min<long long>(32, (64 * 1024) / ((long long)N * 8)));
+        tm = std::max<long long>(1, std::min(tm, std::min(inner, maxfit)));
+        k.G = (int)tm;
+        k.P = (int)tm;
+        k.inner = inner;
+        k.outer = outer;
+        k.chunks = (inner + tm - 1) / tm;
+        k.nunits = outer * k.chunks;
+        k.ntiles = k.nunits;
+        k.smem_bytes = N * k.P * 8 + kBarrierBytes;
+        k.scale = scale;
+        Launch l;
+        l.kp = k;
+        l.src = src;
+        l.dst = dst;
+        l.tw_col_id = add_tw(make_twiddles(N, N));
+        l.perm_col_id = add_perm(make_perm(k.col, inverse));
+        char nm[128];
+        snprintf(nm, sizeof nm, "cols_c2c<N=%d> outer=%lld inner=%lld TM=%d smem=%d", N, outer, inner, k.G, k.smem_bytes);
+        l.name = nm;
+        pd->launches.push_back(l);
+    }
+
+    void add_fused2d(bool inverse, long long nimg, int H, int W, int src, int dst, float scale)
+    {
+        const int M = W / 2;
+        KParams k = base(inverse ? MODE_I2D : MODE_F2D);
+        k.H = H;
+        k.W = W;
+        k.M = M;
+        k.P = inverse ? M + 1 : M;
+        make_line_fft(M, true, &k.row);
+        make_line_fft(H, false, &k.col);
+        const long long unit = (long long)H * k.P * 8;
+        k.nunits = nimg;
+        k.G = pick_group(nimg, unit, 48 * 1024);
+        k.ntiles = (nimg + k.G - 1) / k.G;
+        k.smem_bytes = (int)(k.G * unit) + kBarrierBytes;
+        k.scale = scale;
+        Launch l;
+        l.kp = k;
+        l.src = src;
+        l.dst = dst;
+        l.tw_row_id = add_tw(make_twiddles(M, M));
+        l.tw_col_id = add_tw(make_twiddles(H, H));
+        l.tw_unt_id = add_tw(make_twiddles(W, M + 1));
+        l.perm_row_id = add_perm(make_perm(k.row, inverse));
+        l.perm_col_id = add_perm(make_perm(k.col, inverse));
+        char nm[128];
+        snprintf(nm, sizeof nm, "%s<%d,%d> images=%lld G=%d smem=%d", inverse ? "fused_irfft2" : "fused_rfft2", H, W, nimg, k.G, k.smem_bytes);
+        l.name = nm;
+        pd->launches.push_back(l);
+    }
+
+    void add_naive(int mode, long long total, int W, int N, long long inner, int tw_n, bool inverse, int src, int dst, float scale)
+    {
+        KParams k = base(mode);
+        k.W = W;
+        k.H = N;
+        k.inner = inner;
+        k.nunits = total;
+        k.ntiles = total;
+        k.scale = scale;
+        Launch l;
+        l.kp = k;
+        l.src = src;
+        l.dst = dst;
+        if (mode == MODE_NAIVE_COLS) {
+            l.kp.W = inverse ? 1 : 0;
+            l.tw_col_id = add_tw(make_twiddles(tw_n, tw_n));
+        } else {
+            l.tw_row_id = add_tw(make_twiddles(tw_n, tw_n));
+        }
+        char nm[96];
+        snprintf(nm, sizeof nm, "naive_mode%d<n=%d> elems=%lld", mode, tw_n, total);
+        l.name = nm;
+        pd->launches.push_back(l);
+    }
+};
+
+inline bool line_supported(int n, bool rows_pitch_plus1)
+{
+    LineFFT f;
+    if (!make_line_fft(n, true, &f)) return false;
+    return (long long)(n + (rows_pitch_plus1 ? 1 : 0)) * 8 + kBarrierBytes <= kSmemMax;
+}
+
+// Returns 0 on success, nonzero TRT_DFT_ERR_* style code (1 = invalid argument).
+inline int build_plan(PlanDesc* pd, int direction, int rank, const int64_t* dims, int64_t batch)
+{
+    if (!pd || !dims || rank < 1 || rank > 3 || (direction != 0 && direction != 1) || batch < 0) return 1;
+    for (int i = 0; i < rank; ++i)
+        if (dims[i] < 1 || dims[i] > (1LL << 30)) return 1;
+    pd->direction = direction;
+    pd->rank = rank;
+    pd->batch = batch;
+    for (int i = 0; i < 3; ++i) pd->dims[i] = i < rank ? dims[i] : 1;
+    const bool inv = direction == 1;
+    const int W = (int)dims[rank - 1];
+    const int Mo = W / 2 + 1;
+    const int H = rank >= 2 ? (int)dims[rank - 2] : 1;
+    const int D = rank == 3 ? (int)dims[0] : 1;
+    const long long lead = (long long)H * D;
+    const long long real_floats = batch * lead * W;
+    const long long cplx_floats = batch * lead * Mo * 2;
+    pd->in_floats = inv ? cplx_floats : real_floats;
+    pd->out_floats = inv ? real_floats : cplx_floats;
+    pd->ws_bytes = 0;
+    if (batch == 0) {
+        pd->description = "empty";
+        return 0;
+    }
+    double total = (double)W;
+    if (rank >= 2) total *= H;
+    if (rank == 3) total *= D;
+    const float inv_scale = (float)(1.0 / total);
+    const bool even = (W % 2 == 0);
+    const int M = even ? W / 2 : W;
+
+    Planner P{pd};
+    bool engine = line_supported(M, true);
+    if (rank >= 2) engine = engine && line_supported(H, false);
+    if (rank == 3) engine = engine && line_supported(D, false);
+
+    if (!engine) {
+        // any length: naive O(N^2) passes, ping-ponging through workspace for the strided axes
+        const size_t cbytes = (size_t)cplx_floats * 4;
+        if (!inv) {
+            P.add_naive(MODE_NAIVE_ROWS_R2C, batch * lead * Mo, W, 1, 1, W, false, BUF_IN, BUF_OUT, 1.f);
+            if (rank >= 2 && H > 1) {
+                pd->ws_bytes = cbytes;
+                // out -> ws (axis H), then ws -> out (axis D, or an identity pass of length 1)
+                P.add_naive(MODE_NAIVE_COLS, batch * lead * Mo, 0, H, Mo, H, false, BUF_OUT, BUF_WS, 1.f);
+                P.add_naive(MODE_NAIVE_COLS, batch * lead * Mo, 0, D, (long long)H * Mo, D, false, BUF_WS, BUF_OUT, 1.f);
+            } else if (rank == 3 && D > 1) {
+                pd->ws_bytes = cbytes;
+                P.add_naive(MODE_NAIVE_COLS, batch * lead * Mo, 0, D, (long long)H * Mo, D, false, BUF_OUT, BUF_WS, 1.f);
+                P.add_naive(MODE_NAIVE_COLS, batch * lead * Mo, 0, 1, 1, 1, false, BUF_WS, BUF_OUT, 1.f);
+            }
+        } else {
+            if (rank == 1 || lead == 1) {
+                P.add_naive(MODE_NAIVE_ROWS_C2R, batch * lead * W, W, 1, 1, W, true, BUF_IN, BUF_OUT, inv_scale);
+            } else {
+                // in -> ws[0] (axis D) -> ws[1] (axis H) -> out (rows); ws holds two complex tensors
+                pd->ws1_offset = (cbytes + 255) / 256 * 256;
+                pd->ws_bytes = pd->ws1_offset + cbytes;
+                P.add_naive(MODE_NAIVE_COLS, batch * lead * Mo, 0, D, (long long)H * Mo, D, true, BUF_IN, BUF_WS, 1.f);
+                P.add_naive(MODE_NAIVE_COLS, batch * lead * Mo, 0, H, Mo, H, true, BUF_WS, BUF_WS1, 1.f);
+                P.add_naive(MODE_NAIVE_ROWS_C2R, batch * lead * W, W, 1, 1, W, true, BUF_WS1, BUF_OUT, inv_scale);
+            }
+        }
+    } else {
+        const bool fuse_fwd = rank >= 2 && even && ((long long)H * M * 8 + kBarrierBytes <= kSmemMax);
+        const bool fuse_inv = rank >= 2 && even && ((long long)H * (M + 1) * 8 + kBarrierBytes <= kSmemMax);
+        if (!inv) {
+            if (rank == 1) {
+                P.add_rows(false, batch, W, BUF_IN, BUF_OUT, 1.f);
+            } else {
+                if (fuse_fwd) {
+                    P.add_fused2d(false, batch * D, H, W, BUF_IN, BUF_OUT, 1.f);
+                } else {
+                    P.add_rows(false, batch * lead, W, BUF_IN, BUF_OUT, 1.f);
+                    P.add_cols(false, batch * D, H, Mo, BUF_OUT, BUF_OUT, 1.f);
+                }
+                if (rank == 3) P.add_cols(false, batch, D, (long long)H * Mo, BUF_OUT, BUF_OUT, 1.f);
+            }
+        } else {
+            if (rank == 1) {
+                P.add_rows(true, batch, W, BUF_IN, BUF_OUT, inv_scale);
+            } else {
+                int cur = BUF_IN;
+                if (rank == 3 && D > 1) {
+                    pd->ws_bytes = (size_t)cplx_floats * 4;
+                    P.add_cols(true, batch, D, (long long)H * Mo, cur, BUF_WS, 1.f);
+                    cur = BUF_WS;
+                }
+                if (fuse_inv) {
+                    P.add_fused2d(true, batch * D, H, W, cur, BUF_OUT, inv_scale);
+                } else {
+                    if (H > 1) {
+                        pd->ws_bytes = (size_t)cplx_floats * 4;
+                        P.add_cols(true, batch * D, H, Mo, cur, BUF_WS, 1.f);
+                        cur = BUF_WS;
+                    }
+                    P.add_rows(true, batch * lead, W, cur, BUF_OUT, inv_scale);
+                }
+            }
+        }
+    }
+    std::string d;
+    for (size_t i = 0; i < pd->launches.size(); ++i) {
+        if (i) d += " ; ";
+        d += pd->launches[i].name;
+    }
+    pd->description = d;
+    return 0;
+}
+
+}  // namespace dft

@@ -1,0 +1,308 @@
+// dft_programs.cuh -- per-mode tile programs: load -> FFT phases -> store.
+//
+// `Ctx` supplies tid / nthr / sync() and (device only) a bulk-async (TMA 1-D) loader.  The CUDA
+// kernels instantiate the programs with a CTA context; tests/emu instantiates them with a
+// one-thread host context (sync is a no-op), which checks all the index arithmetic on the CPU.
+#pragma once
+#include <stddef.h>
+#include <stdint.h>
+
+#include "dft_phases.cuh"
+
+namespace dft {
+
+template <class Ctx>
+DFT_HD void run_line_fft(const LineFFT& f, bool cols, float2* buf, int nlines, int pitch,
+                         const float2* tw, int ncols, int img_stride, Ctx& ctx)
+{
+    int L = f.n;
+    for (int s = 0; s < f.nsteps; ++s) {
+        const int r = f.radix[s];
+        if (cols)
+            fft_step_dispatch<true>(r, buf, nlines, pitch, f.n, L, tw, ncols, img_stride, ctx.tid, ctx.nthr);
+        else
+            fft_step_dispatch<false>(r, buf, nlines, pitch, f.n, L, tw, ncols, img_stride, ctx.tid, ctx.nthr);
+        ctx.sync();
+        L /= r;
+    }
+}
+
+// Contiguous global -> shared copy of `nfloats` floats; ends with the data visible to the CTA.
+template <class Ctx>
+DFT_HD void load_contig(Ctx& ctx, float* dst, const float* src, long long nfloats)
+{
+    if (ctx.bulk_load(dst, src, nfloats * 4)) return;  // device: cp.async.bulk + mbarrier wait
+    const uintptr_t a = (uintptr_t)src;
+    if ((a & 15) == 0 && (nfloats & 3) == 0) {
+        const float4* s4 = (const float4*)src;
+        float4* d4 = (float4*)dst;
+        for (long long i = ctx.tid; i < nfloats / 4; i += ctx.nthr) d4[i] = DFT_LDG(s4 + i);
+    } else if ((a & 7) == 0 && (nfloats & 1) == 0) {
+        const float2* s2 = (const float2*)src;
+        float2* d2 = (float2*)dst;
+        for (long long i = ctx.tid; i < nfloats / 2; i += ctx.nthr) d2[i] = DFT_LDG(s2 + i);
+    } else {
+        for (long long i = ctx.tid; i < nfloats; i += ctx.nthr) dst[i] = DFT_LDG(src + i);
+    }
+    ctx.sync();
+}
+
+// ---- MODE_F2D: fused rfft2 of G images per tile ---------------------------------------------
+template <class Ctx>
+DFT_HD void program_f2d(const KParams& p, long long tile, float2* buf, const float* in, float* out, Ctx& ctx)
+{
+    const int H = p.H, M = p.M, Mo = p.M + 1;
+    const long long first = tile * p.G;
+    const int nimg = (int)((p.nunits - first) < p.G ? (p.nunits - first) : p.G);
+    load_contig(ctx, (float*)buf, in + first * H * p.W, (long long)nimg * H * p.W);
+    run_line_fft(p.row, false, buf, nimg * H, M, p.tw_row, 0, 0, ctx);
+    run_line_fft(p.col, true, buf, nimg * M, M, p.tw_col, M, H * M, ctx);
+    float2* o = (float2*)out + first * H * Mo;
+    const int per_img = H * Mo;
+    const int total = nimg * per_img;
+    for (int idx = ctx.tid; idx < total; idx += ctx.nthr) {
+        const int img = idx / per_img;
+        const int rem = idx - img * per_img;
+        const int q = rem / Mo;
+        const int k = rem - q * Mo;
+        const int k1 = (k == M) ? 0 : k;
+        const int k2 = (k == 0 || k == M) ? 0 : M - k;
+        const int q2 = (q == 0) ? 0 : H - q;
+        const float2* ib = buf + img * H * M;
+        const float2 z1 = ib[DFT_LDG(p.perm_col + q) * M + DFT_LDG(p.perm_row + k1)];
+        const float2 z2 = ib[DFT_LDG(p.perm_col + q2) * M + DFT_LDG(p.perm_row + k2)];
+        o[idx] = untangle(z1, z2, DFT_LDG(p.tw_unt + k));
+    }
+    ctx.sync();
+}
+
+// ---- MODE_I2D: fused irfft2 --------------------------------------------------------------------
+template <class Ctx>
+DFT_HD void program_i2d(const KParams& p, long long tile, float2* buf, const float* in, float* out, Ctx& ctx)
+{
+    const int H = p.H, M = p.M, P = p.M + 1;
+    const long long first = tile * p.G;
+    const int nimg = (int)((p.nunits - first) < p.G ? (p.nunits - first) : p.G);
+    load_contig(ctx, (float*)buf, in + first * H * P * 2, (long long)nimg * H * P * 2);
+    run_line_fft(p.col, true, buf, nimg * P, P, p.tw_col, P, H * P, ctx);
+    merge_rows(buf, nimg * H, P, M, p.tw_unt, ctx.tid, ctx.nthr);
+    ctx.sync();
+    run_line_fft(p.row, false, buf, nimg * H, P, p.tw_row, 0, 0, ctx);
+    float2* o = (float2*)out + first * H * M;
+    const int per_img = H * M;
+    const int total = nimg * per_img;
+    const float sc = p.scale;
+    for (int idx = ctx.tid; idx < total; idx += ctx.nthr) {
+        const int img = idx / per_img;
+        const int rem = idx - img * per_img;
+        const int r = rem / M;
+        const int n = rem - r * M;
+        const float2 z = buf[(img * H + DFT_LDG(p.perm_col + r)) * P + DFT_LDG(p.perm_row + n)];
+        o[idx] = float2{z.x * sc, z.y * sc};
+    }
+    ctx.sync();
+}
+
+// ---- MODE_F1D: G rows per tile, W = 2M --------------------------------------------------------
+template <class Ctx>
+DFT_HD void program_f1d(const KParams& p, long long tile, float2* buf, const float* in, float* out, Ctx& ctx)
+{
+    const int M = p.M, Mo = p.M + 1;
+    const long long first = tile * p.G;
+    const int nrows = (int)((p.nunits - first) < p.G ? (p.nunits - first) : p.G);
+    load_contig(ctx, (float*)buf, in + first * p.W, (long long)nrows * p.W);
+    run_line_fft(p.row, false, buf, nrows, M, p.tw_row, 0, 0, ctx);
+    float2* o = (float2*)out + first * Mo;
+    const int total = nrows * Mo;
+    for (int idx = ctx.tid; idx < total; idx += ctx.nthr) {
+        const int r = idx / Mo;
+        const int k = idx - r * Mo;
+        const int k1 = (k == M) ? 0 : k;
+        const int k2 = (k == 0 || k == M) ? 0 : M - k;
+        const float2* rb = buf + r * M;
+        const float2 z1 = rb[DFT_LDG(p.perm_row + k1)];
+        const float2 z2 = rb[DFT_LDG(p.perm_row + k2)];
+        o[idx] = untangle(z1, z2, DFT_LDG(p.tw_unt + k));
+    }
+    ctx.sync();
+}
+
+// ---- MODE_I1D ------------------------------------------------------------------------------------
+template <class Ctx>
+DFT_HD void program_i1d(const KParams& p, long long tile, float2* buf, const float* in, float* out, Ctx& ctx)
+{
+    const int M = p.M, P = p.M + 1;
+    const long long first = tile * p.G;
+    const int nrows = (int)((p.nunits - first) < p.G ? (p.nunits - first) : p.G);
+    load_contig(ctx, (float*)buf, in + first * P * 2, (long long)nrows * P * 2);
+    merge_rows(buf, nrows, P, M, p.tw_unt, ctx.tid, ctx.nthr);
+    ctx.sync();
+    run_line_fft(p.row, false, buf, nrows, P, p.tw_row, 0, 0, ctx);
+    float2* o = (float2*)out + first * M;
+    const int total = nrows * M;
+    const float sc = p.scale;
+    for (int idx = ctx.tid; idx < total; idx += ctx.nthr) {
+        const int r = idx / M;
+        const int n = idx - r * M;
+        const float2 z = buf[r * P + DFT_LDG(p.perm_row + n)];
+        o[idx] = float2{z.x * sc, z.y * sc};
+    }
+    ctx.sync();
+}
+
+// ---- MODE_F1D_ODD: odd W, rows as zero-imaginary complex lines of length W (= p.M) ---------------
+template <class Ctx>
+DFT_HD void program_f1d_odd(const KParams& p, long long tile, float2* buf, const float* in, float* out, Ctx& ctx)
+{
+    const int W = p.W, Mo = p.W / 2 + 1;
+    const long long first = tile * p.G;
+    const int nrows = (int)((p.nunits - first) < p.G ? (p.nunits - first) : p.G);
+    const float* src = in + first * W;
+    for (int idx = ctx.tid; idx < nrows * W; idx += ctx.nthr) buf[idx] = float2{DFT_LDG(src + idx), 0.f};
+    ctx.sync();
+    run_line_fft(p.row, false, buf, nrows, W, p.tw_row, 0, 0, ctx);
+    float2* o = (float2*)out + first * Mo;
+    for (int idx = ctx.tid; idx < nrows * Mo; idx += ctx.nthr) {
+        const int r = idx / Mo;
+        const int k = idx - r * Mo;
+        o[idx] = buf[r * W + DFT_LDG(p.perm_row + k)];
+    }
+    ctx.sync();
+}
+
+// ---- MODE_I1D_ODD: Hermitian extension to W complex bins, full FFT, real part --------------------
+template <class Ctx>
+DFT_HD void program_i1d_odd(const KParams& p, long long tile, float2* buf, const float* in, float* out, Ctx& ctx)
+{
+    const int W = p.W, Mo = p.W / 2 + 1;
+    const long long first = tile * p.G;
+    const int nrows = (int)((p.nunits - first) < p.G ? (p.nunits - first) : p.G);
+    const float2* src = (const float2*)in + first * Mo;
+    for (int idx = ctx.tid; idx < nrows * W; idx += ctx.nthr) {
+        const int r = idx / W;
+        const int n = idx - r * W;
+        float2 v;
+        if (n < Mo) {
+            v = DFT_LDG(src + r * Mo + n);
+        } else {
+            v = DFT_LDG(src + r * Mo + (W - n));
+            v.y = -v.y;
+        }
+        buf[idx] = v;
+    }
+    ctx.sync();
+    run_line_fft(p.row, false, buf, nrows, W, p.tw_row, 0, 0, ctx);
+    float* o = out + first * W;
+    const float sc = p.scale;
+    for (int idx = ctx.tid; idx < nrows * W; idx += ctx.nthr) {
+        const int r = idx / W;
+        const int n = idx - r * W;
+        o[idx] = buf[r * W + DFT_LDG(p.perm_row + n)].x * sc;
+    }
+    ctx.sync();
+}
+
+// ---- MODE_C2C_COLS: data[outer][N][inner]; tile = (slab o, chunk c of G columns) ------------------
+template <class Ctx>
+DFT_HD void program_cols(const KParams& p, long long tile, float2* buf, const float* in, float* out, Ctx& ctx)
+{
+    const int N = p.H, P = p.P;
+    const long long o_ = tile / p.chunks;
+    const long long c_ = tile - o_ * p.chunks;
+    const long long col0 = c_ * p.G;
+    const int ncol = (int)((p.inner - col0) < p.G ? (p.inner - col0) : p.G);
+    const float2* src = (const float2*)in + o_ * N * p.inner + col0;
+    const int total = N * ncol;
+    for (int idx = ctx.tid; idx < total; idx += ctx.nthr) {
+        const int n = idx / ncol;
+        const int j = idx - n * ncol;
+        buf[n * P + j] = DFT_LDG(src + (long long)n * p.inner + j);
+    }
+    ctx.sync();
+    run_line_fft(p.col, true, buf, ncol, P, p.tw_col, ncol, 0, ctx);
+    float2* dst = (float2*)out + o_ * N * p.inner + col0;
+    const float sc = p.scale;
+    for (int idx = ctx.tid; idx < total; idx += ctx.nthr) {
+        const int q = idx / ncol;
+        const int j = idx - q * ncol;
+        const float2 z = buf[DFT_LDG(p.perm_col + q) * P + j];
+        dst[(long long)q * p.inner + j] = float2{z.x * sc, z.y * sc};
+    }
+    ctx.sync();
+}
+
+template <class Ctx>
+DFT_HD void run_tile(const KParams& p, long long tile, float2* buf, const float* in, float* out, Ctx& ctx)
+{
+    switch (p.mode) {
+        case MODE_F2D: program_f2d(p, tile, buf, in, out, ctx); break;
+        case MODE_I2D: program_i2d(p, tile, buf, in, out, ctx); break;
+        case MODE_F1D: program_f1d(p, tile, buf, in, out, ctx); break;
+        case MODE_I1D: program_i1d(p, tile, buf, in, out, ctx); break;
+        case MODE_F1D_ODD: program_f1d_odd(p, tile, buf, in, out, ctx); break;
+        case MODE_I1D_ODD: program_i1d_odd(p, tile, buf, in, out, ctx); break;
+        case MODE_C2C_COLS: program_cols(p, tile, buf, in, out, ctx); break;
+        default: break;
+    }
+}
+
+// ---- naive O(N^2) passes: any length, used only when a length has a prime factor the radix set
+// does not cover or a line does not fit in shared memory.  One output element per index.
+// tw = w_n^j table of the axis length; sign < 0 forward, > 0 inverse.
+DFT_HD void naive_rows_r2c_elem(const KParams& p, long long idx, const float* in, float* out)
+{
+    const int W = p.W, Mo = p.W / 2 + 1;
+    const long long r = idx / Mo;
+    const int k = (int)(idx - r * Mo);
+    const float* x = in + r * W;
+    double sr = 0.0, si = 0.0;
+    for (int n = 0; n < W; ++n) {
+        const float2 w = DFT_LDG(p.tw_row + (int)(((long long)n * k) % W));
+        const double v = (double)DFT_LDG(x + n);
+        sr += v * w.x;
+        si += v * w.y;
+    }
+    ((float2*)out)[idx] = float2{(float)sr, (float)si};
+}
+
+DFT_HD void naive_rows_c2r_elem(const KParams& p, long long idx, const float* in, float* out)
+{
+    const int W = p.W, Mo = p.W / 2 + 1;
+    const long long r = idx / W;
+    const int n = (int)(idx - r * W);
+    const float2* X = (const float2*)in + r * Mo;
+    double s = (double)DFT_LDG(X).x;
+    for (int k = 1; k < Mo; ++k) {
+        const float2 w = DFT_LDG(p.tw_row + (int)(((long long)n * k) % W));  // (c, -s); inverse uses conj
+        const float2 v = DFT_LDG(X + k);
+        if (2 * k == W)
+            s += (double)v.x * w.x;
+        else
+            s += 2.0 * ((double)v.x * w.x + (double)v.y * w.y);
+    }
+    out[idx] = (float)(s * (double)p.scale);
+}
+
+// data[outer][N][inner], out-of-place; p.W != 0 selects the inverse sign.
+DFT_HD void naive_cols_elem(const KParams& p, long long idx, const float* in, float* out)
+{
+    const int N = p.H;
+    const long long slab = (long long)N * p.inner;
+    const long long o_ = idx / slab;
+    const long long rem = idx - o_ * slab;
+    const int q = (int)(rem / p.inner);
+    const long long i = rem - (long long)q * p.inner;
+    const float2* src = (const float2*)in + o_ * slab + i;
+    const double sg = p.W ? -1.0 : 1.0;
+    double sr = 0.0, si = 0.0;
+    for (int n = 0; n < N; ++n) {
+        const float2 w = DFT_LDG(p.tw_col + (int)(((long long)n * q) % N));
+        const float2 v = DFT_LDG(src + (long long)n * p.inner);
+        const double wy = sg * w.y;
+        sr += (double)v.x * w.x - (double)v.y * wy;
+        si += (double)v.x * wy + (double)v.y * w.x;
+    }
+    ((float2*)out)[idx] = float2{(float)(sr * p.scale), (float)(si * p.scale)};
+}
+
+}  // namespace dft

@@ -1,0 +1,66 @@
+// dft_types.h -- plain structs shared by the host planner, the CUDA kernels and the
+// test-only host emulator.  No CUDA runtime calls in here.
+#pragma once
+#include <stdint.h>
+#include <vector_types.h>   // float2 (host-compatible header from the CUDA toolkit)
+
+#if defined(__CUDACC__)
+#define DFT_HD __host__ __device__ __forceinline__
+#else
+#define DFT_HD inline
+#endif
+
+namespace dft {
+
+constexpr int kMaxSteps = 8;
+
+// Radix schedule of one in-place, decimation-in-frequency complex FFT of length n.
+// Step i works on blocks of length L_i = radix[i]*...*radix[nsteps-1]; frequency
+// k = c_0 + r_0*(c_1 + r_1*(...)) ends at position sum_i c_i * (L_i / r_i).
+struct LineFFT {
+    int n;
+    int nsteps;
+    int radix[kMaxSteps];
+};
+
+enum Mode : int {
+    MODE_F2D = 0,       // fused rfft2: real image [H][W] (W = 2M) -> complex [H][M+1]
+    MODE_I2D = 1,       // fused irfft2
+    MODE_F1D = 2,       // batched rows R2C, W = 2M
+    MODE_I1D = 3,       // batched rows C2R, W = 2M
+    MODE_F1D_ODD = 4,   // batched rows R2C, odd W (full complex FFT of zero-imag rows)
+    MODE_I1D_ODD = 5,   // batched rows C2R, odd W (Hermitian extension, full complex FFT)
+    MODE_C2C_COLS = 6,  // batched complex FFT along a strided axis: data[outer][N][inner]
+    MODE_NAIVE_ROWS_R2C = 7,
+    MODE_NAIVE_ROWS_C2R = 8,
+    MODE_NAIVE_COLS = 9,
+};
+
+// One kernel launch.  All pointers are device pointers (host pointers in the emulator).
+struct KParams {
+    int mode;
+    int threads;             // CTA size
+    int smem_bytes;          // dynamic shared memory
+    long long ntiles;        // persistent loop bound
+    long long nunits;        // images (2-D modes) / rows (1-D modes) / outer*chunks (cols)
+    int G;                   // units per tile (2-D: images, 1-D: rows); cols: columns per tile (TM)
+    int H;                   // 2-D: rows per image; cols mode: FFT length N
+    int M;                   // complex row-FFT length (W/2 for even W, W for odd W)
+    int W;                   // real row length
+    int P;                   // shared-memory pitch in complex elements
+    LineFFT row;             // FFT along the contiguous axis (length M)
+    LineFFT col;             // FFT along the strided axis (length H)
+    const float2* tw_row;    // w_M^j,  j in [0,M)        w_n = exp(-2*pi*i/n)
+    const float2* tw_col;    // w_H^j,  j in [0,H)
+    const float2* tw_unt;    // w_W^k,  k in [0,M]        (real-FFT split twiddles)
+    const int* perm_row;     // smem position of output index k of the row FFT
+    const int* perm_col;     // smem position of output index q of the column FFT
+    float scale;             // applied when the result is stored
+    long long inner;         // cols mode: contiguous inner extent (complex elements)
+    long long outer;         // cols mode: number of [N][inner] slabs
+    long long chunks;        // cols mode: column chunks per slab = ceil(inner / G)
+    int in_place_ok;         // informational
+    int io_align;            // 16 if in/out base pointers and unit strides allow 16-byte bulk copies
+};
+
+}  // namespace dft
