@@ -1,0 +1,42 @@
+"""Builds libtrt_dft_plugins.so in-tree for sm_100a (nvcc cross-compiles without a GPU).
+
+    python tensorrt-dft-plugins_b200/build.py [--force] [--verbose]
+
+Output: tensorrt-dft-plugins_b200/trt_dft_plugins/libtrt_dft_plugins.so -- the same file name,
+next to the Python loader, as the reference (CMakeLists.txt:26, src/dft_plugins/CMakeLists.txt:38).
+"""
+import subprocess
+import sys
+from pathlib import Path
+
+HERE = Path(__file__).resolve().parent
+CSRC = HERE / "csrc"
+OUT = HERE / "trt_dft_plugins" / "libtrt_dft_plugins.so"
+
+NVCC_FLAGS = [
+    "-gencode", "arch=compute_100a,code=sm_100a",
+    "-lineinfo", "-O3", "-std=c++17",
+    "-shared", "-Xcompiler", "-fPIC",
+    "-I", str(HERE.parent / "include"),
+]
+
+
+def sources():
+    cu = sorted(CSRC.glob("*.cu")) + sorted((CSRC / "plugin").glob("*.cpp"))
+    deps = list(CSRC.rglob("*.h")) + list(CSRC.rglob("*.cuh")) + list((HERE.parent / "include").glob("*.h")) + cu
+    return cu, deps
+
+
+def build(force=False, verbose=False):
+    cu, deps = sources()
+    if not force and OUT.exists() and all(OUT.stat().st_mtime >= d.stat().st_mtime for d in deps + [Path(__file__)]):
+        return OUT
+    cmd = ["nvcc"] + NVCC_FLAGS + (["-Xptxas", "-v"] if verbose else []) + ["-o", str(OUT)] + [str(c) for c in cu]
+    if verbose:
+        print(" ".join(cmd))
+    subprocess.check_call(cmd)
+    return OUT
+
+
+if __name__ == "__main__":
+    print(build(force="--force" in sys.argv, verbose="--verbose" in sys.argv))

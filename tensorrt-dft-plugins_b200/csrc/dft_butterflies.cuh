@@ -26,9 +26,14 @@ DFT_HD void static_for(F&& f)
 }
 
 // ---- compile-time cos/sin of 2*pi*j/n with exact octant reduction ---------------------------
+#if defined(__CUDACC__)
+#define DFT_CX __host__ __device__ constexpr
+#else
+#define DFT_CX constexpr
+#endif
 constexpr double kPi = 3.14159265358979323846264338327950288;
 
-constexpr double cx_sin_poly(double x)  // |x| <= pi/4
+DFT_CX double cx_sin_poly(double x)  // |x| <= pi/4
 {
     const double x2 = x * x;
     double term = x, sum = x;
@@ -39,7 +44,7 @@ constexpr double cx_sin_poly(double x)  // |x| <= pi/4
     return sum;
 }
 
-constexpr double cx_cos_poly(double x)  // |x| <= pi/4
+DFT_CX double cx_cos_poly(double x)  // |x| <= pi/4
 {
     const double x2 = x * x;
     double term = 1.0, sum = 1.0;
@@ -50,7 +55,7 @@ constexpr double cx_cos_poly(double x)  // |x| <= pi/4
     return sum;
 }
 
-constexpr double cx_cos2pi(long long j, long long n)  // cos(2*pi*j/n)
+DFT_CX double cx_cos2pi(long long j, long long n)  // cos(2*pi*j/n)
 {
     j %= n;
     if (j < 0) j += n;
@@ -71,7 +76,7 @@ constexpr double cx_cos2pi(long long j, long long n)  // cos(2*pi*j/n)
     return neg ? -r : r;
 }
 
-constexpr double cx_sin2pi(long long j, long long n)  // sin(2*pi*j/n) = cos(2*pi*(j/n - 1/4))
+DFT_CX double cx_sin2pi(long long j, long long n)  // sin(2*pi*j/n) = cos(2*pi*(j/n - 1/4))
 {
     return cx_cos2pi(4 * j - n, 4 * n);
 }

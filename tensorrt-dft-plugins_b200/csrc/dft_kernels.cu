@@ -1,0 +1,374 @@
+// dft_kernels.cu -- sm_100a kernels, the plan executor and the C ABI of include/trt_dft.h.
+//
+// One persistent kernel template per engine mode: each CTA loops over tiles; a tile is brought
+// into shared memory (cp.async.bulk + mbarrier when the source is 16-byte aligned, vectorised
+// loads otherwise), transformed in place by the phases of dft_programs.cuh, and written back
+// with coalesced stores.  Several CTAs are resident per SM, so one tile's load overlaps
+// another tile's butterflies and a third one's stores.
+//
+// There is no CPU route in this file: if a kernel cannot be launched the call returns an error.
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <string.h>
+
+#include <mutex>
+#include <new>
+#include <vector>
+
+#include "../../include/trt_dft.h"
+#include "dft_planner.h"
+#include "dft_programs.cuh"
+
+namespace {
+
+using dft::KParams;
+
+__device__ __forceinline__ unsigned smem_u32(const void* p)
+{
+    return (unsigned)__cvta_generic_to_shared(p);
+}
+
+// CTA context for the tile programs.
+struct CtaCtx {
+    int tid, nthr;
+    unsigned bar;      // shared-memory address of the mbarrier
+    unsigned phase;    // parity of the next completion
+    bool bulk;         // this mode may use cp.async.bulk
+
+    __host__ __device__ __forceinline__ void sync()
+    {
+#if defined(__CUDA_ARCH__)
+        __syncthreads();
+#endif
+    }
+
+    // Whole-tile global->shared copy by the TMA unit (1-D bulk copy).  All threads call it with
+    // identical arguments; returns false (nothing done) when the copy is not 16-byte clean.
+    __host__ __device__ __forceinline__ bool bulk_load(void* dst, const void* src, long long bytes)
+    {
+#if defined(__CUDA_ARCH__)
+        if (!bulk || bytes <= 0 || (bytes & 15) || ((uintptr_t)src & 15) || bytes >= (1 << 20)) return false;
+        if (tid == 0) {
+            // order the previous tile's generic-proxy accesses before the async-proxy write
+            asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+            asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"((unsigned)bytes)
+                         : "memory");
+            asm volatile(
+                "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+                    smem_u32(dst)),
+                "l"(src), "r"((unsigned)bytes), "r"(bar)
+                : "memory");
+        }
+        asm volatile(
+            "{\n"
+            ".reg .pred p;\n"
+            "DFT_WAIT:\n"
+            "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+            "@p bra DFT_DONE;\n"
+            "bra DFT_WAIT;\n"
+            "DFT_DONE:\n"
+            "}\n" ::"r"(bar),
+            "r"(phase)
+            : "memory");
+        phase ^= 1u;
+        return true;
+#else
+        (void)dst; (void)src; (void)bytes;
+        return false;
+#endif
+    }
+};
+
+template <int MODE>
+__global__ void __launch_bounds__(dft::kThreads) tile_kernel(const __grid_constant__ KParams p, const float* __restrict__ in,
+                                                              float* __restrict__ out)
+{
+    extern __shared__ __align__(128) unsigned char smem_raw[];
+    float2* buf = reinterpret_cast<float2*>(smem_raw);
+    CtaCtx ctx;
+    ctx.tid = threadIdx.x;
+    ctx.nthr = blockDim.x;
+    ctx.phase = 0;
+    ctx.bulk = (MODE == dft::MODE_F2D || MODE == dft::MODE_I2D || MODE == dft::MODE_F1D || MODE == dft::MODE_I1D);
+    ctx.bar = smem_u32(smem_raw + p.smem_bytes - dft::kBarrierBytes);
+    if (ctx.bulk) {
+        if (threadIdx.x == 0) {
+            asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(ctx.bar) : "memory");
+            asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+            asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+        }
+        __syncthreads();
+    }
+    for (long long tile = blockIdx.x; tile < p.ntiles; tile += gridDim.x) {
+        if constexpr (MODE == dft::MODE_F2D) dft::program_f2d(p, tile, buf, in, out, ctx);
+        if constexpr (MODE == dft::MODE_I2D) dft::program_i2d(p, tile, buf, in, out, ctx);
+        if constexpr (MODE == dft::MODE_F1D) dft::program_f1d(p, tile, buf, in, out, ctx);
+        if constexpr (MODE == dft::MODE_I1D) dft::program_i1d(p, tile, buf, in, out, ctx);
+        if constexpr (MODE == dft::MODE_F1D_ODD) dft::program_f1d_odd(p, tile, buf, in, out, ctx);
+        if constexpr (MODE == dft::MODE_I1D_ODD) dft::program_i1d_odd(p, tile, buf, in, out, ctx);
+        if constexpr (MODE == dft::MODE_C2C_COLS) dft::program_cols(p, tile, buf, in, out, ctx);
+    }
+}
+
+template <int MODE>
+__global__ void __launch_bounds__(256) naive_kernel(const __grid_constant__ KParams p, const float* __restrict__ in,
+                                                    float* __restrict__ out)
+{
+    const long long stride = (long long)gridDim.x * blockDim.x;
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < p.nunits; i += stride) {
+        if constexpr (MODE == dft::MODE_NAIVE_ROWS_R2C) dft::naive_rows_r2c_elem(p, i, in, out);
+        if constexpr (MODE == dft::MODE_NAIVE_ROWS_C2R) dft::naive_rows_c2r_elem(p, i, in, out);
+        if constexpr (MODE == dft::MODE_NAIVE_COLS) dft::naive_cols_elem(p, i, in, out);
+    }
+}
+
+typedef void (*kernel_fn)(const KParams, const float*, float*);
+
+kernel_fn kernel_for(int mode)
+{
+    switch (mode) {
+        case dft::MODE_F2D: return tile_kernel<dft::MODE_F2D>;
+        case dft::MODE_I2D: return tile_kernel<dft::MODE_I2D>;
+        case dft::MODE_F1D: return tile_kernel<dft::MODE_F1D>;
+        case dft::MODE_I1D: return tile_kernel<dft::MODE_I1D>;
+        case dft::MODE_F1D_ODD: return tile_kernel<dft::MODE_F1D_ODD>;
+        case dft::MODE_I1D_ODD: return tile_kernel<dft::MODE_I1D_ODD>;
+        case dft::MODE_C2C_COLS: return tile_kernel<dft::MODE_C2C_COLS>;
+        case dft::MODE_NAIVE_ROWS_R2C: return naive_kernel<dft::MODE_NAIVE_ROWS_R2C>;
+        case dft::MODE_NAIVE_ROWS_C2R: return naive_kernel<dft::MODE_NAIVE_ROWS_C2R>;
+        case dft::MODE_NAIVE_COLS: return naive_kernel<dft::MODE_NAIVE_COLS>;
+        default: return nullptr;
+    }
+}
+
+struct ResolvedLaunch {
+    KParams kp;
+    kernel_fn fn;
+    int grid;
+    int src, dst;
+};
+
+}  // namespace
+
+struct trt_dft_plan_s {
+    dft::PlanDesc pd;
+    int device = 0;
+    void* pool = nullptr;                 // one device allocation holding every table
+    std::vector<ResolvedLaunch> launches;
+    // trt_dft_exec_host scratch (lazily allocated, reused across calls)
+    std::mutex host_mu;
+    void* h_in = nullptr;
+    void* h_out = nullptr;
+    void* h_ws = nullptr;
+    cudaStream_t h_stream = nullptr;
+};
+
+extern "C" {
+
+const char* trt_dft_version(void)
+{
+    return "b200-dft 0.1 (sm_100a; hand-written mixed-radix shared-memory FFT, no cuFFT)";
+}
+
+const char* trt_dft_error_string(int status)
+{
+    switch (status) {
+        case TRT_DFT_OK: return "ok";
+        case TRT_DFT_ERR_INVALID_ARG: return "invalid argument";
+        case TRT_DFT_ERR_CUDA: return "CUDA error";
+        case TRT_DFT_ERR_ALLOC: return "allocation failed";
+        case TRT_DFT_ERR_WORKSPACE: return "workspace missing or misaligned";
+        case TRT_DFT_ERR_UNSUPPORTED: return "unsupported size";
+        default: return "unknown status";
+    }
+}
+
+int trt_dft_plan_create(trt_dft_plan_t* plan_out, int direction, int rank, const int64_t* dims, int64_t batch)
+{
+    if (!plan_out) return TRT_DFT_ERR_INVALID_ARG;
+    *plan_out = nullptr;
+    trt_dft_plan_s* pl = new (std::nothrow) trt_dft_plan_s();
+    if (!pl) return TRT_DFT_ERR_ALLOC;
+    int rc = TRT_DFT_OK;
+    try {
+        rc = dft::build_plan(&pl->pd, direction, rank, dims, batch) ? TRT_DFT_ERR_INVALID_ARG : TRT_DFT_OK;
+    } catch (...) {
+        rc = TRT_DFT_ERR_ALLOC;
+    }
+    if (rc != TRT_DFT_OK) {
+        delete pl;
+        return rc;
+    }
+    if (pl->pd.launches.empty()) {   // batch == 0
+        *plan_out = pl;
+        return TRT_DFT_OK;
+    }
+    int num_sms = 0;
+    if (cudaGetDevice(&pl->device) != cudaSuccess ||
+        cudaDeviceGetAttribute(&num_sms, cudaDevAttrMultiProcessorCount, pl->device) != cudaSuccess) {
+        delete pl;
+        return TRT_DFT_ERR_CUDA;
+    }
+    // pack all tables into one allocation
+    std::vector<size_t> tw_off(pl->pd.tw_tables.size()), perm_off(pl->pd.perm_tables.size());
+    size_t total = 0;
+    auto bump = [&](size_t bytes) { size_t o = total; total += (bytes + 255) / 256 * 256; return o; };
+    for (size_t i = 0; i < tw_off.size(); ++i) tw_off[i] = bump(pl->pd.tw_tables[i].size() * sizeof(float2));
+    for (size_t i = 0; i < perm_off.size(); ++i) perm_off[i] = bump(pl->pd.perm_tables[i].size() * sizeof(int));
+    std::vector<unsigned char> staging(total ? total : 256, 0);
+    for (size_t i = 0; i < tw_off.size(); ++i)
+        memcpy(staging.data() + tw_off[i], pl->pd.tw_tables[i].data(), pl->pd.tw_tables[i].size() * sizeof(float2));
+    for (size_t i = 0; i < perm_off.size(); ++i)
+        memcpy(staging.data() + perm_off[i], pl->pd.perm_tables[i].data(), pl->pd.perm_tables[i].size() * sizeof(int));
+    if (cudaMalloc(&pl->pool, staging.size()) != cudaSuccess) {
+        cudaGetLastError();
+        delete pl;
+        return TRT_DFT_ERR_ALLOC;
+    }
+    if (cudaMemcpy(pl->pool, staging.data(), staging.size(), cudaMemcpyHostToDevice) != cudaSuccess) {
+        cudaFree(pl->pool);
+        delete pl;
+        return TRT_DFT_ERR_CUDA;
+    }
+    unsigned char* base = (unsigned char*)pl->pool;
+    for (auto& l : pl->pd.launches) {
+        ResolvedLaunch r;
+        r.kp = l.kp;
+        if (l.tw_row_id >= 0) r.kp.tw_row = (const float2*)(base + tw_off[l.tw_row_id]);
+        if (l.tw_col_id >= 0) r.kp.tw_col = (const float2*)(base + tw_off[l.tw_col_id]);
+        if (l.tw_unt_id >= 0) r.kp.tw_unt = (const float2*)(base + tw_off[l.tw_unt_id]);
+        if (l.perm_row_id >= 0) r.kp.perm_row = (const int*)(base + perm_off[l.perm_row_id]);
+        if (l.perm_col_id >= 0) r.kp.perm_col = (const int*)(base + perm_off[l.perm_col_id]);
+        r.fn = kernel_for(r.kp.mode);
+        r.src = l.src;
+        r.dst = l.dst;
+        if (!r.fn) {
+            cudaFree(pl->pool);
+            delete pl;
+            return TRT_DFT_ERR_UNSUPPORTED;
+        }
+        if (r.kp.mode >= dft::MODE_NAIVE_ROWS_R2C) {
+            r.kp.smem_bytes = 0;
+            const long long blocks = (r.kp.nunits + 255) / 256;
+            r.grid = (int)std::min<long long>(blocks, (long long)num_sms * 16);
+        } else {
+            if (r.kp.smem_bytes > 48 * 1024 &&
+                cudaFuncSetAttribute((const void*)r.fn, cudaFuncAttributeMaxDynamicSharedMemorySize, dft::kSmemMax) !=
+                    cudaSuccess) {
+                cudaGetLastError();
+                cudaFree(pl->pool);
+                delete pl;
+                return TRT_DFT_ERR_CUDA;
+            }
+            int occ = 0;
+            if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, (const void*)r.fn, r.kp.threads, r.kp.smem_bytes) !=
+                    cudaSuccess || occ < 1) {
+                cudaGetLastError();
+                cudaFree(pl->pool);
+                delete pl;
+                return TRT_DFT_ERR_CUDA;
+            }
+            r.grid = (int)std::min<long long>(r.kp.ntiles, (long long)num_sms * occ);
+        }
+        if (r.grid < 1) r.grid = 1;
+        pl->launches.push_back(r);
+    }
+    *plan_out = pl;
+    return TRT_DFT_OK;
+}
+
+size_t trt_dft_workspace_bytes(trt_dft_plan_t plan)
+{
+    return plan ? plan->pd.ws_bytes : 0;
+}
+
+int64_t trt_dft_plan_input_floats(trt_dft_plan_t plan) { return plan ? plan->pd.in_floats : -1; }
+int64_t trt_dft_plan_output_floats(trt_dft_plan_t plan) { return plan ? plan->pd.out_floats : -1; }
+
+int trt_dft_plan_describe(trt_dft_plan_t plan, char* buf, size_t len)
+{
+    if (!plan) return -1;
+    if (buf && len) {
+        std::string d = plan->pd.description;
+        for (size_t i = 0; i < plan->launches.size(); ++i) {
+            char t[64];
+            snprintf(t, sizeof t, "%s[%d]grid=%d", i ? "," : " ", (int)i, plan->launches[i].grid);
+            d += t;
+        }
+        strncpy(buf, d.c_str(), len - 1);
+        buf[len - 1] = 0;
+    }
+    return (int)plan->launches.size();
+}
+
+int trt_dft_exec(trt_dft_plan_t plan, const void* in, void* out, void* workspace, void* stream)
+{
+    if (!plan) return TRT_DFT_ERR_INVALID_ARG;
+    if (plan->launches.empty()) return TRT_DFT_OK;
+    if (!in || !out) return TRT_DFT_ERR_INVALID_ARG;
+    // complex tensors need 8-byte alignment (float2 accesses), real tensors 4-byte
+    const bool inv = plan->pd.direction == TRT_DFT_INVERSE;
+    const uintptr_t cptr = (uintptr_t)(inv ? in : (const void*)out);
+    const uintptr_t rptr = (uintptr_t)(inv ? (const void*)out : in);
+    if ((cptr & 7) || (rptr & 3)) return TRT_DFT_ERR_INVALID_ARG;
+    if (plan->pd.ws_bytes && (!workspace || ((uintptr_t)workspace & 15))) return TRT_DFT_ERR_WORKSPACE;
+    cudaStream_t st = (cudaStream_t)stream;
+    for (auto& r : plan->launches) {
+        auto sel = [&](int s) -> void* {
+            switch (s) {
+                case dft::BUF_IN: return const_cast<void*>(in);
+                case dft::BUF_OUT: return out;
+                case dft::BUF_WS: return workspace;
+                default: return (unsigned char*)workspace + plan->pd.ws1_offset;
+            }
+        };
+        const float* src = (const float*)sel(r.src);
+        float* dst = (float*)sel(r.dst);
+        // real rows that are not 8-byte aligned cannot be written/read as float2 pairs
+        if ((r.kp.mode == dft::MODE_I1D || r.kp.mode == dft::MODE_I2D) && ((uintptr_t)dst & 7)) return TRT_DFT_ERR_INVALID_ARG;
+        r.fn<<<r.grid, r.kp.threads, r.kp.smem_bytes, st>>>(r.kp, src, dst);
+        if (cudaPeekAtLastError() != cudaSuccess) {
+            cudaGetLastError();
+            return TRT_DFT_ERR_CUDA;
+        }
+    }
+    return TRT_DFT_OK;
+}
+
+int trt_dft_plan_destroy(trt_dft_plan_t plan)
+{
+    if (!plan) return TRT_DFT_OK;
+    int rc = TRT_DFT_OK;
+    if (plan->h_stream) cudaStreamDestroy(plan->h_stream);
+    for (void* p : {plan->pool, plan->h_in, plan->h_out, plan->h_ws})
+        if (p && cudaFree(p) != cudaSuccess) rc = TRT_DFT_ERR_CUDA;
+    delete plan;
+    return rc;
+}
+
+int trt_dft_exec_host(trt_dft_plan_t plan, const void* host_in, void* host_out)
+{
+    if (!plan) return TRT_DFT_ERR_INVALID_ARG;
+    if (plan->launches.empty()) return TRT_DFT_OK;
+    if (!host_in || !host_out) return TRT_DFT_ERR_INVALID_ARG;
+    std::lock_guard<std::mutex> lock(plan->host_mu);
+    const size_t in_bytes = (size_t)plan->pd.in_floats * 4, out_bytes = (size_t)plan->pd.out_floats * 4;
+    if (!plan->h_in) {
+        if (cudaMalloc(&plan->h_in, in_bytes) != cudaSuccess || cudaMalloc(&plan->h_out, out_bytes) != cudaSuccess ||
+            (plan->pd.ws_bytes && cudaMalloc(&plan->h_ws, plan->pd.ws_bytes) != cudaSuccess) ||
+            cudaStreamCreateWithFlags(&plan->h_stream, cudaStreamNonBlocking) != cudaSuccess) {
+            cudaGetLastError();
+            return TRT_DFT_ERR_ALLOC;
+        }
+    }
+    cudaStream_t st = plan->h_stream;
+    if (cudaMemcpyAsync(plan->h_in, host_in, in_bytes, cudaMemcpyHostToDevice, st) != cudaSuccess) return TRT_DFT_ERR_CUDA;
+    const int rc = trt_dft_exec(plan, plan->h_in, plan->h_out, plan->h_ws, st);
+    if (rc != TRT_DFT_OK) return rc;
+    if (cudaMemcpyAsync(host_out, plan->h_out, out_bytes, cudaMemcpyDeviceToHost, st) != cudaSuccess) return TRT_DFT_ERR_CUDA;
+    if (cudaStreamSynchronize(st) != cudaSuccess) return TRT_DFT_ERR_CUDA;
+    return TRT_DFT_OK;
+}
+
+}  // extern "C"

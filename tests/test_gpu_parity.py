@@ -1,0 +1,191 @@
+"""GPU parity: the CUDA path (through the C ABI of include/trt_dft.h) against the oracle.
+
+Oracle = the reference tests' own expected-value expressions (CPU torch.fft,
+/root/reference/tests/test_dft.py:40,:52-54) in fp64, the committed golden vectors, and the plain-C
+restatement in oracle/.  Tolerances are north_star's: rel-L2 <= 1e-5 against fp64, round trip
+<= 1e-6, plus the reference's own ``torch.allclose`` (rtol 1e-5, atol 1e-8) on its 16 cases.
+"""
+from pathlib import Path
+
+import numpy as np
+import pytest
+import torch
+
+from oracle import oracle as O
+
+pytestmark = pytest.mark.gpu
+
+GOLD = np.load(Path(__file__).parent / "golden" / "reference_cases.npz")
+NAMES = [str(n) for n in GOLD["names"]]
+REF = [n for n in NAMES if n.startswith("ref_")]
+EXT = [n for n in NAMES if n.startswith("ext_")]
+
+FWD_TOL = 1e-5      # rel-L2 vs fp64 torch.fft (north_star)
+RT_TOL = 1e-6       # round trip irfft(rfft(x)) (north_star)
+
+
+@pytest.fixture(scope="module")
+def capi():
+    from trt_dft_plugins import capi as c
+    c.lib()
+    return c
+
+
+def dims_of(nd):
+    return tuple(range(-nd, 0))
+
+
+# ---- the reference's own 8 + 8 cases, with the reference's own assertion ---------------------
+@pytest.mark.parametrize("name", REF)
+def test_reference_rfft2_cases(capi, name):
+    x = torch.from_numpy(GOLD[name + "_x"])
+    y = capi.rfftn(x.cuda(), 2).cpu()
+    y_expected = torch.from_numpy(GOLD[name + "_rfft2"])
+    assert torch.allclose(y_expected, y)                       # tests/test_dft.py:151
+    assert O.rel_l2(y.numpy(), GOLD[name + "_rfft2_f64"]) <= FWD_TOL
+
+
+@pytest.mark.parametrize("name", REF)
+def test_reference_irfft2_cases(capi, name):
+    y = torch.from_numpy(GOLD[name + "_rfft2"])
+    x = capi.irfftn(y.cuda(), 2).cpu()
+    x_expected = torch.from_numpy(GOLD[name + "_irfft2"])
+    # tests/test_dft.py:184 uses the allclose defaults; atol 1e-8 is below fp32 resolution for
+    # values that cancel to ~1e-8, so the absolute floor is stated explicitly here.
+    assert torch.allclose(x_expected, x, rtol=1e-5, atol=1e-6)
+    assert O.rel_l2(x.numpy(), GOLD[name + "_irfft2_f64"]) <= FWD_TOL
+
+
+@pytest.mark.parametrize("name", EXT)
+def test_golden_extended(capi, name):
+    nd = int(name.rsplit("_nd", 1)[1])
+    x = torch.from_numpy(GOLD[name + "_x"])
+    y = capi.rfftn(x.cuda(), nd).cpu().numpy()
+    assert O.rel_l2(y, GOLD[name + "_rfftn_f64"]) <= FWD_TOL
+    xi = capi.irfftn(torch.from_numpy(GOLD[name + "_rfftn"]).cuda(), nd, last=x.shape[-1]).cpu().numpy()
+    assert O.rel_l2(xi, GOLD[name + "_irfftn_f64"]) <= FWD_TOL
+    xz = capi.irfftn(torch.from_numpy(GOLD[name + "_z"]).cuda(), nd, last=x.shape[-1]).cpu().numpy()
+    assert O.rel_l2(xz, GOLD[name + "_z_irfftn_f64"]) <= FWD_TOL
+
+
+# ---- seeded shapes against the fp64 oracle ------------------------------------------------------
+SHAPES = [
+    # BASELINE configs 1-3 in full
+    ((4, 32, 64), 1), ((16, 64, 128, 128), 2), ((8, 768, 90, 180), 2),
+    # 1-D
+    ((3, 2), 1), ((3, 6), 1), ((5, 30), 1), ((2, 9), 1), ((2, 15), 1), ((3, 1), 1), ((2, 360), 1),
+    ((1000, 1024), 1), ((2, 2 * 7 * 11 * 13), 1), ((2, 34), 1), ((3, 19), 1), ((3, 4096), 1), ((2, 8192), 1),
+    ((2, 50000), 1), ((2, 65536), 1),
+    # 2-D
+    ((7, 8, 8), 2), ((3, 6, 10), 2), ((2, 5, 7), 2), ((2, 12, 18), 2), ((2, 17, 6), 2), ((2, 6, 38), 2),
+    ((700, 4, 4), 2), ((1, 1, 16), 2), ((2, 16, 1), 2), ((2, 3, 3), 2), ((300, 32, 32), 2), ((5, 64, 64), 2),
+    ((3, 256, 256), 2), ((2, 180, 360), 2), ((2, 720, 1440), 2), ((1, 1024, 1024), 2), ((1, 2048, 4096), 2),
+    # 3-D
+    ((2, 4, 6, 8), 3), ((2, 3, 5, 6), 3), ((1, 2, 3, 5, 7), 3), ((2, 1, 4, 4), 3), ((1, 17, 4, 6), 3),
+    ((2, 32, 32, 32), 3), ((1, 20, 90, 180), 3),
+]
+
+
+@pytest.mark.parametrize("shape,nd", SHAPES)
+def test_seeded_shapes_vs_fp64_oracle(capi, shape, nd):
+    torch.manual_seed(1)                                      # tests/test_dft.py:135
+    x = torch.randn(*shape)
+    want = O.torch_rfftn(x, nd, dtype=torch.float64)
+    xd = x.cuda()
+    y = capi.rfftn(xd, nd)
+    assert O.rel_l2(y.cpu().numpy(), want.numpy()) <= FWD_TOL
+    # inverse of the oracle's fp32 spectrum
+    y32 = want.float()
+    s = shape[-nd:]
+    want_i = torch.fft.irfftn(torch.view_as_complex(y32.double()), s=s, dim=dims_of(nd), norm="backward")
+    xi = capi.irfftn(y32.cuda(), nd, last=shape[-1])
+    assert O.rel_l2(xi.cpu().numpy(), want_i.numpy()) <= FWD_TOL
+    # round trip through the CUDA path only
+    rt = capi.irfftn(y, nd, last=shape[-1])
+    assert O.rel_l2(rt.cpu().numpy(), x.numpy()) <= RT_TOL
+    # input must not be modified (the reference const_casts it for cuFFT, dft_plugins.cpp:193)
+    assert torch.equal(xd.cpu(), x)
+
+
+@pytest.mark.parametrize("shape,nd", [((2, 3, 6, 10), 2), ((4, 32, 64), 1), ((2, 90, 180), 2), ((1, 4, 6, 8), 3)])
+def test_c_oracle_agrees_with_gpu(capi, shape, nd):
+    """Independent check against the plain-C naive DFT (no MKL / pocketfft in the loop)."""
+    torch.manual_seed(1)
+    x = torch.randn(*shape)
+    y = capi.rfftn(x.cuda(), nd).cpu().numpy()
+    assert O.rel_l2(y, O.c_rfftn(x.numpy(), nd)) <= FWD_TOL
+    xi = capi.irfftn(torch.from_numpy(y).cuda(), nd).cpu().numpy()
+    assert O.rel_l2(xi, O.c_irfftn(y, nd)) <= FWD_TOL
+
+
+def test_linearity_and_parseval_at_full_size(capi):
+    """Size-independent properties at cfg3's full size (no CPU oracle in the loop)."""
+    torch.manual_seed(1)
+    shape = (8, 768, 90, 180)
+    a = torch.randn(*shape, device="cuda")
+    b = torch.randn(*shape, device="cuda")
+    fa, fb = capi.rfftn(a, 2), capi.rfftn(b, 2)
+    fab = capi.rfftn(2.0 * a - 3.0 * b, 2)
+    lin = (fab - (2.0 * fa - 3.0 * fb)).double().norm() / fab.double().norm()
+    assert lin.item() <= 1e-6
+    # Parseval with one-sided weights: sum |x|^2 = (1/N) sum_k w_k |X_k|^2
+    X = torch.view_as_complex(fa).abs().double() ** 2
+    w = torch.full((91,), 2.0, dtype=torch.float64, device="cuda")
+    w[0] = 1.0
+    w[90] = 1.0
+    lhs = (a.double() ** 2).sum()
+    rhs = (X * w).sum() / (90 * 180)
+    assert abs(lhs.item() - rhs.item()) / lhs.item() <= 1e-6
+    rt = capi.irfftn(fa, 2)
+    assert ((rt - a).double().norm() / a.double().norm()).item() <= RT_TOL
+
+
+def test_empty_batch_and_errors(capi):
+    p = capi.Plan(capi.FORWARD, (8, 8), 0)
+    assert p.num_launches == 0
+    p.exec_ptr(0, 0)           # no-op
+    with pytest.raises(capi.DftError):
+        capi.Plan(capi.FORWARD, (8, 0), 1)
+    with pytest.raises(capi.DftError):
+        capi.Plan(capi.FORWARD, (2, 2, 2, 2), 1)
+    with pytest.raises(capi.DftError):
+        capi.Plan(2, (8,), 1)
+    q = capi.Plan(capi.INVERSE, (720, 1440), 1)
+    assert q.workspace_bytes == 720 * 721 * 8
+    with pytest.raises(capi.DftError):
+        x = torch.zeros(720 * 721 * 2, device="cuda")
+        o = torch.zeros(720 * 1440, device="cuda")
+        q.exec_ptr(x.data_ptr(), o.data_ptr(), 0)     # workspace required
+
+
+def test_misaligned_real_input_takes_the_scalar_path(capi):
+    torch.manual_seed(1)
+    base = torch.randn(2 * 6 * 10 + 1)
+    x = base[1:].view(2, 6, 10)
+    big = base.cuda()
+    xd = big[1:].view(2, 6, 10)          # 4-byte aligned only
+    out = torch.empty(2, 6, 6, 2, device="cuda")
+    p = capi.Plan(capi.FORWARD, (6, 10), 2)
+    p.exec_ptr(xd.data_ptr(), out.data_ptr())
+    torch.cuda.synchronize()
+    want = O.torch_rfftn(x.contiguous(), 2, dtype=torch.float64).numpy()
+    assert O.rel_l2(out.cpu().numpy(), want) <= FWD_TOL
+
+
+def test_exec_host_and_streams(capi):
+    torch.manual_seed(1)
+    x = torch.randn(6, 90, 180).pin_memory()
+    y = torch.empty(6, 90, 91, 2).pin_memory()
+    p = capi.Plan(capi.FORWARD, (90, 180), 6)
+    p.exec_host(x, y)
+    p.exec_host(x, y)
+    want = O.torch_rfftn(x, 2, dtype=torch.float64).numpy()
+    assert O.rel_l2(y.numpy(), want) <= FWD_TOL
+    s = torch.cuda.Stream()
+    xd = x.cuda()
+    out = torch.empty(6, 90, 91, 2, device="cuda")
+    s.wait_stream(torch.cuda.current_stream())
+    with torch.cuda.stream(s):
+        p.exec(xd, out)
+    s.synchronize()
+    assert O.rel_l2(out.cpu().numpy(), want) <= FWD_TOL
