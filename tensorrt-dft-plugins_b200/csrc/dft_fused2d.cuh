@@ -1,0 +1,350 @@
+// dft_fused2d.cuh -- shape-specialised fused rfft2 / irfft2 kernels (one image per tile).
+//
+// The whole image lives in shared memory exactly once: H x M complex for the forward
+// transform (the real row of W = 2M floats *is* the packed complex row z[n] = x[2n] + i x[2n+1]),
+// H x (M+1) complex for the inverse.  Row FFT length M = RA*RB, column FFT length H = CA*CB, each
+// done as two in-place decimation-in-frequency steps with register butterflies.  All geometry is
+// a template parameter, so every index is an immediate and every division a multiply-shift.
+//
+//   forward : TMA bulk load -> row step RA -> row step RB -> col step CA
+//             -> [col step CB + real-FFT split + coalesced global stores]      (no separate store pass)
+//   inverse : TMA bulk load -> col step CA -> [col step CB + Hermitian merge, rows to natural order]
+//             -> row step RA -> [row step RB, natural order, dense pitch, 1/(H*W)] -> TMA bulk store
+//
+// The 2-D real-FFT split uses  X[q][k] = (Y[q][k] + conj Y[H-q][M-k])/2 - (i/2) w_W^k (Y[q][k] - conj Y[H-q][M-k])
+// where Y is the full H x M complex 2-D FFT of the packed image; one thread owns both partner
+// butterflies, so the pair never goes back through shared memory.
+//
+// Algorithmic HBM bytes per image: H*W*4 + H*(M+1)*8 (read once, written once); the kernels move
+// exactly that.  3 CTAs are resident per SM (64.8 KB tile at 90x180), so one tile's load, another's
+// butterflies and a third's stores overlap.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "dft_butterflies.cuh"
+
+namespace dft {
+
+template <int H_, int W_, int RA_, int RB_, int CA_, int CB_, int NT_, int MINB_>
+struct FusedCfg {
+    static constexpr int H = H_, W = W_, M = W_ / 2, RA = RA_, RB = RB_, CA = CA_, CB = CB_, NT = NT_, MINB = MINB_;
+    static_assert(W_ % 2 == 0 && RA_ * RB_ == W_ / 2 && CA_ * CB_ == H_, "bad factorisation");
+    static constexpr int NTW_R = (RA - 1) * RB;   // twR[(c-1)*RB + b] = w_M^(b*c)
+    static constexpr int NTW_C = (CA - 1) * CB;   // twC[(c-1)*CB + b] = w_H^(b*c)
+    static constexpr int KH = M / 2 + 1;          // column pairs (k, M-k), k = 0..M/2
+    static constexpr int NTAB = NTW_R + NTW_C + KH;
+    static constexpr int PI = M + 1;              // inverse pitch (one-sided spectrum row)
+    static constexpr int SMEM_F = (H * M + NTAB) * 8 + 16;
+    static constexpr int SMEM_I = (H * PI + NTAB) * 8 + 16;
+    static constexpr bool BULK_REAL = (H * W * 4) % 16 == 0;
+    static constexpr bool BULK_CPLX = (H * PI * 8) % 16 == 0;
+};
+
+#if defined(__CUDACC__)
+
+__device__ __forceinline__ unsigned f2d_smem_u32(const void* p) { return (unsigned)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ void f2d_mbar_init(unsigned bar)
+{
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(bar) : "memory");
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+}
+
+// issue by one thread: 1-D TMA bulk copy global -> shared, completion on the mbarrier
+__device__ __forceinline__ void f2d_bulk_load(void* dst, const void* src, unsigned bytes, unsigned bar)
+{
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+                     f2d_smem_u32(dst)),
+                 "l"(src), "r"(bytes), "r"(bar)
+                 : "memory");
+}
+
+__device__ __forceinline__ void f2d_mbar_wait(unsigned bar, unsigned phase)
+{
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "F2D_WAIT:\n"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+        "@p bra F2D_DONE;\n"
+        "bra F2D_WAIT;\n"
+        "F2D_DONE:\n"
+        "}\n" ::"r"(bar),
+        "r"(phase)
+        : "memory");
+}
+
+// issue by one thread: 1-D TMA bulk copy shared -> global, then wait until the source was read
+__device__ __forceinline__ void f2d_bulk_store_and_wait(void* gdst, const void* ssrc, unsigned bytes)
+{
+    asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(gdst), "r"(f2d_smem_u32(ssrc)),
+                 "r"(bytes)
+                 : "memory");
+    asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+    asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
+}
+
+// ---- forward ---------------------------------------------------------------------------------
+template <class C>
+__global__ void __launch_bounds__(C::NT, C::MINB)
+    fused_rfft2_kernel(const float* __restrict__ in, float* __restrict__ out, long long nimg,
+                       const float2* __restrict__ tables, float /*scale: forward is unnormalised*/)
+{
+    constexpr int H = C::H, W = C::W, M = C::M, RA = C::RA, RB = C::RB, CA = C::CA, CB = C::CB, NT = C::NT;
+    constexpr int KH = C::KH, MO = M + 1;
+    extern __shared__ __align__(128) unsigned char smem_raw[];
+    float2* buf = reinterpret_cast<float2*>(smem_raw);
+    float2* twR = buf + H * M;
+    float2* twC = twR + C::NTW_R;
+    float2* twU = twC + C::NTW_C;            // 0.5 * w_W^k, k = 0..M/2
+    const unsigned bar = f2d_smem_u32(twU + KH);
+    const int tid = threadIdx.x;
+
+    for (int i = tid; i < C::NTAB; i += NT) twR[i] = __ldg(tables + i);
+    if (tid == 0) f2d_mbar_init(bar);
+    __syncthreads();
+    unsigned phase = 0;
+    const bool bulk = C::BULK_REAL && (((uintptr_t)in & 15) == 0);
+    const bool vec2 = (((uintptr_t)in & 7) == 0);
+
+    for (long long img = blockIdx.x; img < nimg; img += gridDim.x) {
+        const float* src = in + img * (long long)(H * W);
+        if (bulk) {
+            if (tid == 0) f2d_bulk_load(buf, src, H * W * 4, bar);
+            f2d_mbar_wait(bar, phase);
+            phase ^= 1u;
+        } else {
+            if (vec2) {
+                for (int i = tid; i < H * M; i += NT) buf[i] = __ldg(reinterpret_cast<const float2*>(src) + i);
+            } else {
+                float* bf = reinterpret_cast<float*>(buf);
+                for (int i = tid; i < H * W; i += NT) bf[i] = __ldg(src + i);
+            }
+            __syncthreads();
+        }
+
+        // rows, step RA: elements b + a*RB of each row
+#pragma unroll 1
+        for (int t = tid; t < H * RB; t += NT) {
+            const int row = t / RB, b = t - row * RB;
+            float2* p = buf + row * M + b;
+            float2 v[RA];
+            static_for<0, RA>([&](auto ac) { constexpr int a = decltype(ac)::value; v[a] = p[a * RB]; });
+            dft_reg<RA>(v);
+            static_for<1, RA>([&](auto cc) { constexpr int c = decltype(cc)::value; v[c] = cmul(v[c], twR[(c - 1) * RB + b]); });
+            static_for<0, RA>([&](auto cc) { constexpr int c = decltype(cc)::value; p[c * RB] = v[c]; });
+        }
+        __syncthreads();
+        // rows, step RB: RB contiguous elements; row frequency k = k1 + RA*k2 ends at k1*RB + k2
+#pragma unroll 1
+        for (int t = tid; t < H * RA; t += NT) {
+            float2* p = buf + t * RB;
+            float2 v[RB];
+            static_for<0, RB>([&](auto jc) { constexpr int j = decltype(jc)::value; v[j] = p[j]; });
+            dft_reg<RB>(v);
+            static_for<0, RB>([&](auto jc) { constexpr int j = decltype(jc)::value; p[j] = v[j]; });
+        }
+        __syncthreads();
+        // columns, step CA: rows b + a*CB of each column (threads run along the row: stride 1)
+#pragma unroll 1
+        for (int t = tid; t < CB * M; t += NT) {
+            const int b = t / M;
+            float2* p = buf + t;
+            float2 v[CA];
+            static_for<0, CA>([&](auto ac) { constexpr int a = decltype(ac)::value; v[a] = p[a * CB * M]; });
+            dft_reg<CA>(v);
+            static_for<1, CA>([&](auto cc) { constexpr int c = decltype(cc)::value; v[c] = cmul(v[c], twC[(c - 1) * CB + b]); });
+            static_for<0, CA>([&](auto cc) { constexpr int c = decltype(cc)::value; p[c * CB * M] = v[c]; });
+        }
+        __syncthreads();
+        // columns, step CB fused with the real-FFT split and the global stores
+        float2* oimg = reinterpret_cast<float2*>(out) + img * (long long)(H * MO);
+#pragma unroll 1
+        for (int t = tid; t < CA * KH; t += NT) {
+            const int q1 = t / KH, k = t - q1 * KH;
+            const int kk = (k == 0) ? 0 : M - k;
+            const int colA = (k % RA) * RB + k / RA;
+            const int colB = (kk % RA) * RB + kk / RA;
+            const int q1B = (q1 == 0) ? 0 : CA - q1;
+            const float2* pa = buf + q1 * CB * M + colA;
+            const float2* pb = buf + q1B * CB * M + colB;
+            float2 A[CB], B[CB];
+            static_for<0, CB>([&](auto jc) { constexpr int j = decltype(jc)::value; A[j] = pa[j * M]; B[j] = pb[j * M]; });
+            dft_reg<CB>(A);
+            dft_reg<CB>(B);
+            // A[k2] = Y[q1 + CA*k2][k]; its partner Y[(H-q) mod H][M-k] is B[CB-1-k2] (q1 > 0) or
+            // B[(CB-k2) mod CB] (q1 == 0): rotate B by one in the latter case.
+            if (q1 == 0) {
+                const float2 b0 = B[0];
+                static_for<0, CB - 1>([&](auto jc) { constexpr int j = decltype(jc)::value; B[j] = B[j + 1]; });
+                B[CB - 1] = b0;
+            }
+            const float2 wh = twU[k];
+            float2* oa = oimg + q1 * MO + k;                 // row q1 + CA*k2, column k
+            float2* ob = oimg + (H - q1) * MO + (M - k);     // row H - q1 - CA*k2, column M-k
+            static_for<0, CB>([&](auto kc) {
+                constexpr int k2 = decltype(kc)::value;
+                const float2 z1 = A[k2], z2 = B[CB - 1 - k2];
+                const float ex = 0.5f * (z1.x + z2.x), ey = 0.5f * (z1.y - z2.y);
+                const float dx = z1.x - z2.x, dy = z1.y + z2.y;
+                const float tx = wh.x * dx - wh.y * dy, ty = wh.x * dy + wh.y * dx;
+                oa[k2 * CA * MO] = float2{ex + ty, ey - tx};
+                float2* pbk = ob - k2 * CA * MO;
+                if (k2 == 0 && q1 == 0) pbk -= H * MO;       // (H - 0) mod H = 0
+                *pbk = float2{ex - ty, -ey - tx};
+            });
+        }
+        __syncthreads();
+    }
+}
+
+// ---- inverse ---------------------------------------------------------------------------------
+template <class C>
+__global__ void __launch_bounds__(C::NT, C::MINB)
+    fused_irfft2_kernel(const float* __restrict__ in, float* __restrict__ out, long long nimg,
+                        const float2* __restrict__ tables, float scale /* 1/prod(signal dims) */)
+{
+    constexpr int H = C::H, W = C::W, M = C::M, RA = C::RA, RB = C::RB, CA = C::CA, CB = C::CB, NT = C::NT;
+    constexpr int KH = C::KH, PI = C::PI;
+    extern __shared__ __align__(128) unsigned char smem_raw[];
+    float2* buf = reinterpret_cast<float2*>(smem_raw);
+    float2* twR = buf + H * PI;
+    float2* twC = twR + C::NTW_R;
+    float2* twU = twC + C::NTW_C;            // scale * w_W^k, k = 0..M/2
+    const unsigned bar = f2d_smem_u32(twU + KH);
+    const int tid = threadIdx.x;
+
+    for (int i = tid; i < C::NTAB; i += NT) twR[i] = __ldg(tables + i);
+    if (tid == 0) f2d_mbar_init(bar);
+    __syncthreads();
+    unsigned phase = 0;
+    const bool bulk_in = C::BULK_CPLX && (((uintptr_t)in & 15) == 0);
+    const bool bulk_out = C::BULK_REAL && (((uintptr_t)out & 15) == 0);
+
+    for (long long img = blockIdx.x; img < nimg; img += gridDim.x) {
+        const float2* src = reinterpret_cast<const float2*>(in) + img * (long long)(H * PI);
+        if (bulk_in) {
+            if (tid == 0) f2d_bulk_load(buf, src, H * PI * 8, bar);
+            f2d_mbar_wait(bar, phase);
+            phase ^= 1u;
+        } else {
+            for (int i = tid; i < H * PI; i += NT) buf[i] = __ldg(src + i);
+            __syncthreads();
+        }
+        // columns, step CA over all M+1 columns
+#pragma unroll 1
+        for (int t = tid; t < CB * PI; t += NT) {
+            const int b = t / PI;
+            float2* p = buf + t;
+            float2 v[CA];
+            static_for<0, CA>([&](auto ac) { constexpr int a = decltype(ac)::value; v[a] = p[a * CB * PI]; });
+            dft_reg<CA>(v);
+            static_for<1, CA>([&](auto cc) { constexpr int c = decltype(cc)::value; v[c] = cmul(v[c], twC[(c - 1) * CB + b]); });
+            static_for<0, CA>([&](auto cc) { constexpr int c = decltype(cc)::value; p[c * CB * PI] = v[c]; });
+        }
+        __syncthreads();
+        // columns, step CB on the column pair (k, M-k), Hermitian merge, rows written in natural order.
+        // Rounds hold whole column pairs (all CA row blocks), so read -> barrier -> write is race free.
+        {
+            constexpr int KPR = NT / CA;             // column pairs per round
+            constexpr int NTR = KPR * CA;
+#pragma unroll 1
+            for (int k0 = 0; k0 < KH; k0 += KPR) {
+                const int kl = tid / CA, q1 = tid - kl * CA;
+                const int k = k0 + kl;
+                const bool active = (tid < NTR) && (k < KH);
+                float2 A[CB], B[CB];
+                if (active) {
+                    const int kk = M - k;
+                    const float2* pa = buf + q1 * CB * PI + k;
+                    const float2* pb = buf + q1 * CB * PI + kk;
+                    static_for<0, CB>([&](auto jc) { constexpr int j = decltype(jc)::value; A[j] = pa[j * PI]; B[j] = pb[j * PI]; });
+                    dft_reg<CB>(A);
+                    dft_reg<CB>(B);
+                }
+                __syncthreads();
+                if (active) {
+                    const int kk = M - k;
+                    const float2 ws = twU[k];        // scale * (c, s) = scale * exp(-2 pi i k / W)
+                    static_for<0, CB>([&](auto kc) {
+                        constexpr int k2 = decltype(kc)::value;
+                        // position q1*CB + k2 holds column frequency q1 + CA*k2 = inverse row (H - that) mod H
+                        int r = H - q1 - CA * k2;
+                        if (k2 == 0 && q1 == 0) r = 0;
+                        const float2 a = A[k2], b = B[k2];
+                        float2* row = buf + r * PI;
+                        if (k == 0) {
+                            row[0] = float2{scale * (a.x + b.x), scale * (a.x - b.x)};
+                        } else {
+                            const float sx = a.x + b.x, sy = a.y - b.y;
+                            const float dx = a.x - b.x, dy = a.y + b.y;
+                            const float ux = ws.x * dx + ws.y * dy, uy = ws.x * dy - ws.y * dx;
+                            row[k] = float2{fmaf(scale, sx, -uy), fmaf(scale, sy, ux)};
+                            if (kk != k) row[kk] = float2{fmaf(scale, sx, uy), fmaf(-scale, sy, ux)};
+                        }
+                    });
+                }
+            }
+        }
+        __syncthreads();
+        // rows, step RA (pitch M+1)
+#pragma unroll 1
+        for (int t = tid; t < H * RB; t += NT) {
+            const int row = t / RB, b = t - row * RB;
+            float2* p = buf + row * PI + b;
+            float2 v[RA];
+            static_for<0, RA>([&](auto ac) { constexpr int a = decltype(ac)::value; v[a] = p[a * RB]; });
+            dft_reg<RA>(v);
+            static_for<1, RA>([&](auto cc) { constexpr int c = decltype(cc)::value; v[c] = cmul(v[c], twR[(c - 1) * RB + b]); });
+            static_for<0, RA>([&](auto cc) { constexpr int c = decltype(cc)::value; p[c * RB] = v[c]; });
+        }
+        __syncthreads();
+        // rows, step RB; results leave in natural order n = (M - f) mod M at dense pitch M.
+        // Rounds hold whole rows in increasing order: new row r (pitch M) only overlaps old rows r-1, r.
+        {
+            constexpr int RPR = NT / RA;             // rows per round
+            constexpr int NTR = RPR * RA;
+#pragma unroll 1
+            for (int r0 = 0; r0 < H; r0 += RPR) {
+                const int rl = tid / RA, k1 = tid - rl * RA;
+                const int row = r0 + rl;
+                const bool active = (tid < NTR) && (row < H);
+                float2 v[RB];
+                if (active) {
+                    const float2* p = buf + row * PI + k1 * RB;
+                    static_for<0, RB>([&](auto jc) { constexpr int j = decltype(jc)::value; v[j] = p[j]; });
+                    dft_reg<RB>(v);
+                }
+                __syncthreads();
+                if (active) {
+                    float2* d = buf + row * M;
+                    static_for<0, RB>([&](auto kc) {
+                        constexpr int k2 = decltype(kc)::value;
+                        int n = M - k1 - RA * k2;
+                        if (k2 == 0 && k1 == 0) n = 0;
+                        d[n] = v[k2];
+                    });
+                }
+            }
+        }
+        float* dst = out + img * (long long)(H * W);
+        if (bulk_out) {
+            asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+            __syncthreads();
+            if (tid == 0) f2d_bulk_store_and_wait(dst, buf, H * W * 4);
+            if (!bulk_in) __syncthreads();
+        } else {
+            __syncthreads();
+            for (int i = tid; i < H * M; i += NT) reinterpret_cast<float2*>(dst)[i] = buf[i];
+            __syncthreads();
+        }
+    }
+}
+
+#endif  // __CUDACC__
+
+}  // namespace dft

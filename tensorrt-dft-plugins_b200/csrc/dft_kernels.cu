@@ -10,6 +10,7 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 #include <stdio.h>
+#include <stdlib.h>
 #include <string.h>
 
 #include <mutex>
@@ -17,6 +18,7 @@
 #include <vector>
 
 #include "../../include/trt_dft.h"
+#include "dft_fused2d.cuh"
 #include "dft_planner.h"
 #include "dft_programs.cuh"
 
@@ -142,11 +144,67 @@ kernel_fn kernel_for(int mode)
     }
 }
 
+// ---- shape-specialised fused 2-D kernels (dft_fused2d.cuh) ------------------------------------
+typedef void (*spec_fn)(const float*, float*, long long, const float2*, float);
+
+struct SpecEntry {
+    int H, W, RA, RB, CA, CB, NT;
+    int smem_f, smem_i;
+    spec_fn fwd, inv;
+};
+
+template <class C>
+SpecEntry make_spec()
+{
+    return SpecEntry{C::H, C::W, C::RA, C::RB, C::CA, C::CB, C::NT, C::SMEM_F, C::SMEM_I,
+                     dft::fused_rfft2_kernel<C>, dft::fused_irfft2_kernel<C>};
+}
+
+const SpecEntry* find_spec(int H, int W)
+{
+    //                              H    W   RA  RB  CA  CB   NT  min CTAs/SM
+    static const SpecEntry table[] = {
+        make_spec<dft::FusedCfg<90, 180, 10, 9, 10, 9, 320, 3>>(),     // FourCastNet AFNO (BASELINE cfg3)
+        make_spec<dft::FusedCfg<128, 128, 8, 8, 16, 8, 256, 3>>(),     // FNO (BASELINE cfg2)
+        make_spec<dft::FusedCfg<64, 64, 8, 4, 8, 8, 256, 4>>(),
+    };
+    for (const auto& e : table)
+        if (e.H == H && e.W == W) return &e;
+    return nullptr;
+}
+
+// twR[(c-1)*RB + b] = w_M^(b c) | twC[(c-1)*CB + b] = w_H^(b c) | twU[k] = f * w_W^k, k = 0..M/2
+std::vector<float2> spec_tables(const SpecEntry& e, bool inverse, double scale)
+{
+    const int M = e.W / 2;
+    const double two_pi = 6.283185307179586476925286766559;
+    std::vector<float2> t;
+    for (int c = 1; c < e.RA; ++c)
+        for (int b = 0; b < e.RB; ++b) {
+            const double a = two_pi * (double)((b * c) % M) / M;
+            t.push_back(float2{(float)cos(a), (float)-sin(a)});
+        }
+    for (int c = 1; c < e.CA; ++c)
+        for (int b = 0; b < e.CB; ++b) {
+            const double a = two_pi * (double)((b * c) % e.H) / e.H;
+            t.push_back(float2{(float)cos(a), (float)-sin(a)});
+        }
+    const double f = inverse ? scale : 0.5;   // inverse: the plan's 1/prod(dims) rides on the merge twiddle
+    for (int k = 0; k <= M / 2; ++k) {
+        const double a = two_pi * (double)k / e.W;
+        t.push_back(float2{(float)(f * cos(a)), (float)(-f * sin(a))});
+    }
+    return t;
+}
+
 struct ResolvedLaunch {
     KParams kp;
     kernel_fn fn;
     int grid;
     int src, dst;
+    spec_fn spec = nullptr;          // non-null: launch the specialised kernel instead of fn
+    const float2* spec_tab = nullptr;
+    int spec_smem = 0, spec_nt = 0;
 };
 
 }  // namespace
@@ -210,6 +268,25 @@ int trt_dft_plan_create(trt_dft_plan_t* plan_out, int direction, int rank, const
         delete pl;
         return TRT_DFT_ERR_CUDA;
     }
+    // shape-specialised fused kernels bring their own (small) table
+    std::vector<int> spec_tab_id(pl->pd.launches.size(), -1);
+    std::vector<const SpecEntry*> spec_of(pl->pd.launches.size(), nullptr);
+    for (size_t i = 0; i < pl->pd.launches.size(); ++i) {
+        const KParams& k = pl->pd.launches[i].kp;
+        if (k.mode != dft::MODE_F2D && k.mode != dft::MODE_I2D) continue;
+        if (getenv("TRT_DFT_NO_SPEC")) continue;     // benchmarking override: force the generic engine
+        const SpecEntry* e = find_spec(k.H, k.W);
+        if (!e) continue;
+        spec_of[i] = e;
+        pl->pd.tw_tables.push_back(spec_tables(*e, k.mode == dft::MODE_I2D, (double)k.scale));
+        spec_tab_id[i] = (int)pl->pd.tw_tables.size() - 1;
+        pl->pd.launches[i].name += " [specialised]";
+    }
+    {
+        std::string d;
+        for (size_t i = 0; i < pl->pd.launches.size(); ++i) d += (i ? " ; " : "") + pl->pd.launches[i].name;
+        pl->pd.description = d;
+    }
     // pack all tables into one allocation
     std::vector<size_t> tw_off(pl->pd.tw_tables.size()), perm_off(pl->pd.perm_tables.size());
     size_t total = 0;
@@ -232,7 +309,8 @@ int trt_dft_plan_create(trt_dft_plan_t* plan_out, int direction, int rank, const
         return TRT_DFT_ERR_CUDA;
     }
     unsigned char* base = (unsigned char*)pl->pool;
-    for (auto& l : pl->pd.launches) {
+    for (size_t li = 0; li < pl->pd.launches.size(); ++li) {
+        auto& l = pl->pd.launches[li];
         ResolvedLaunch r;
         r.kp = l.kp;
         if (l.tw_row_id >= 0) r.kp.tw_row = (const float2*)(base + tw_off[l.tw_row_id]);
@@ -248,7 +326,24 @@ int trt_dft_plan_create(trt_dft_plan_t* plan_out, int direction, int rank, const
             delete pl;
             return TRT_DFT_ERR_UNSUPPORTED;
         }
-        if (r.kp.mode >= dft::MODE_NAIVE_ROWS_R2C) {
+        if (spec_of[li]) {
+            const SpecEntry* e = spec_of[li];
+            const bool invm = r.kp.mode == dft::MODE_I2D;
+            r.spec = invm ? e->inv : e->fwd;
+            r.spec_smem = invm ? e->smem_i : e->smem_f;
+            r.spec_nt = e->NT;
+            r.spec_tab = (const float2*)(base + tw_off[spec_tab_id[li]]);
+            int occ = 0;
+            if (cudaFuncSetAttribute((const void*)r.spec, cudaFuncAttributeMaxDynamicSharedMemorySize, r.spec_smem) != cudaSuccess ||
+                cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, (const void*)r.spec, r.spec_nt, r.spec_smem) != cudaSuccess ||
+                occ < 1) {
+                cudaGetLastError();
+                cudaFree(pl->pool);
+                delete pl;
+                return TRT_DFT_ERR_CUDA;
+            }
+            r.grid = (int)std::min<long long>(r.kp.nunits, (long long)num_sms * occ);
+        } else if (r.kp.mode >= dft::MODE_NAIVE_ROWS_R2C) {
             r.kp.smem_bytes = 0;
             const long long blocks = (r.kp.nunits + 255) / 256;
             r.grid = (int)std::min<long long>(blocks, (long long)num_sms * 16);
@@ -327,7 +422,10 @@ int trt_dft_exec(trt_dft_plan_t plan, const void* in, void* out, void* workspace
         float* dst = (float*)sel(r.dst);
         // real rows that are not 8-byte aligned cannot be written/read as float2 pairs
         if ((r.kp.mode == dft::MODE_I1D || r.kp.mode == dft::MODE_I2D) && ((uintptr_t)dst & 7)) return TRT_DFT_ERR_INVALID_ARG;
-        r.fn<<<r.grid, r.kp.threads, r.kp.smem_bytes, st>>>(r.kp, src, dst);
+        if (r.spec)
+            r.spec<<<r.grid, r.spec_nt, r.spec_smem, st>>>(src, dst, r.kp.nunits, r.spec_tab, r.kp.scale);
+        else
+            r.fn<<<r.grid, r.kp.threads, r.kp.smem_bytes, st>>>(r.kp, src, dst);
         if (cudaPeekAtLastError() != cudaSuccess) {
             cudaGetLastError();
             return TRT_DFT_ERR_CUDA;
