@@ -2,8 +2,8 @@
 //
 // Every index is a compile-time constant (static_for + integral constants), so a float2 v[R]
 // lives entirely in registers and every internal twiddle is an immediate.  Radices: the
-// primes 2,3,5,7,11,13 (symmetric half-sum form) and the composites 4,6,8,9,10,16 built by
-// one Cooley-Tukey split with constant twiddles.  The inverse transform never needs its own
+// primes 2,3,5,7,11,13 (symmetric half-sum form); 6,10,12,15 by a twiddle-free Good-Thomas
+// prime-factor split; 8,9,16 by one Cooley-Tukey split with constant twiddles.  The inverse transform never needs its own
 // butterflies: IDFT(x)[n] = DFT(x)[(N-n) mod N], and the index reversal is folded into the
 // permutation tables used when results are stored (see dft_planner.cpp).
 #pragma once
@@ -196,6 +196,50 @@ DFT_HD void dft_ct(float2 (&v)[R1 * R2])
     });
 }
 
+// Good-Thomas prime-factor split N = R1*R2 with gcd(R1,R2) = 1: a true R1 x R2 two-dimensional
+// DFT, no twiddles.  n = (R2*n1 + R1*n2) mod N,  k = (R2*(R2^-1 mod R1)*k1 + R1*(R1^-1 mod R2)*k2) mod N.
+constexpr int cx_modinv(int a, int m)
+{
+    a %= m;
+    for (int x = 1; x < m; ++x)
+        if ((a * x) % m == 1) return x;
+    return 1;
+}
+
+template <int R1, int R2>
+DFT_HD void dft_pfa(float2 (&v)[R1 * R2])
+{
+    constexpr int N = R1 * R2;
+    constexpr int I2 = cx_modinv(R2, R1), I1 = cx_modinv(R1, R2);
+    float2 t[N];  // t[k1*R2 + n2]
+    static_for<0, R2>([&](auto n2c) {
+        constexpr int n2 = decltype(n2c)::value;
+        float2 s[R1];
+        static_for<0, R1>([&](auto n1c) {
+            constexpr int n1 = decltype(n1c)::value;
+            s[n1] = v[(R2 * n1 + R1 * n2) % N];
+        });
+        dft_reg<R1>(s);
+        static_for<0, R1>([&](auto k1c) {
+            constexpr int k1 = decltype(k1c)::value;
+            t[k1 * R2 + n2] = s[k1];
+        });
+    });
+    static_for<0, R1>([&](auto k1c) {
+        constexpr int k1 = decltype(k1c)::value;
+        float2 s[R2];
+        static_for<0, R2>([&](auto n2c) {
+            constexpr int n2 = decltype(n2c)::value;
+            s[n2] = t[k1 * R2 + n2];
+        });
+        dft_reg<R2>(s);
+        static_for<0, R2>([&](auto k2c) {
+            constexpr int k2 = decltype(k2c)::value;
+            v[(R2 * I2 * k1 + R1 * I1 * k2) % N] = s[k2];
+        });
+    });
+}
+
 template <int R>
 DFT_HD void dft_reg(float2 (&v)[R])
 {
@@ -215,17 +259,17 @@ DFT_HD void dft_reg(float2 (&v)[R])
     } else if constexpr (R == 3 || R == 5 || R == 7 || R == 11 || R == 13) {
         dft_prime<R>(v);
     } else if constexpr (R == 6) {
-        dft_ct<2, 3>(v);
+        dft_pfa<2, 3>(v);
     } else if constexpr (R == 8) {
         dft_ct<2, 4>(v);
     } else if constexpr (R == 9) {
         dft_ct<3, 3>(v);
     } else if constexpr (R == 10) {
-        dft_ct<2, 5>(v);
+        dft_pfa<2, 5>(v);
     } else if constexpr (R == 12) {
-        dft_ct<3, 4>(v);
+        dft_pfa<3, 4>(v);
     } else if constexpr (R == 15) {
-        dft_ct<3, 5>(v);
+        dft_pfa<3, 5>(v);
     } else if constexpr (R == 16) {
         dft_ct<4, 4>(v);
     } else {

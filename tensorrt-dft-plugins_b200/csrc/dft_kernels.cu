@@ -19,6 +19,7 @@
 
 #include "../../include/trt_dft.h"
 #include "dft_fused2d.cuh"
+#include "dft_pipe2d.cuh"
 #include "dft_planner.h"
 #include "dft_programs.cuh"
 
@@ -151,25 +152,35 @@ struct SpecEntry {
     int H, W, RA, RB, CA, CB, NT;
     int smem_f, smem_i;
     spec_fn fwd, inv;
+    bool pipelined;      // dft_pipe2d.cuh: one persistent CTA per SM, needs 16-byte aligned in/out
 };
 
 template <class C>
 SpecEntry make_spec()
 {
     return SpecEntry{C::H, C::W, C::RA, C::RB, C::CA, C::CB, C::NT, C::SMEM_F, C::SMEM_I,
-                     dft::fused_rfft2_kernel<C>, dft::fused_irfft2_kernel<C>};
+                     dft::fused_rfft2_kernel<C>, dft::fused_irfft2_kernel<C>, false};
+}
+
+template <class C>
+SpecEntry make_pipe()
+{
+    return SpecEntry{C::H, C::W, C::RA, C::RB, C::CA, C::CB, C::THREADS, C::SMEM, C::SMEM,
+                     dft::pipe_rfft2_kernel<C>, dft::pipe_irfft2_kernel<C>, true};
 }
 
 const SpecEntry* find_spec(int H, int W)
 {
-    //                              H    W   RA  RB  CA  CB   NT  min CTAs/SM
     static const SpecEntry table[] = {
-        make_spec<dft::FusedCfg<90, 180, 10, 9, 10, 9, 320, 3>>(),     // FourCastNet AFNO (BASELINE cfg3)
+        //                     H    W   RA  RB  CA  CB  group threads, groups, stages
+        make_pipe<dft::PipeCfg<90, 180, 9, 10, 10, 9, 480, 2, 3>>(),   // FourCastNet AFNO (BASELINE cfg3)
+        //                      H    W   RA  RB  CA  CB   NT  min CTAs/SM
         make_spec<dft::FusedCfg<128, 128, 8, 8, 16, 8, 256, 3>>(),     // FNO (BASELINE cfg2)
         make_spec<dft::FusedCfg<64, 64, 8, 4, 8, 8, 256, 4>>(),
     };
+    const bool no_pipe = getenv("TRT_DFT_NO_PIPE") != nullptr;   // benchmarking override
     for (const auto& e : table)
-        if (e.H == H && e.W == W) return &e;
+        if (e.H == H && e.W == W && !(no_pipe && e.pipelined)) return &e;
     return nullptr;
 }
 
@@ -179,11 +190,20 @@ std::vector<float2> spec_tables(const SpecEntry& e, bool inverse, double scale)
     const int M = e.W / 2;
     const double two_pi = 6.283185307179586476925286766559;
     std::vector<float2> t;
-    for (int c = 1; c < e.RA; ++c)
-        for (int b = 0; b < e.RB; ++b) {
-            const double a = two_pi * (double)((b * c) % M) / M;
-            t.push_back(float2{(float)cos(a), (float)-sin(a)});
-        }
+    if (e.pipelined && inverse) {
+        // inverse rows run decimation-in-time: twR[(n2-1)*RA + k1] = w_M^(k1 n2)
+        for (int n2 = 1; n2 < e.RB; ++n2)
+            for (int k1 = 0; k1 < e.RA; ++k1) {
+                const double a = two_pi * (double)((k1 * n2) % M) / M;
+                t.push_back(float2{(float)cos(a), (float)-sin(a)});
+            }
+    } else {
+        for (int c = 1; c < e.RA; ++c)
+            for (int b = 0; b < e.RB; ++b) {
+                const double a = two_pi * (double)((b * c) % M) / M;
+                t.push_back(float2{(float)cos(a), (float)-sin(a)});
+            }
+    }
     for (int c = 1; c < e.CA; ++c)
         for (int b = 0; b < e.CB; ++b) {
             const double a = two_pi * (double)((b * c) % e.H) / e.H;
@@ -204,7 +224,8 @@ struct ResolvedLaunch {
     int src, dst;
     spec_fn spec = nullptr;          // non-null: launch the specialised kernel instead of fn
     const float2* spec_tab = nullptr;
-    int spec_smem = 0, spec_nt = 0;
+    int spec_smem = 0, spec_nt = 0, spec_grid = 0;
+    bool spec_needs_align16 = false; // pipelined kernels move whole images with TMA bulk copies only
 };
 
 }  // namespace
@@ -342,8 +363,12 @@ int trt_dft_plan_create(trt_dft_plan_t* plan_out, int direction, int rank, const
                 delete pl;
                 return TRT_DFT_ERR_CUDA;
             }
-            r.grid = (int)std::min<long long>(r.kp.nunits, (long long)num_sms * occ);
-        } else if (r.kp.mode >= dft::MODE_NAIVE_ROWS_R2C) {
+            r.spec_grid = (int)std::min<long long>(r.kp.nunits, (long long)num_sms * occ);
+            r.spec_needs_align16 = e->pipelined;
+        }
+        // the generic engine launch is always prepared: it is the route for buffers the
+        // specialised kernels cannot take (not 16-byte aligned)
+        if (r.kp.mode >= dft::MODE_NAIVE_ROWS_R2C) {
             r.kp.smem_bytes = 0;
             const long long blocks = (r.kp.nunits + 255) / 256;
             r.grid = (int)std::min<long long>(blocks, (long long)num_sms * 16);
@@ -388,7 +413,9 @@ int trt_dft_plan_describe(trt_dft_plan_t plan, char* buf, size_t len)
         std::string d = plan->pd.description;
         for (size_t i = 0; i < plan->launches.size(); ++i) {
             char t[64];
-            snprintf(t, sizeof t, "%s[%d]grid=%d", i ? "," : " ", (int)i, plan->launches[i].grid);
+            const auto& rl = plan->launches[i];
+            snprintf(t, sizeof t, "%s[%d]grid=%dx%d", i ? "," : " ", (int)i, rl.spec ? rl.spec_grid : rl.grid,
+                     rl.spec ? rl.spec_nt : rl.kp.threads);
             d += t;
         }
         strncpy(buf, d.c_str(), len - 1);
@@ -422,8 +449,8 @@ int trt_dft_exec(trt_dft_plan_t plan, const void* in, void* out, void* workspace
         float* dst = (float*)sel(r.dst);
         // real rows that are not 8-byte aligned cannot be written/read as float2 pairs
         if ((r.kp.mode == dft::MODE_I1D || r.kp.mode == dft::MODE_I2D) && ((uintptr_t)dst & 7)) return TRT_DFT_ERR_INVALID_ARG;
-        if (r.spec)
-            r.spec<<<r.grid, r.spec_nt, r.spec_smem, st>>>(src, dst, r.kp.nunits, r.spec_tab, r.kp.scale);
+        if (r.spec && !(r.spec_needs_align16 && ((((uintptr_t)src) | ((uintptr_t)dst)) & 15)))
+            r.spec<<<r.spec_grid, r.spec_nt, r.spec_smem, st>>>(src, dst, r.kp.nunits, r.spec_tab, r.kp.scale);
         else
             r.fn<<<r.grid, r.kp.threads, r.kp.smem_bytes, st>>>(r.kp, src, dst);
         if (cudaPeekAtLastError() != cudaSuccess) {

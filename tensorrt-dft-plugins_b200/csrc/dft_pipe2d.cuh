@@ -1,0 +1,379 @@
+// dft_pipe2d.cuh -- persistent, warp-specialised fused rfft2 / irfft2 kernels.
+//
+// One CTA per SM.  A producer warp streams whole images into a ring of NS shared-memory stages
+// with 1-D TMA bulk copies (cp.async.bulk + mbarrier full/empty pairs); NG compute groups of GT
+// threads each take every NG-th image, transform it in place in its stage and hand the stage
+// back.  Because one stage is always being filled while the groups work on the others, HBM
+// reads run continuously under the butterflies; groups synchronise among themselves with named
+// barriers (bar.sync id, GT), never CTA-wide.
+//
+//   forward : rows DIF  [radix RA, stride RB, twiddle] -> [radix RB, contiguous 128-bit chunks]
+//             cols DIF  [radix CA, stride CB rows, twiddle] -> [radix CB on the column pair
+//             (k, M-k) + real-FFT split + coalesced 8-byte global stores]
+//   inverse : cols DIF  [radix CA] -> [radix CB on the pair (k, M-k) + Hermitian merge; rows land
+//             in natural order, columns in digit-reversed order, pitch M, conjugated, scaled]
+//             rows DIT  [radix RB chunks, twiddle] -> [radix RA, stride RB -> natural order,
+//             conjugated back] -> one TMA bulk store of the dense real image
+//
+// Shared-memory bank behaviour (8-byte elements, 16 lanes per wavefront): a strided step maps
+// consecutive work items t to addresses congruent to t mod 16 when RB == pitch mod 16
+// (90 = 5*16 + 10, RB = 10), and the contiguous chunks are read with 128-bit accesses whose
+// 80-byte lane stride is odd in 16-byte units -- both conflict free.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "dft_butterflies.cuh"
+
+namespace dft {
+
+template <int H_, int W_, int RA_, int RB_, int CA_, int CB_, int GT_, int NG_, int NS_>
+struct PipeCfg {
+    static constexpr int H = H_, W = W_, M = W_ / 2, RA = RA_, RB = RB_, CA = CA_, CB = CB_;
+    static constexpr int GT = GT_, NG = NG_, NS = NS_;
+    static_assert(W_ % 2 == 0 && RA_ * RB_ == W_ / 2 && CA_ * CB_ == H_, "bad factorisation");
+    static_assert(RB_ % 2 == 0, "row chunks are accessed 128 bits at a time");
+    static constexpr int PI = M + 1;
+    static constexpr int KH = M / 2 + 1;
+    static_assert(CA_ * KH <= GT_, "the pair step must fit one round of a group");
+    static constexpr int TILE_F = H * M * 8;       // bytes: real image == packed complex image
+    static constexpr int TILE_I = H * PI * 8;      // bytes: one-sided spectrum
+    static_assert(TILE_F % 16 == 0 && TILE_I % 16 == 0, "bulk copies need 16-byte multiples");
+    static constexpr int STAGE = (TILE_I + 127) / 128 * 128;
+    static constexpr int NTW_RF = (RA - 1) * RB;   // forward rows: twR[(c-1)*RB + b]   = w_M^(b c)
+    static constexpr int NTW_RI = (RB - 1) * RA;   // inverse rows: twR[(n2-1)*RA + k1] = w_M^(k1 n2)
+    static constexpr int NTW_C = (CA - 1) * CB;    // columns:      twC[(c-1)*CB + b]   = w_H^(b c)
+    static constexpr int NTAB_F = NTW_RF + NTW_C + KH;
+    static constexpr int NTAB_I = NTW_RI + NTW_C + KH;
+    static constexpr int NTAB = NTAB_F > NTAB_I ? NTAB_F : NTAB_I;
+    static constexpr int THREADS = NG * GT + 32;
+    static constexpr int SMEM = NS * STAGE + NTAB * 8 + 2 * NS * 8 + 16;
+};
+
+#if defined(__CUDACC__)
+
+namespace pipe {
+
+__device__ __forceinline__ unsigned s32(const void* p) { return (unsigned)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(unsigned bar, unsigned count)
+{
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(unsigned bar, unsigned parity)
+{
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "PIPE_WAIT:\n"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+        "@p bra PIPE_DONE;\n"
+        "bra PIPE_WAIT;\n"
+        "PIPE_DONE:\n"
+        "}\n" ::"r"(bar),
+        "r"(parity)
+        : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(unsigned bar)
+{
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
+}
+__device__ __forceinline__ void fence_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+__device__ __forceinline__ void group_sync(int id, int n) { asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(n) : "memory"); }
+
+// producer lane: keep the ring of stages full
+template <class C>
+__device__ __forceinline__ void producer(const unsigned char* __restrict__ src, long long tile_bytes_stride, unsigned bytes,
+                                         long long nimg, unsigned char* stages, unsigned full0, unsigned empty0)
+{
+    long long it = 0;
+    for (long long tile = blockIdx.x; tile < nimg; tile += gridDim.x, ++it) {
+        const int s = (int)(it % C::NS);
+        if (it >= C::NS) mbar_wait(empty0 + 8 * s, (unsigned)(((it / C::NS) - 1) & 1));
+        fence_async();
+        const unsigned bar = full0 + 8 * s;
+        asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+        asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+                         s32(stages + (size_t)s * C::STAGE)),
+                     "l"(src + tile * tile_bytes_stride), "r"(bytes), "r"(bar)
+                     : "memory");
+    }
+}
+
+template <int R>
+__device__ __forceinline__ void load_chunk(float2 (&v)[R], const float2* p)
+{
+    static_assert(R % 2 == 0, "");
+    const float4* p4 = reinterpret_cast<const float4*>(p);
+    static_for<0, R / 2>([&](auto jc) {
+        constexpr int j = decltype(jc)::value;
+        const float4 q = p4[j];
+        v[2 * j] = float2{q.x, q.y};
+        v[2 * j + 1] = float2{q.z, q.w};
+    });
+}
+template <int R>
+__device__ __forceinline__ void store_chunk(const float2 (&v)[R], float2* p)
+{
+    float4* p4 = reinterpret_cast<float4*>(p);
+    static_for<0, R / 2>([&](auto jc) {
+        constexpr int j = decltype(jc)::value;
+        p4[j] = float4{v[2 * j].x, v[2 * j].y, v[2 * j + 1].x, v[2 * j + 1].y};
+    });
+}
+
+}  // namespace pipe
+
+// ---- forward ---------------------------------------------------------------------------------
+template <class C>
+__global__ void __launch_bounds__(C::THREADS, 1)
+    pipe_rfft2_kernel(const float* __restrict__ in, float* __restrict__ out, long long nimg,
+                      const float2* __restrict__ tables, float /*scale*/)
+{
+    constexpr int H = C::H, M = C::M, RA = C::RA, RB = C::RB, CA = C::CA, CB = C::CB, GT = C::GT, NG = C::NG, NS = C::NS;
+    constexpr int KH = C::KH, MO = M + 1;
+    extern __shared__ __align__(128) unsigned char smem_raw[];
+    unsigned char* stages = smem_raw;
+    float2* twR = reinterpret_cast<float2*>(smem_raw + NS * C::STAGE);
+    float2* twC = twR + C::NTW_RF;
+    float2* twU = twC + C::NTW_C;                       // 0.5 * w_W^k
+    const unsigned full0 = pipe::s32(twR + C::NTAB);
+    const unsigned empty0 = full0 + 8 * NS;
+    const int tid = threadIdx.x;
+
+    for (int i = tid; i < C::NTAB_F; i += C::THREADS) twR[i] = __ldg(tables + i);
+    if (tid == 0) {
+        for (int s = 0; s < NS; ++s) {
+            pipe::mbar_init(full0 + 8 * s, 1);
+            pipe::mbar_init(empty0 + 8 * s, 1);
+        }
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        pipe::fence_async();
+    }
+    __syncthreads();
+
+    if (tid >= NG * GT) {                               // producer warp
+        if (tid == NG * GT)
+            pipe::producer<C>(reinterpret_cast<const unsigned char*>(in), (long long)C::TILE_F, C::TILE_F, nimg, stages, full0, empty0);
+        return;
+    }
+    const int g = tid / GT;
+    const int gt = tid - g * GT;
+    const int bar_id = 1 + g;
+
+    long long it = g;
+    for (long long tile = blockIdx.x + (long long)g * gridDim.x; tile < nimg; tile += (long long)NG * gridDim.x, it += NG) {
+        const int s = (int)(it % NS);
+        float2* buf = reinterpret_cast<float2*>(stages + (size_t)s * C::STAGE);
+        pipe::mbar_wait(full0 + 8 * s, (unsigned)((it / NS) & 1));
+
+        // rows, DIF step RA: elements b + a*RB
+#pragma unroll 1
+        for (int t = gt; t < H * RB; t += GT) {
+            const int row = t / RB, b = t - row * RB;
+            float2* p = buf + row * M + b;
+            float2 v[RA];
+            static_for<0, RA>([&](auto ac) { constexpr int a = decltype(ac)::value; v[a] = p[a * RB]; });
+            dft_reg<RA>(v);
+            static_for<1, RA>([&](auto cc) { constexpr int c = decltype(cc)::value; v[c] = cmul(v[c], twR[(c - 1) * RB + b]); });
+            static_for<0, RA>([&](auto cc) { constexpr int c = decltype(cc)::value; p[c * RB] = v[c]; });
+        }
+        pipe::group_sync(bar_id, GT);
+        // rows, DIF step RB: contiguous chunk; frequency k = k1 + RA*k2 stays at k1*RB + k2
+#pragma unroll 1
+        for (int t = gt; t < H * RA; t += GT) {
+            float2* p = buf + t * RB;
+            float2 v[RB];
+            pipe::load_chunk<RB>(v, p);
+            dft_reg<RB>(v);
+            pipe::store_chunk<RB>(v, p);
+        }
+        pipe::group_sync(bar_id, GT);
+        // columns, DIF step CA: rows b + a*CB; threads run along the row
+#pragma unroll 1
+        for (int t = gt; t < CB * M; t += GT) {
+            const int b = t / M;
+            float2* p = buf + t;
+            float2 v[CA];
+            static_for<0, CA>([&](auto ac) { constexpr int a = decltype(ac)::value; v[a] = p[a * CB * M]; });
+            dft_reg<CA>(v);
+            static_for<1, CA>([&](auto cc) { constexpr int c = decltype(cc)::value; v[c] = cmul(v[c], twC[(c - 1) * CB + b]); });
+            static_for<0, CA>([&](auto cc) { constexpr int c = decltype(cc)::value; p[c * CB * M] = v[c]; });
+        }
+        pipe::group_sync(bar_id, GT);
+        // columns, step CB on the pair (k, M-k) + real-FFT split + global stores
+        if (gt < CA * KH) {
+            float2* oimg = reinterpret_cast<float2*>(out) + tile * (long long)(H * MO);
+            const int q1 = gt / KH, k = gt - q1 * KH;
+            const int kk = (k == 0) ? 0 : M - k;
+            const int colA = (k % RA) * RB + k / RA;
+            const int colB = (kk % RA) * RB + kk / RA;
+            const int q1B = (q1 == 0) ? 0 : CA - q1;
+            const float2* pa = buf + q1 * CB * M + colA;
+            const float2* pb = buf + q1B * CB * M + colB;
+            float2 A[CB], B[CB];
+            static_for<0, CB>([&](auto jc) { constexpr int j = decltype(jc)::value; A[j] = pa[j * M]; B[j] = pb[j * M]; });
+            dft_reg<CB>(A);
+            dft_reg<CB>(B);
+            if (q1 == 0) {   // partner of A[k2] is B[(CB-k2) mod CB] instead of B[CB-1-k2]: rotate
+                const float2 b0 = B[0];
+                static_for<0, CB - 1>([&](auto jc) { constexpr int j = decltype(jc)::value; B[j] = B[j + 1]; });
+                B[CB - 1] = b0;
+            }
+            const float2 wh = twU[k];
+            float2* oa = oimg + q1 * MO + k;
+            float2* ob = oimg + (H - q1) * MO + (M - k);
+            static_for<0, CB>([&](auto kc) {
+                constexpr int k2 = decltype(kc)::value;
+                const float2 z1 = A[k2], z2 = B[CB - 1 - k2];
+                const float ex = 0.5f * (z1.x + z2.x), ey = 0.5f * (z1.y - z2.y);
+                const float dx = z1.x - z2.x, dy = z1.y + z2.y;
+                const float tx = wh.x * dx - wh.y * dy, ty = wh.x * dy + wh.y * dx;
+                oa[k2 * CA * MO] = float2{ex + ty, ey - tx};
+                float2* pbk = ob - k2 * CA * MO;
+                if (k2 == 0 && q1 == 0) pbk -= H * MO;
+                *pbk = float2{ex - ty, -ey - tx};
+            });
+        }
+        pipe::fence_async();
+        pipe::group_sync(bar_id, GT);
+        if (gt == 0) pipe::mbar_arrive(empty0 + 8 * s);
+    }
+}
+
+// ---- inverse ---------------------------------------------------------------------------------
+template <class C>
+__global__ void __launch_bounds__(C::THREADS, 1)
+    pipe_irfft2_kernel(const float* __restrict__ in, float* __restrict__ out, long long nimg,
+                       const float2* __restrict__ tables, float scale)
+{
+    constexpr int H = C::H, M = C::M, RA = C::RA, RB = C::RB, CA = C::CA, CB = C::CB, GT = C::GT, NG = C::NG, NS = C::NS;
+    constexpr int KH = C::KH, PI = C::PI;
+    extern __shared__ __align__(128) unsigned char smem_raw[];
+    unsigned char* stages = smem_raw;
+    float2* twR = reinterpret_cast<float2*>(smem_raw + NS * C::STAGE);
+    float2* twC = twR + C::NTW_RI;
+    float2* twU = twC + C::NTW_C;                       // scale * w_W^k
+    const unsigned full0 = pipe::s32(reinterpret_cast<float2*>(smem_raw + NS * C::STAGE) + C::NTAB);
+    const unsigned empty0 = full0 + 8 * NS;
+    const int tid = threadIdx.x;
+
+    for (int i = tid; i < C::NTAB_I; i += C::THREADS) twR[i] = __ldg(tables + i);
+    if (tid == 0) {
+        for (int s = 0; s < NS; ++s) {
+            pipe::mbar_init(full0 + 8 * s, 1);
+            pipe::mbar_init(empty0 + 8 * s, 1);
+        }
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        pipe::fence_async();
+    }
+    __syncthreads();
+
+    if (tid >= NG * GT) {
+        if (tid == NG * GT)
+            pipe::producer<C>(reinterpret_cast<const unsigned char*>(in), (long long)C::TILE_I, C::TILE_I, nimg, stages, full0, empty0);
+        return;
+    }
+    const int g = tid / GT;
+    const int gt = tid - g * GT;
+    const int bar_id = 1 + g;
+
+    long long it = g;
+    for (long long tile = blockIdx.x + (long long)g * gridDim.x; tile < nimg; tile += (long long)NG * gridDim.x, it += NG) {
+        const int s = (int)(it % NS);
+        float2* buf = reinterpret_cast<float2*>(stages + (size_t)s * C::STAGE);
+        pipe::mbar_wait(full0 + 8 * s, (unsigned)((it / NS) & 1));
+
+        // columns, DIF step CA over all M+1 columns (pitch M+1)
+#pragma unroll 1
+        for (int t = gt; t < CB * PI; t += GT) {
+            const int b = t / PI;
+            float2* p = buf + t;
+            float2 v[CA];
+            static_for<0, CA>([&](auto ac) { constexpr int a = decltype(ac)::value; v[a] = p[a * CB * PI]; });
+            dft_reg<CA>(v);
+            static_for<1, CA>([&](auto cc) { constexpr int c = decltype(cc)::value; v[c] = cmul(v[c], twC[(c - 1) * CB + b]); });
+            static_for<0, CA>([&](auto cc) { constexpr int c = decltype(cc)::value; p[c * CB * PI] = v[c]; });
+        }
+        pipe::group_sync(bar_id, GT);
+        // columns, step CB on the pair (k, M-k) + Hermitian merge.  One round holds every item, so
+        // read -> barrier -> write may re-pitch the tile: row r (natural order) at r*M, column
+        // frequency k at (k mod RA)*RB + k/RA, value conj(Z'[k]) * scale.
+        {
+            const bool active = gt < CA * KH;
+            const int q1 = gt / KH, k = gt - q1 * KH;
+            const int kk = M - k;
+            float2 A[CB], B[CB];
+            if (active) {
+                const float2* pa = buf + q1 * CB * PI + k;
+                const float2* pb = buf + q1 * CB * PI + kk;
+                static_for<0, CB>([&](auto jc) { constexpr int j = decltype(jc)::value; A[j] = pa[j * PI]; B[j] = pb[j * PI]; });
+                dft_reg<CB>(A);
+                dft_reg<CB>(B);
+            }
+            pipe::group_sync(bar_id, GT);
+            if (active) {
+                const float2 ws = twU[k];
+                const int posA = (k % RA) * RB + k / RA;
+                const int kkm = (kk == M) ? 0 : kk;          // k == 0: column M only feeds Z'[0]
+                const int posB = (kkm % RA) * RB + kkm / RA;
+                static_for<0, CB>([&](auto kc) {
+                    constexpr int k2 = decltype(kc)::value;
+                    int r = H - q1 - CA * k2;                // column frequency q1 + CA*k2 -> inverse row (H - f) mod H
+                    if (k2 == 0 && q1 == 0) r = 0;
+                    const float2 a = A[k2], b = B[k2];
+                    float2* row = buf + r * M;
+                    if (k == 0) {
+                        row[0] = float2{scale * (a.x + b.x), scale * (b.x - a.x)};
+                    } else {
+                        const float sx = a.x + b.x, sy = a.y - b.y;
+                        const float dx = a.x - b.x, dy = a.y + b.y;
+                        const float ux = ws.x * dx + ws.y * dy, uy = ws.x * dy - ws.y * dx;
+                        // Z'[k] = (sx - uy, sy + ux), Z'[M-k] = (sx + uy, -sy + ux); stored conjugated
+                        row[posA] = float2{fmaf(scale, sx, -uy), -fmaf(scale, sy, ux)};
+                        if (kk != k) row[posB] = float2{fmaf(scale, sx, uy), fmaf(scale, sy, -ux)};
+                    }
+                });
+            }
+        }
+        pipe::group_sync(bar_id, GT);
+        // rows, DIT step RB: contiguous chunk k1*RB + k2 -> n2, twiddle w_M^(k1 n2)
+#pragma unroll 1
+        for (int t = gt; t < H * RA; t += GT) {
+            const int row = t / RA, k1 = t - row * RA;
+            float2* p = buf + t * RB;
+            float2 v[RB];
+            pipe::load_chunk<RB>(v, p);
+            dft_reg<RB>(v);
+            static_for<1, RB>([&](auto nc) { constexpr int n2 = decltype(nc)::value; v[n2] = cmul(v[n2], twR[(n2 - 1) * RA + k1]); });
+            pipe::store_chunk<RB>(v, p);
+        }
+        pipe::group_sync(bar_id, GT);
+        // rows, DIT step RA: elements k1*RB + n2 -> n = n1*RB + n2 (natural order); conjugate back
+#pragma unroll 1
+        for (int t = gt; t < H * RB; t += GT) {
+            const int row = t / RB, n2 = t - row * RB;
+            float2* p = buf + row * M + n2;
+            float2 v[RA];
+            static_for<0, RA>([&](auto ac) { constexpr int a = decltype(ac)::value; v[a] = p[a * RB]; });
+            dft_reg<RA>(v);
+            static_for<0, RA>([&](auto cc) { constexpr int c = decltype(cc)::value; p[c * RB] = float2{v[c].x, -v[c].y}; });
+        }
+        pipe::fence_async();
+        pipe::group_sync(bar_id, GT);
+        if (gt == 0) {
+            float* dst = out + tile * (long long)(H * C::W);
+            asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(dst), "r"(pipe::s32(buf)),
+                         "r"((unsigned)C::TILE_F)
+                         : "memory");
+            asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+            asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
+            pipe::mbar_arrive(empty0 + 8 * s);
+        }
+    }
+    // the last bulk stores must have completed before the CTA (and its shared memory) goes away
+    if (gt == 0) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
+}
+
+#endif  // __CUDACC__
+
+}  // namespace dft
