@@ -92,6 +92,25 @@ int trt_dft_exec_host(trt_dft_plan_t plan, const void* host_in, void* host_out);
  * Returns the number of kernel launches one trt_dft_exec issues (> 0), or -1. */
 int trt_dft_plan_describe(trt_dft_plan_t plan, char* buf, size_t len);
 
+/*
+ * No counterpart in the reference (its cuFFT work area always comes from TensorRT's workspace,
+ * dft_plugins.cpp:189).  Same as trt_dft_exec, for callers that cannot supply a workspace
+ * buffer because they cannot allocate one where they run -- inside an enqueue, in a serving
+ * loop that must not hit cudaMalloc's device-wide synchronisation, or behind an op interface
+ * that has inputs and outputs only.  The workspace is a fixed region of
+ * TRT_DFT_STATIC_WS_BYTES that the library reserves on every GPU it is loaded on (held until
+ * the process exits); the call itself allocates and frees nothing.
+ *   - plans needing more than TRT_DFT_STATIC_WS_BYTES are refused with
+ *     TRT_DFT_ERR_UNSUPPORTED (and a message on stderr); plans needing none run as usual;
+ *   - all calls on one GPU share the region: calls whose GPU work may overlap (different
+ *     streams) race -- keep them on one stream or order them with events;
+ *   - the region is never cleared and never needs to be: each call overwrites what it reads;
+ *   - the first call on each GPU looks up the region's device address (with that GPU current);
+ *     make that first call before beginning a stream capture on that GPU.
+ */
+#define TRT_DFT_STATIC_WS_BYTES (32u * 1024u * 1024u)
+int trt_dft_exec_static_ws(trt_dft_plan_t plan, const void* in, void* out, void* stream);
+
 /* Number of elements (floats) of the input / output tensors of a plan, for callers that
  * size buffers from the plan instead of recomputing the shape rules. */
 int64_t trt_dft_plan_input_floats(trt_dft_plan_t plan);
