@@ -62,6 +62,11 @@ int trt_dft_plan_create(trt_dft_plan_t* plan, int direction, int rank, const int
  * getWorkspaceSize reports (:114-129).  0 for every single-kernel plan. */
 size_t trt_dft_workspace_bytes(trt_dft_plan_t plan);
 
+/* Host-only variant of the above for TensorRT's getWorkspaceSize (dft_plugins.cpp:114-129), which is
+ * asked about shapes before any plan exists: runs the planner without touching a device.
+ * Returns 0 for invalid arguments too. */
+size_t trt_dft_query_workspace_bytes(int direction, int rank, const int64_t* dims, int64_t batch);
+
 /*
  * Replaces cufftSetStream + cufftSetWorkArea + cufftXtExec (+ cublasSetStream + cublasScalEx
  * for the inverse): dft_plugins.cpp:185-195 and :454-468.

@@ -21,6 +21,17 @@ NVCC_FLAGS = [
 ]
 
 
+def tensorrt_include():
+    """The real <NvInfer.h> wins when available (TENSORRT_INCLUDE_DIR or a standard location);
+    otherwise the plugin shell compiles against the stand-in in csrc/plugin/trt_min (test aid)."""
+    import os
+    cands = [os.environ.get("TENSORRT_INCLUDE_DIR"), "/usr/include/x86_64-linux-gnu", "/usr/include", "/usr/local/tensorrt/include"]
+    for c in cands:
+        if c and (Path(c) / "NvInfer.h").exists():
+            return c
+    return str(CSRC / "plugin" / "trt_min")
+
+
 def sources():
     cu = sorted(CSRC.glob("*.cu")) + sorted((CSRC / "plugin").glob("*.cpp"))
     deps = list(CSRC.rglob("*.h")) + list(CSRC.rglob("*.cuh")) + list((HERE.parent / "include").glob("*.h")) + cu
@@ -31,7 +42,7 @@ def build(force=False, verbose=False):
     cu, deps = sources()
     if not force and OUT.exists() and all(OUT.stat().st_mtime >= d.stat().st_mtime for d in deps + [Path(__file__)]):
         return OUT
-    cmd = ["nvcc"] + NVCC_FLAGS + (["-Xptxas", "-v"] if verbose else []) + ["-o", str(OUT)] + [str(c) for c in cu]
+    cmd = ["nvcc"] + NVCC_FLAGS + ["-I", tensorrt_include()] + (["-Xptxas", "-v"] if verbose else []) + ["-o", str(OUT)] + [str(c) for c in cu]
     if verbose:
         print(" ".join(cmd))
     subprocess.check_call(cmd)

@@ -198,7 +198,7 @@ DFT_HD void dft_ct(float2 (&v)[R1 * R2])
 
 // Good-Thomas prime-factor split N = R1*R2 with gcd(R1,R2) = 1: a true R1 x R2 two-dimensional
 // DFT, no twiddles.  n = (R2*n1 + R1*n2) mod N,  k = (R2*(R2^-1 mod R1)*k1 + R1*(R1^-1 mod R2)*k2) mod N.
-constexpr int cx_modinv(int a, int m)
+DFT_CX int cx_modinv(int a, int m)
 {
     a %= m;
     for (int x = 1; x < m; ++x)

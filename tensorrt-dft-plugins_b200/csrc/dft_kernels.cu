@@ -403,6 +403,17 @@ size_t trt_dft_workspace_bytes(trt_dft_plan_t plan)
     return plan ? plan->pd.ws_bytes : 0;
 }
 
+size_t trt_dft_query_workspace_bytes(int direction, int rank, const int64_t* dims, int64_t batch)
+{
+    try {
+        dft::PlanDesc pd;
+        if (dft::build_plan(&pd, direction, rank, dims, batch)) return 0;
+        return pd.ws_bytes;
+    } catch (...) {
+        return 0;
+    }
+}
+
 int64_t trt_dft_plan_input_floats(trt_dft_plan_t plan) { return plan ? plan->pd.in_floats : -1; }
 int64_t trt_dft_plan_output_floats(trt_dft_plan_t plan) { return plan ? plan->pd.out_floats : -1; }
 
