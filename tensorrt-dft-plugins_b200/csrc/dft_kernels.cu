@@ -240,7 +240,11 @@ struct trt_dft_plan_s {
     void* h_in = nullptr;
     void* h_out = nullptr;
     void* h_ws = nullptr;
-    cudaStream_t h_stream = nullptr;
+    int64_t h_chunk = 0;                  // images per pipeline chunk
+    trt_dft_plan_t h_sub = nullptr;       // plan for one chunk (null: the whole batch is one chunk)
+    trt_dft_plan_t h_sub_tail = nullptr;  // plan for the last, shorter chunk
+    cudaStream_t h_streams[3] = {nullptr, nullptr, nullptr};
+    cudaEvent_t h_events[16] = {};
 };
 
 extern "C" {
@@ -476,7 +480,12 @@ int trt_dft_plan_destroy(trt_dft_plan_t plan)
 {
     if (!plan) return TRT_DFT_OK;
     int rc = TRT_DFT_OK;
-    if (plan->h_stream) cudaStreamDestroy(plan->h_stream);
+    if (plan->h_sub) trt_dft_plan_destroy(plan->h_sub);
+    if (plan->h_sub_tail) trt_dft_plan_destroy(plan->h_sub_tail);
+    for (cudaStream_t st : plan->h_streams)
+        if (st) cudaStreamDestroy(st);
+    for (cudaEvent_t ev : plan->h_events)
+        if (ev) cudaEventDestroy(ev);
     for (void* p : {plan->pool, plan->h_in, plan->h_out, plan->h_ws})
         if (p && cudaFree(p) != cudaSuccess) rc = TRT_DFT_ERR_CUDA;
     delete plan;
@@ -490,20 +499,49 @@ int trt_dft_exec_host(trt_dft_plan_t plan, const void* host_in, void* host_out)
     if (!host_in || !host_out) return TRT_DFT_ERR_INVALID_ARG;
     std::lock_guard<std::mutex> lock(plan->host_mu);
     const size_t in_bytes = (size_t)plan->pd.in_floats * 4, out_bytes = (size_t)plan->pd.out_floats * 4;
+    const int64_t batch = plan->pd.batch;
     if (!plan->h_in) {
-        if (cudaMalloc(&plan->h_in, in_bytes) != cudaSuccess || cudaMalloc(&plan->h_out, out_bytes) != cudaSuccess ||
-            (plan->pd.ws_bytes && cudaMalloc(&plan->h_ws, plan->pd.ws_bytes) != cudaSuccess) ||
-            cudaStreamCreateWithFlags(&plan->h_stream, cudaStreamNonBlocking) != cudaSuccess) {
+        // Large transfers are cut into batch chunks and run as a 3-stream pipeline (H2D | kernels | D2H),
+        // so the two PCIe directions and the kernels overlap.
+        int nchunks = (in_bytes + out_bytes) >= ((size_t)64 << 20) ? 8 : 1;
+        if (nchunks > batch) nchunks = (int)batch;
+        plan->h_chunk = (batch + nchunks - 1) / nchunks;
+        const int64_t tail = batch % plan->h_chunk;
+        bool ok = cudaMalloc(&plan->h_in, in_bytes) == cudaSuccess && cudaMalloc(&plan->h_out, out_bytes) == cudaSuccess;
+        if (ok && plan->h_chunk != batch) {
+            ok = trt_dft_plan_create(&plan->h_sub, plan->pd.direction, plan->pd.rank, plan->pd.dims, plan->h_chunk) == TRT_DFT_OK;
+            if (ok && tail)
+                ok = trt_dft_plan_create(&plan->h_sub_tail, plan->pd.direction, plan->pd.rank, plan->pd.dims, tail) == TRT_DFT_OK;
+        }
+        const size_t ws = plan->h_sub ? trt_dft_workspace_bytes(plan->h_sub) : plan->pd.ws_bytes;
+        ok = ok && (!ws || cudaMalloc(&plan->h_ws, ws) == cudaSuccess);
+        for (int i = 0; ok && i < 3; ++i) ok = cudaStreamCreateWithFlags(&plan->h_streams[i], cudaStreamNonBlocking) == cudaSuccess;
+        for (int i = 0; ok && i < 16; ++i) ok = cudaEventCreateWithFlags(&plan->h_events[i], cudaEventDisableTiming) == cudaSuccess;
+        if (!ok) {
             cudaGetLastError();
             return TRT_DFT_ERR_ALLOC;
         }
     }
-    cudaStream_t st = plan->h_stream;
-    if (cudaMemcpyAsync(plan->h_in, host_in, in_bytes, cudaMemcpyHostToDevice, st) != cudaSuccess) return TRT_DFT_ERR_CUDA;
-    const int rc = trt_dft_exec(plan, plan->h_in, plan->h_out, plan->h_ws, st);
-    if (rc != TRT_DFT_OK) return rc;
-    if (cudaMemcpyAsync(host_out, plan->h_out, out_bytes, cudaMemcpyDeviceToHost, st) != cudaSuccess) return TRT_DFT_ERR_CUDA;
-    if (cudaStreamSynchronize(st) != cudaSuccess) return TRT_DFT_ERR_CUDA;
+    cudaStream_t s_in = plan->h_streams[0], s_run = plan->h_streams[1], s_out = plan->h_streams[2];
+    const size_t in_unit = in_bytes / (size_t)batch, out_unit = out_bytes / (size_t)batch;
+    int ci = 0;
+    for (int64_t b0 = 0; b0 < batch; b0 += plan->h_chunk, ++ci) {
+        const int64_t nb = (batch - b0) < plan->h_chunk ? (batch - b0) : plan->h_chunk;
+        trt_dft_plan_t sub = plan->h_sub ? (nb == plan->h_chunk ? plan->h_sub : plan->h_sub_tail) : plan;
+        unsigned char* din = (unsigned char*)plan->h_in + (size_t)b0 * in_unit;
+        unsigned char* dout = (unsigned char*)plan->h_out + (size_t)b0 * out_unit;
+        if (cudaMemcpyAsync(din, (const unsigned char*)host_in + (size_t)b0 * in_unit, (size_t)nb * in_unit,
+                            cudaMemcpyHostToDevice, s_in) != cudaSuccess) return TRT_DFT_ERR_CUDA;
+        cudaEventRecord(plan->h_events[2 * ci], s_in);
+        cudaStreamWaitEvent(s_run, plan->h_events[2 * ci], 0);
+        const int rc = trt_dft_exec(sub, din, dout, plan->h_ws, s_run);
+        if (rc != TRT_DFT_OK) return rc;
+        cudaEventRecord(plan->h_events[2 * ci + 1], s_run);
+        cudaStreamWaitEvent(s_out, plan->h_events[2 * ci + 1], 0);
+        if (cudaMemcpyAsync((unsigned char*)host_out + (size_t)b0 * out_unit, dout, (size_t)nb * out_unit,
+                            cudaMemcpyDeviceToHost, s_out) != cudaSuccess) return TRT_DFT_ERR_CUDA;
+    }
+    if (cudaStreamSynchronize(s_out) != cudaSuccess) return TRT_DFT_ERR_CUDA;
     return TRT_DFT_OK;
 }
 
