@@ -316,21 +316,28 @@ __global__ void __launch_bounds__(C::THREADS, 1)
                 const int posA = (k % RA) * RB + k / RA;
                 const int kkm = (kk == M) ? 0 : kk;          // k == 0: column M only feeds Z'[0]
                 const int posB = (kkm % RA) * RB + kkm / RA;
+                // column frequency q1 + CA*k2 is inverse row (H - q1 - CA*k2) mod H: a fixed pointer minus
+                // compile-time offsets (the one wrap, q1 == 0 && k2 == 0 -> row 0, is patched below)
+                float2* pA = buf + (H - q1) * M + posA;
+                float2* pB = buf + (H - q1) * M + posB;
                 static_for<0, CB>([&](auto kc) {
                     constexpr int k2 = decltype(kc)::value;
-                    int r = H - q1 - CA * k2;                // column frequency q1 + CA*k2 -> inverse row (H - f) mod H
-                    if (k2 == 0 && q1 == 0) r = 0;
                     const float2 a = A[k2], b = B[k2];
-                    float2* row = buf + r * M;
+                    float2* wa = pA - k2 * CA * M;
+                    float2* wb = pB - k2 * CA * M;
+                    if (k2 == 0 && q1 == 0) {
+                        wa -= H * M;
+                        wb -= H * M;
+                    }
                     if (k == 0) {
-                        row[0] = float2{scale * (a.x + b.x), scale * (b.x - a.x)};
+                        *wa = float2{scale * (a.x + b.x), scale * (b.x - a.x)};
                     } else {
                         const float sx = a.x + b.x, sy = a.y - b.y;
                         const float dx = a.x - b.x, dy = a.y + b.y;
                         const float ux = ws.x * dx + ws.y * dy, uy = ws.x * dy - ws.y * dx;
                         // Z'[k] = (sx - uy, sy + ux), Z'[M-k] = (sx + uy, -sy + ux); stored conjugated
-                        row[posA] = float2{fmaf(scale, sx, -uy), -fmaf(scale, sy, ux)};
-                        if (kk != k) row[posB] = float2{fmaf(scale, sx, uy), fmaf(scale, sy, -ux)};
+                        *wa = float2{fmaf(scale, sx, -uy), -fmaf(scale, sy, ux)};
+                        if (kk != k) *wb = float2{fmaf(scale, sx, uy), fmaf(scale, sy, -ux)};
                     }
                 });
             }
