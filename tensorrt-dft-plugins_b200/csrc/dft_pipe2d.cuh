@@ -35,7 +35,7 @@ struct PipeCfg {
     static_assert(RB_ % 2 == 0, "row chunks are accessed 128 bits at a time");
     static constexpr int PI = M + 1;
     static constexpr int KH = M / 2 + 1;
-    static_assert(CA_ * KH <= GT_, "the pair step must fit one round of a group");
+    static_assert(CA_ * KH <= GT_ && (KH + 31) / 32 * 32 + (CA_ - 1) * KH <= GT_, "the pair step must fit one round of a group");
     static constexpr int TILE_F = H * M * 8;       // bytes: real image == packed complex image
     static constexpr int TILE_I = H * PI * 8;      // bytes: one-sided spectrum
     static_assert(TILE_F % 16 == 0 && TILE_I % 16 == 0, "bulk copies need 16-byte multiples");
@@ -123,6 +123,41 @@ __device__ __forceinline__ void store_chunk(const float2 (&v)[R], float2* p)
 
 }  // namespace pipe
 
+// One item of the forward kernel's last phase: radix-CB butterflies of column k (row block q1) and of
+// its partner column M-k (row block CA-q1), the real-FFT split of the CB partner pairs, and the
+// 2*CB coalesced 8-byte stores.  A[k2] = Y[q1 + CA*k2][k]; its partner Y[(H-q) mod H][M-k] is
+// B[CB-1-k2] for q1 > 0 and B[(CB-k2) mod CB] for q1 == 0 (Q0).
+template <class C, bool Q0>
+__device__ __forceinline__ void split_store(const float2* buf, const float2* twU, float2* oimg, int q1, int k)
+{
+    constexpr int H = C::H, M = C::M, RA = C::RA, RB = C::RB, CA = C::CA, CB = C::CB, MO = M + 1;
+    const int kk = (k == 0) ? 0 : M - k;
+    const int colA = (k % RA) * RB + k / RA;
+    const int colB = (kk % RA) * RB + kk / RA;
+    const int q1B = Q0 ? 0 : CA - q1;
+    const float2* pa = buf + q1 * CB * M + colA;
+    const float2* pb = buf + q1B * CB * M + colB;
+    float2 A[CB], B[CB];
+    static_for<0, CB>([&](auto jc) { constexpr int j = decltype(jc)::value; A[j] = pa[j * M]; B[j] = pb[j * M]; });
+    dft_reg<CB>(A);
+    dft_reg<CB>(B);
+    const float2 wh = twU[k];                            // 0.5 * w_W^k
+    float2* oa = oimg + q1 * MO + k;                     // row q1 + CA*k2, column k
+    float2* ob = oimg + (H - q1) * MO + (M - k);         // row H - q1 - CA*k2, column M-k
+    static_for<0, CB>([&](auto kc) {
+        constexpr int k2 = decltype(kc)::value;
+        constexpr int kp = Q0 ? (CB - k2) % CB : CB - 1 - k2;
+        const float2 z1 = A[k2], z2 = B[kp];
+        const float sx = z1.x + z2.x, sy = z1.y - z2.y;  // z1 + conj z2
+        const float dx = z1.x - z2.x, dy = z1.y + z2.y;  // z1 - conj z2
+        const float tx = wh.x * dx - wh.y * dy, ty = wh.x * dy + wh.y * dx;
+        oa[k2 * CA * MO] = float2{fmaf(0.5f, sx, ty), fmaf(0.5f, sy, -tx)};
+        float2* pbk = ob - k2 * CA * MO;
+        if (Q0 && k2 == 0) pbk -= H * MO;                // (H - 0) mod H = 0
+        *pbk = float2{fmaf(0.5f, sx, -ty), fmaf(-0.5f, sy, -tx)};
+    });
+}
+
 // ---- forward ---------------------------------------------------------------------------------
 template <class C>
 __global__ void __launch_bounds__(C::THREADS, 1)
@@ -144,7 +179,7 @@ __global__ void __launch_bounds__(C::THREADS, 1)
     if (tid == 0) {
         for (int s = 0; s < NS; ++s) {
             pipe::mbar_init(full0 + 8 * s, 1);
-            pipe::mbar_init(empty0 + 8 * s, 1);
+            pipe::mbar_init(empty0 + 8 * s, GT / 32);   // every warp of the owning group releases the stage
         }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
         pipe::fence_async();
@@ -200,43 +235,24 @@ __global__ void __launch_bounds__(C::THREADS, 1)
             static_for<0, CA>([&](auto cc) { constexpr int c = decltype(cc)::value; p[c * CB * M] = v[c]; });
         }
         pipe::group_sync(bar_id, GT);
-        // columns, step CB on the pair (k, M-k) + real-FFT split + global stores
-        if (gt < CA * KH) {
+        // columns, step CB on the pair (k, M-k) + real-FFT split + global stores.  Items with q1 == 0
+        // pair differently (see split_store), so they get whole warps of their own: threads [0, KHP)
+        // take q1 == 0 (KHP = KH rounded up to a warp), the rest take q1 = 1 .. CA-1.
+        {
+            constexpr int KHP = (KH + 31) / 32 * 32;
             float2* oimg = reinterpret_cast<float2*>(out) + tile * (long long)(H * MO);
-            const int q1 = gt / KH, k = gt - q1 * KH;
-            const int kk = (k == 0) ? 0 : M - k;
-            const int colA = (k % RA) * RB + k / RA;
-            const int colB = (kk % RA) * RB + kk / RA;
-            const int q1B = (q1 == 0) ? 0 : CA - q1;
-            const float2* pa = buf + q1 * CB * M + colA;
-            const float2* pb = buf + q1B * CB * M + colB;
-            float2 A[CB], B[CB];
-            static_for<0, CB>([&](auto jc) { constexpr int j = decltype(jc)::value; A[j] = pa[j * M]; B[j] = pb[j * M]; });
-            dft_reg<CB>(A);
-            dft_reg<CB>(B);
-            if (q1 == 0) {   // partner of A[k2] is B[(CB-k2) mod CB] instead of B[CB-1-k2]: rotate
-                const float2 b0 = B[0];
-                static_for<0, CB - 1>([&](auto jc) { constexpr int j = decltype(jc)::value; B[j] = B[j + 1]; });
-                B[CB - 1] = b0;
+            if (gt < KHP) {
+                if (gt < KH) split_store<C, true>(buf, twU, oimg, 0, gt);
+            } else {
+                const int u = gt - KHP;
+                const int q1 = 1 + u / KH, k = u - (q1 - 1) * KH;
+                if (q1 < CA) split_store<C, false>(buf, twU, oimg, q1, k);
             }
-            const float2 wh = twU[k];
-            float2* oa = oimg + q1 * MO + k;
-            float2* ob = oimg + (H - q1) * MO + (M - k);
-            static_for<0, CB>([&](auto kc) {
-                constexpr int k2 = decltype(kc)::value;
-                const float2 z1 = A[k2], z2 = B[CB - 1 - k2];
-                const float ex = 0.5f * (z1.x + z2.x), ey = 0.5f * (z1.y - z2.y);
-                const float dx = z1.x - z2.x, dy = z1.y + z2.y;
-                const float tx = wh.x * dx - wh.y * dy, ty = wh.x * dy + wh.y * dx;
-                oa[k2 * CA * MO] = float2{ex + ty, ey - tx};
-                float2* pbk = ob - k2 * CA * MO;
-                if (k2 == 0 && q1 == 0) pbk -= H * MO;
-                *pbk = float2{ex - ty, -ey - tx};
-            });
         }
+        // release: every warp hands the stage back on its own (no group barrier at the tile end)
         pipe::fence_async();
-        pipe::group_sync(bar_id, GT);
-        if (gt == 0) pipe::mbar_arrive(empty0 + 8 * s);
+        __syncwarp();
+        if ((gt & 31) == 0) pipe::mbar_arrive(empty0 + 8 * s);
     }
 }
 
