@@ -315,8 +315,14 @@ __global__ void __launch_bounds__(C::THREADS, 1)
         // read -> barrier -> write may re-pitch the tile: row r (natural order) at r*M, column
         // frequency k at (k mod RA)*RB + k/RA, value conj(Z'[k]) * scale.
         {
+            // items: threads [0, CA*(KH-1)) take (q1, k >= 1); the CA items with k == 0 (which pair column 0
+            // with the Nyquist column M and ignore imaginary parts) sit together at the end, so that at most
+            // one warp sees both kinds.
+            constexpr int NK = KH - 1;
             const bool active = gt < CA * KH;
-            const int q1 = gt / KH, k = gt - q1 * KH;
+            const bool k_is_0 = gt >= CA * NK;
+            const int q1 = k_is_0 ? gt - CA * NK : gt / NK;
+            const int k = k_is_0 ? 0 : 1 + (gt - q1 * NK);
             const int kk = M - k;
             float2 A[CB], B[CB];
             if (active) {
@@ -328,34 +334,40 @@ __global__ void __launch_bounds__(C::THREADS, 1)
             }
             pipe::group_sync(bar_id, GT);
             if (active) {
-                const float2 ws = twU[k];
-                const int posA = (k % RA) * RB + k / RA;
-                const int kkm = (kk == M) ? 0 : kk;          // k == 0: column M only feeds Z'[0]
-                const int posB = (kkm % RA) * RB + kkm / RA;
                 // column frequency q1 + CA*k2 is inverse row (H - q1 - CA*k2) mod H: a fixed pointer minus
                 // compile-time offsets (the one wrap, q1 == 0 && k2 == 0 -> row 0, is patched below)
-                float2* pA = buf + (H - q1) * M + posA;
-                float2* pB = buf + (H - q1) * M + posB;
-                static_for<0, CB>([&](auto kc) {
-                    constexpr int k2 = decltype(kc)::value;
-                    const float2 a = A[k2], b = B[k2];
-                    float2* wa = pA - k2 * CA * M;
-                    float2* wb = pB - k2 * CA * M;
-                    if (k2 == 0 && q1 == 0) {
-                        wa -= H * M;
-                        wb -= H * M;
-                    }
-                    if (k == 0) {
-                        *wa = float2{scale * (a.x + b.x), scale * (b.x - a.x)};
-                    } else {
+                if (k_is_0) {
+                    float2* p0 = buf + (H - q1) * M;
+                    static_for<0, CB>([&](auto kc) {
+                        constexpr int k2 = decltype(kc)::value;
+                        float2* w0 = p0 - k2 * CA * M;
+                        if (k2 == 0 && q1 == 0) w0 -= H * M;
+                        *w0 = float2{scale * (A[k2].x + B[k2].x), scale * (B[k2].x - A[k2].x)};
+                    });
+                } else {
+                    const float2 ws = twU[k];
+                    const int posA = (k % RA) * RB + k / RA;
+                    const int posB = (kk % RA) * RB + kk / RA;
+                    float2* pA = buf + (H - q1) * M + posA;
+                    float2* pB = buf + (H - q1) * M + posB;
+                    static_for<0, CB>([&](auto kc) {
+                        constexpr int k2 = decltype(kc)::value;
+                        const float2 a = A[k2], b = B[k2];
+                        float2* wa = pA - k2 * CA * M;
+                        float2* wb = pB - k2 * CA * M;
+                        if (k2 == 0 && q1 == 0) {
+                            wa -= H * M;
+                            wb -= H * M;
+                        }
                         const float sx = a.x + b.x, sy = a.y - b.y;
                         const float dx = a.x - b.x, dy = a.y + b.y;
                         const float ux = ws.x * dx + ws.y * dy, uy = ws.x * dy - ws.y * dx;
-                        // Z'[k] = (sx - uy, sy + ux), Z'[M-k] = (sx + uy, -sy + ux); stored conjugated
+                        // Z'[k] = (sx - uy, sy + ux), Z'[M-k] = (sx + uy, -sy + ux); stored conjugated.
+                        // (k == M-k, M even: both stores write the same value to the same place.)
                         *wa = float2{fmaf(scale, sx, -uy), -fmaf(scale, sy, ux)};
-                        if (kk != k) *wb = float2{fmaf(scale, sx, uy), fmaf(scale, sy, -ux)};
-                    }
-                });
+                        *wb = float2{fmaf(scale, sx, uy), fmaf(scale, sy, -ux)};
+                    });
+                }
             }
         }
         pipe::group_sync(bar_id, GT);
