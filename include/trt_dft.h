@@ -58,6 +58,17 @@ const char* trt_dft_error_string(int status);
  */
 int trt_dft_plan_create(trt_dft_plan_t* plan, int direction, int rank, const int64_t* dims, int64_t batch);
 
+/*
+ * The strided-axis half of a multi-dimensional plan on its own: complex-to-complex FFT of length n
+ * along the middle axis of data[outer][n][inner] (interleaved complex fp32), unnormalised, every
+ * stored value multiplied by `scale`.  In the reference this work is hidden inside the rank-2/3
+ * cufftXtExec (dft_plugins.cpp:171-176, :192); it is exposed because the pencil-decomposed multi-GPU
+ * rfft2 runs it after the all-to-all transpose.  direction TRT_DFT_FORWARD uses
+ * exp(-i..), TRT_DFT_INVERSE exp(+i..).  `in` may equal `out` in trt_dft_exec (each tile is read
+ * completely before it is written).  Needs no workspace.
+ */
+int trt_dft_plan_create_c2c(trt_dft_plan_t* plan, int direction, int64_t n, int64_t outer, int64_t inner, float scale);
+
 /* Replaces the workSize out-parameter of cufftXtMakePlanMany (dft_plugins.cpp:175) that
  * getWorkspaceSize reports (:114-129).  0 for every single-kernel plan. */
 size_t trt_dft_workspace_bytes(trt_dft_plan_t plan);

@@ -233,6 +233,7 @@ struct ResolvedLaunch {
 struct trt_dft_plan_s {
     dft::PlanDesc pd;
     int device = 0;
+    bool c2c = false;                     // trt_dft_plan_create_c2c: complex on both sides
     void* pool = nullptr;                 // one device allocation holding every table
     std::vector<ResolvedLaunch> launches;
     // trt_dft_exec_host scratch (lazily allocated, reused across calls)
@@ -267,6 +268,8 @@ const char* trt_dft_error_string(int status)
     }
 }
 
+static int realize_plan(trt_dft_plan_s* pl, trt_dft_plan_t* plan_out);
+
 int trt_dft_plan_create(trt_dft_plan_t* plan_out, int direction, int rank, const int64_t* dims, int64_t batch)
 {
     if (!plan_out) return TRT_DFT_ERR_INVALID_ARG;
@@ -283,6 +286,32 @@ int trt_dft_plan_create(trt_dft_plan_t* plan_out, int direction, int rank, const
         delete pl;
         return rc;
     }
+    return realize_plan(pl, plan_out);
+}
+
+int trt_dft_plan_create_c2c(trt_dft_plan_t* plan_out, int direction, int64_t n, int64_t outer, int64_t inner, float scale)
+{
+    if (!plan_out) return TRT_DFT_ERR_INVALID_ARG;
+    *plan_out = nullptr;
+    trt_dft_plan_s* pl = new (std::nothrow) trt_dft_plan_s();
+    if (!pl) return TRT_DFT_ERR_ALLOC;
+    int rc = TRT_DFT_OK;
+    try {
+        rc = dft::build_c2c_plan(&pl->pd, direction, n, outer, inner, scale) ? TRT_DFT_ERR_INVALID_ARG : TRT_DFT_OK;
+    } catch (...) {
+        rc = TRT_DFT_ERR_ALLOC;
+    }
+    if (rc != TRT_DFT_OK) {
+        delete pl;
+        return rc;
+    }
+    pl->c2c = true;
+    return realize_plan(pl, plan_out);
+}
+
+// Device side of plan creation: tables to the GPU, kernel attributes, grid sizes.
+static int realize_plan(trt_dft_plan_s* pl, trt_dft_plan_t* plan_out)
+{
     if (pl->pd.launches.empty()) {   // batch == 0
         *plan_out = pl;
         return TRT_DFT_OK;
@@ -448,7 +477,7 @@ int trt_dft_exec(trt_dft_plan_t plan, const void* in, void* out, void* workspace
     const bool inv = plan->pd.direction == TRT_DFT_INVERSE;
     const uintptr_t cptr = (uintptr_t)(inv ? in : (const void*)out);
     const uintptr_t rptr = (uintptr_t)(inv ? (const void*)out : in);
-    if ((cptr & 7) || (rptr & 3)) return TRT_DFT_ERR_INVALID_ARG;
+    if ((cptr & 7) || (rptr & 3) || (plan->c2c && (rptr & 7))) return TRT_DFT_ERR_INVALID_ARG;
     if (plan->pd.ws_bytes && (!workspace || ((uintptr_t)workspace & 15))) return TRT_DFT_ERR_WORKSPACE;
     cudaStream_t st = (cudaStream_t)stream;
     for (auto& r : plan->launches) {

@@ -396,4 +396,35 @@ inline int build_plan(PlanDesc* pd, int direction, int rank, const int64_t* dims
     return 0;
 }
 
+// Complex-to-complex FFT of length n along the middle axis of data[outer][n][inner] (unnormalised;
+// `scale` is applied when the result is stored).  This is the strided-axis pass of a multi-dimensional
+// transform on its own, which the pencil-decomposed multi-GPU rfft2 runs after its all-to-all.
+inline int build_c2c_plan(PlanDesc* pd, int direction, int64_t n, int64_t outer, int64_t inner, float scale)
+{
+    if (!pd || (direction != 0 && direction != 1) || n < 1 || n > (1LL << 30) || outer < 0 || inner < 1) return 1;
+    pd->direction = direction;
+    pd->rank = 1;
+    pd->dims[0] = n;
+    pd->batch = outer * inner;
+    pd->in_floats = pd->out_floats = outer * n * inner * 2;
+    pd->ws_bytes = 0;
+    if (outer == 0) {
+        pd->description = "empty";
+        return 0;
+    }
+    Planner P{pd};
+    LineFFT f;
+    const bool engine = make_line_fft((int)n, false, &f) && (long long)n * 8 + kBarrierBytes <= kSmemMax;
+    if (engine) {
+        const size_t before = pd->launches.size();
+        P.add_cols(direction == 1, outer, (int)n, inner, BUF_IN, BUF_OUT, scale);
+        if (pd->launches.size() == before)   // n == 1 and nothing to do but copy / scale
+            P.add_naive(MODE_NAIVE_COLS, outer * n * inner, 0, 1, inner, 1, direction == 1, BUF_IN, BUF_OUT, scale);
+    } else {
+        P.add_naive(MODE_NAIVE_COLS, outer * n * inner, 0, (int)n, inner, (int)n, direction == 1, BUF_IN, BUF_OUT, scale);
+    }
+    pd->description = pd->launches[0].name;
+    return 0;
+}
+
 }  // namespace dft

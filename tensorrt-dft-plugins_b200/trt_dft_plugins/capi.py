@@ -178,3 +178,20 @@ def irfftn(y, signal_ndim: int, out=None, last=None):
         torch.cuda.current_stream(y.device).synchronize()
         plan.destroy()
     return out
+
+
+class C2CPlan(Plan):
+    """Complex FFT of length n along the middle axis of data[outer][n][inner] (trt_dft_plan_create_c2c).
+    Used by the pencil-decomposed multi-GPU rfft2 for the column pass after the all-to-all."""
+
+    def __init__(self, direction: int, n: int, outer: int, inner: int, scale: float = 1.0):
+        L = lib()
+        L.trt_dft_plan_create_c2c.restype = c_int
+        L.trt_dft_plan_create_c2c.argtypes = [ctypes.POINTER(c_void_p), c_int, c_int64, c_int64, c_int64, ctypes.c_float]
+        self.direction = int(direction)
+        self.dims = (int(n),)
+        self.batch = int(outer) * int(inner)
+        self._h = c_void_p()
+        self._ws = None
+        _check(L.trt_dft_plan_create_c2c(ctypes.byref(self._h), self.direction, int(n), int(outer), int(inner),
+                                         float(scale)), "trt_dft_plan_create_c2c")

@@ -189,3 +189,22 @@ def test_exec_host_and_streams(capi):
         p.exec(xd, out)
     s.synchronize()
     assert O.rel_l2(out.cpu().numpy(), want) <= FWD_TOL
+
+
+@pytest.mark.parametrize("outer,n,inner", [(2, 90, 91), (3, 64, 5), (1, 720, 37), (2, 1, 8), (1, 17, 6), (1, 8192, 12)])
+@pytest.mark.parametrize("direction", [0, 1])
+def test_c2c_strided_axis_plan(capi, outer, n, inner, direction):
+    """trt_dft_plan_create_c2c: the column pass on its own (used by the pencil decomposition)."""
+    torch.manual_seed(1)
+    z = torch.randn(outer, n, inner, 2)
+    zc = torch.view_as_complex(z.double())
+    want = torch.fft.fft(zc, dim=1) if direction == 0 else torch.fft.ifft(zc, dim=1, norm="forward")
+    plan = capi.C2CPlan(direction, n, outer, inner, scale=0.5)
+    zd = z.cuda()
+    out = torch.empty_like(zd)
+    plan.exec(zd, out)
+    torch.cuda.synchronize()
+    assert O.rel_l2(out.cpu().numpy(), 0.5 * torch.view_as_real(want).numpy()) <= FWD_TOL
+    plan.exec(zd, zd)                                   # in place
+    torch.cuda.synchronize()
+    assert torch.equal(zd, out)
