@@ -83,8 +83,8 @@ struct CtaCtx {
     }
 };
 
-template <int MODE>
-__global__ void __launch_bounds__(dft::kThreads) tile_kernel(const __grid_constant__ KParams p, const float* __restrict__ in,
+template <int MODE, int NT>
+__global__ void __launch_bounds__(NT) tile_kernel(const __grid_constant__ KParams p, const float* __restrict__ in,
                                                               float* __restrict__ out)
 {
     extern __shared__ __align__(128) unsigned char smem_raw[];
@@ -128,16 +128,17 @@ __global__ void __launch_bounds__(256) naive_kernel(const __grid_constant__ KPar
 
 typedef void (*kernel_fn)(const KParams, const float*, float*);
 
-kernel_fn kernel_for(int mode)
+kernel_fn kernel_for(int mode, int threads)
 {
     switch (mode) {
-        case dft::MODE_F2D: return tile_kernel<dft::MODE_F2D>;
-        case dft::MODE_I2D: return tile_kernel<dft::MODE_I2D>;
-        case dft::MODE_F1D: return tile_kernel<dft::MODE_F1D>;
-        case dft::MODE_I1D: return tile_kernel<dft::MODE_I1D>;
-        case dft::MODE_F1D_ODD: return tile_kernel<dft::MODE_F1D_ODD>;
-        case dft::MODE_I1D_ODD: return tile_kernel<dft::MODE_I1D_ODD>;
-        case dft::MODE_C2C_COLS: return tile_kernel<dft::MODE_C2C_COLS>;
+        case dft::MODE_F2D: return tile_kernel<dft::MODE_F2D, 256>;
+        case dft::MODE_I2D: return tile_kernel<dft::MODE_I2D, 256>;
+        case dft::MODE_F1D: return tile_kernel<dft::MODE_F1D, 256>;
+        case dft::MODE_I1D: return tile_kernel<dft::MODE_I1D, 256>;
+        case dft::MODE_F1D_ODD: return tile_kernel<dft::MODE_F1D_ODD, 256>;
+        case dft::MODE_I1D_ODD: return tile_kernel<dft::MODE_I1D_ODD, 256>;
+        case dft::MODE_C2C_COLS:
+            return threads == 512 ? tile_kernel<dft::MODE_C2C_COLS, 512> : tile_kernel<dft::MODE_C2C_COLS, 256>;
         case dft::MODE_NAIVE_ROWS_R2C: return naive_kernel<dft::MODE_NAIVE_ROWS_R2C>;
         case dft::MODE_NAIVE_ROWS_C2R: return naive_kernel<dft::MODE_NAIVE_ROWS_C2R>;
         case dft::MODE_NAIVE_COLS: return naive_kernel<dft::MODE_NAIVE_COLS>;
@@ -372,7 +373,8 @@ static int realize_plan(trt_dft_plan_s* pl, trt_dft_plan_t* plan_out)
         if (l.tw_unt_id >= 0) r.kp.tw_unt = (const float2*)(base + tw_off[l.tw_unt_id]);
         if (l.perm_row_id >= 0) r.kp.perm_row = (const int*)(base + perm_off[l.perm_row_id]);
         if (l.perm_col_id >= 0) r.kp.perm_col = (const int*)(base + perm_off[l.perm_col_id]);
-        r.fn = kernel_for(r.kp.mode);
+        if (r.kp.mode != dft::MODE_C2C_COLS) r.kp.threads = 256;
+        r.fn = kernel_for(r.kp.mode, r.kp.threads);
         r.src = l.src;
         r.dst = l.dst;
         if (!r.fn) {

@@ -23,26 +23,43 @@
 
 namespace dft {
 
+// ---- small integer helpers ---------------------------------------------------------------------
+DFT_HD unsigned magic_of(unsigned d) { return d <= 1u ? 0u : (unsigned)(((1ull << 32) + d - 1) / d); }
+DFT_HD int fdiv(int x, unsigned magic)   // floor(x / d) for the d that produced `magic`; exact for x*d < 2^32
+{
+    if (magic == 0u) return x;
+#if defined(__CUDA_ARCH__)
+    return (int)__umulhi((unsigned)x, magic);
+#else
+    return (int)(((unsigned long long)(unsigned)x * magic) >> 32);
+#endif
+}
+// skewed shared-memory position of logical element p of a power-of-two row (pad != 0)
+DFT_HD int phys(int p, int pad) { return pad ? p + (p >> 4) + (p >> 8) : p; }
+
 // ---- one radix-R step over all lines of the tile -------------------------------------------
-// ROWS (COLS=false): line l, element e at buf[l*pitch + e].
+// ROWS (COLS=false): line l, logical element e at buf[l*pitch + phys(e)].
 // COLS (COLS=true) : line = (img, col) with ncols columns per image; element e at
 //                    buf[img*img_stride + e*pitch + col]; consecutive threads take
 //                    consecutive columns (bank-conflict free, stride 1).
+// With pad != 0 the radix schedule is r_top,16,16,... so that within one butterfly the skew is
+// linear in the element index (see dft_planner.h).
 template <int R, bool COLS>
 DFT_HD void fft_step(float2* buf, int nlines, int pitch, int N, int L, const float2* tw, int ncols,
-                     int img_stride, int tid, int nthr)
+                     int img_stride, unsigned mmag, unsigned bmag, unsigned lmag, int pad, int tid, int nthr)
 {
     const int m = L / R;         // element stride inside the butterfly
     const int bpl = N / R;       // butterflies per line
     const int tws = N / L;       // twiddle table stride: w_L^x = w_N^(x*tws)
     const int total = nlines * bpl;
+    const int es_rows = pad ? m + (m >> 4) + (m >> 8) : m;
     for (int t = tid; t < total; t += nthr) {
         int line, u;
         if (COLS) {
-            u = t / nlines;
+            u = fdiv(t, lmag);           // lmag: magic of nlines
             line = t - u * nlines;
         } else {
-            line = t / bpl;
+            line = fdiv(t, bmag);
             u = t - line * bpl;
         }
         int blk, b;
@@ -50,7 +67,7 @@ DFT_HD void fft_step(float2* buf, int nlines, int pitch, int N, int L, const flo
             blk = u;
             b = 0;
         } else {
-            blk = u / m;
+            blk = fdiv(u, mmag);
             b = u - blk * m;
         }
         const int e0 = blk * L + b;
@@ -65,8 +82,8 @@ DFT_HD void fft_step(float2* buf, int nlines, int pitch, int N, int L, const flo
             p = buf + base + e0 * pitch;
             es = m * pitch;
         } else {
-            p = buf + line * pitch + e0;
-            es = m;
+            p = buf + line * pitch + phys(e0, pad);
+            es = es_rows;
         }
         float2 v[R];
         static_for<0, R>([&](auto ac) {
@@ -75,9 +92,11 @@ DFT_HD void fft_step(float2* buf, int nlines, int pitch, int N, int L, const flo
         });
         dft_reg<R>(v);
         if (m > 1) {
+            const float2* twb = tw + (long long)b * tws;
+            const int tstep = b * tws;
             static_for<1, R>([&](auto cc) {
                 constexpr int c = decltype(cc)::value;
-                const float2 w = DFT_LDG(tw + (long long)b * c * tws);
+                const float2 w = DFT_LDG(twb + (c - 1) * tstep);
                 v[c] = cmul(v[c], w);
             });
         }
@@ -90,12 +109,13 @@ DFT_HD void fft_step(float2* buf, int nlines, int pitch, int N, int L, const flo
 
 template <bool COLS>
 DFT_HD void fft_step_dispatch(int radix, float2* buf, int nlines, int pitch, int N, int L,
-                              const float2* tw, int ncols, int img_stride, int tid, int nthr)
+                              const float2* tw, int ncols, int img_stride, unsigned mmag, unsigned bmag,
+                              unsigned lmag, int pad, int tid, int nthr)
 {
     switch (radix) {
 #define DFT_CASE(R)                                                                     \
     case R:                                                                             \
-        fft_step<R, COLS>(buf, nlines, pitch, N, L, tw, ncols, img_stride, tid, nthr);  \
+        fft_step<R, COLS>(buf, nlines, pitch, N, L, tw, ncols, img_stride, mmag, bmag, lmag, pad, tid, nthr); \
         break;
         DFT_CASE(2)
         DFT_CASE(3)
@@ -134,23 +154,24 @@ DFT_HD float2 untangle(float2 z1, float2 z2, float2 w)
 // From the one-sided row T[0..M] build Z'[k] = (T[k] + conj T[M-k]) + i conj(w_W^k)(T[k] - conj T[M-k]),
 // k = 0..M-1, whose (unnormalised) inverse M-point FFT is W*x packed as x[2n] + i x[2n+1].
 // The imaginary parts of T[0] and T[M] are ignored (C2R semantics).
-DFT_HD void merge_rows(float2* buf, int nrows, int pitch, int M, const float2* tw_unt, int tid, int nthr)
+DFT_HD void merge_rows(float2* buf, int nrows, int pitch, int M, const float2* tw_unt, int pad, int tid, int nthr)
 {
     const int half = M / 2;                  // pairs k = 0..half  (k and M-k)
     const int per_row = half + 1;
     const int total = nrows * per_row;
+    const unsigned pmag = magic_of((unsigned)per_row);
     for (int t = tid; t < total; t += nthr) {
-        const int r = t / per_row;
+        const int r = fdiv(t, pmag);
         const int k = t - r * per_row;
         float2* row = buf + r * pitch;
         if (k == 0) {
-            const float a = row[0].x, b = row[M].x;
+            const float a = row[0].x, b = row[phys(M, pad)].x;
             row[0] = float2{a + b, a - b};
             continue;
         }
         const int k2 = M - k;
-        if (k2 < k) continue;                // only when M is odd and k == half+... (never for k<=half) guard
-        const float2 a = row[k], b = row[k2];
+        const int pk = phys(k, pad), pk2 = phys(k2, pad);
+        const float2 a = row[pk], b = row[pk2];
         const float2 w = DFT_LDG(tw_unt + k);  // (c, s) = exp(-2 pi i k / W)
         // Z'[k]   = (a + conj b) + i*conj(w)*(a - conj b)
         // Z'[M-k] = (b + conj a) - i*w*(b - conj a)
@@ -159,12 +180,12 @@ DFT_HD void merge_rows(float2* buf, int nrows, int pitch, int M, const float2* t
         // conj(w)*(d) = (c - i s)(dx + i dy) = (c dx + s dy) + i(c dy - s dx)
         const float ux = w.x * dx + w.y * dy, uy = w.x * dy - w.y * dx;
         // i*u = (-uy, ux)
-        row[k] = float2{sx - uy, sy + ux};
+        row[pk] = float2{sx - uy, sy + ux};
         if (k2 != k) {
             // b + conj a = (sx, -sy) ; b - conj a = (-dx, dy)
             // w*(b - conj a) = (c + i s)(-dx + i dy) = (-c dx - s dy) + i(c dy - s dx) = (-ux, uy)
             // -i*(-ux + i uy) = (uy, ux)
-            row[k2] = float2{sx + uy, -sy + ux};
+            row[pk2] = float2{sx + uy, -sy + ux};
         }
     }
 }

@@ -70,6 +70,9 @@ inline void factor_search(int n, int start, std::vector<int>& cur, std::vector<i
     }
 }
 
+inline bool is_pow2(int n) { return n > 0 && (n & (n - 1)) == 0; }
+inline int phys_index(int p, bool pad) { return pad ? p + (p >> 4) + (p >> 8) : p; }
+
 // false when n has a prime factor outside {2,3,5,7,11,13} or needs too many steps.
 inline bool make_line_fft(int n, bool rows, LineFFT* f)
 {
@@ -85,9 +88,21 @@ inline bool make_line_fft(int n, bool rows, LineFFT* f)
     factor_search(n, 0, cur, best);
     if (best.empty() || (int)best.size() > kMaxSteps) return false;
     std::sort(best.begin(), best.end(), [](int a, int b) { return a > b; });
-    if (rows) {
-        // the last row step reads r contiguous elements per thread; an odd radix makes the
-        // lane stride odd in 8-byte units, i.e. shared-memory bank-conflict free
+    if (rows && is_pow2(n) && n >= 32) {
+        // power-of-two rows are stored skewed (phys(p) = p + p/16 + p/256); the skew is linear inside a
+        // butterfly when the schedule is r_top, 16, 16, ... (n = r_top * 16^k)
+        best.clear();
+        int rest = n;
+        while (rest > 16) {
+            best.insert(best.begin(), 16);
+            rest /= 16;
+        }
+        if (rest > 1) best.insert(best.begin(), rest);
+    } else if (rows) {
+        // (1) the last row step reads r contiguous elements per thread: an odd radix makes the lane stride
+        //     odd in 8-byte units, i.e. shared-memory bank-conflict free;
+        // (2) results are gathered in natural order k = c0 + r0*(...) from position c0*(n/r0) + ...: with all
+        //     factors of two in r0, n/r0 is odd and consecutive k hit different banks.
         int pick = -1;
         for (int i = 0; i < (int)best.size(); ++i)
             if (best[i] % 2 == 1) { pick = i; break; }
@@ -96,9 +111,34 @@ inline bool make_line_fft(int n, bool rows, LineFFT* f)
             best.erase(best.begin() + pick);
             best.push_back(r);
         }
+        // try to put every factor of two into the first radix without adding steps
+        int two = 1;
+        while (n % (two * 2) == 0 && two < 16) two *= 2;
+        if (two >= 2 && n % (two * 2) != 0) {
+            std::vector<int> pick_list;
+            for (int r0 : {16, 10, 8, 6, 4, 2}) {
+                if (n % r0 || r0 % two || (r0 / two) % 2 == 0) continue;
+                std::vector<int> c2, b2;
+                if (n / r0 > 1) factor_search(n / r0, 0, c2, b2);
+                if (n / r0 > 1 && b2.empty()) continue;
+                if (b2.size() + 1 <= best.size() && (pick_list.empty() || b2.size() + 1 < pick_list.size())) {
+                    std::sort(b2.begin(), b2.end(), [](int a, int b) { return a > b; });
+                    pick_list = b2;
+                    pick_list.insert(pick_list.begin(), r0);
+                }
+            }
+            if (!pick_list.empty()) best = pick_list;
+        }
     }
     f->nsteps = (int)best.size();
-    for (int i = 0; i < f->nsteps; ++i) f->radix[i] = best[i];
+    int L = n;
+    for (int i = 0; i < f->nsteps; ++i) {
+        f->radix[i] = best[i];
+        const unsigned m = (unsigned)(L / best[i]), bpl = (unsigned)(n / best[i]);
+        f->mmag[i] = m <= 1 ? 0u : (unsigned)(((1ull << 32) + m - 1) / m);
+        f->bmag[i] = bpl <= 1 ? 0u : (unsigned)(((1ull << 32) + bpl - 1) / bpl);
+        L /= best[i];
+    }
     return true;
 }
 
@@ -116,10 +156,10 @@ inline int dif_position(const LineFFT& f, int k)
     return pos;
 }
 
-inline std::vector<int> make_perm(const LineFFT& f, bool inverse)
+inline std::vector<int> make_perm(const LineFFT& f, bool inverse, bool pad = false)
 {
     std::vector<int> p(f.n);
-    for (int i = 0; i < f.n; ++i) p[i] = dif_position(f, inverse ? (f.n - i) % f.n : i);
+    for (int i = 0; i < f.n; ++i) p[i] = phys_index(dif_position(f, inverse ? (f.n - i) % f.n : i), pad);
     return p;
 }
 
@@ -169,8 +209,9 @@ struct Planner {
         k.W = W;
         k.M = M;
         k.H = 1;
-        k.P = (inverse && even) ? M + 1 : M;
         make_line_fft(M, true, &k.row);
+        k.pad = (even && is_pow2(M) && M >= 32) ? 1 : 0;
+        k.P = k.pad ? phys_index(M, true) + 1 : ((inverse && even) ? M + 1 : M);
         k.nunits = nrows;
         k.G = pick_group(nrows, (long long)k.P * 8, 32 * 1024);
         k.ntiles = (nrows + k.G - 1) / k.G;
@@ -181,7 +222,7 @@ struct Planner {
         l.src = src;
         l.dst = dst;
         l.tw_row_id = add_tw(make_twiddles(M, M));
-        l.perm_row_id = add_perm(make_perm(k.row, inverse));
+        l.perm_row_id = add_perm(make_perm(k.row, inverse, k.pad != 0));
         if (even) l.tw_unt_id = add_tw(make_twiddles(W, M + 1));
         char nm[128];
         snprintf(nm, sizeof nm, "%s<W=%d> rows=%lld G=%d smem=%d", inverse ? (even ? "rows_c2r" : "rows_c2r_odd") : (even ? "rows_r2c" : "rows_r2c_odd"),
@@ -209,6 +250,7 @@ struct Planner {
         k.ntiles = k.nunits;
         k.smem_bytes = N * k.P * 8 + kBarrierBytes;
         k.scale = scale;
+        k.threads = ((long long)N * tm >= 8192) ? 512 : 256;   // big tiles: more warps to hide the strided loads
         Launch l;
         l.kp = k;
         l.src = src;
@@ -282,7 +324,8 @@ inline bool line_supported(int n, bool rows_pitch_plus1)
 {
     LineFFT f;
     if (!make_line_fft(n, true, &f)) return false;
-    return (long long)(n + (rows_pitch_plus1 ? 1 : 0)) * 8 + kBarrierBytes <= kSmemMax;
+    const long long pitch = (rows_pitch_plus1 && is_pow2(n) && n >= 32) ? phys_index(n, true) + 1 : n + (rows_pitch_plus1 ? 1 : 0);
+    return pitch * 8 + kBarrierBytes <= kSmemMax;
 }
 
 // Returns 0 on success, nonzero TRT_DFT_ERR_* style code (1 = invalid argument).

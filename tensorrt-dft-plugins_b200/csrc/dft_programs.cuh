@@ -13,15 +13,18 @@ namespace dft {
 
 template <class Ctx>
 DFT_HD void run_line_fft(const LineFFT& f, bool cols, float2* buf, int nlines, int pitch,
-                         const float2* tw, int ncols, int img_stride, Ctx& ctx)
+                         const float2* tw, int ncols, int img_stride, Ctx& ctx, int pad = 0)
 {
     int L = f.n;
+    const unsigned lmag = cols ? magic_of((unsigned)nlines) : 0u;   // nlines differs on the last, partial tile
     for (int s = 0; s < f.nsteps; ++s) {
         const int r = f.radix[s];
         if (cols)
-            fft_step_dispatch<true>(r, buf, nlines, pitch, f.n, L, tw, ncols, img_stride, ctx.tid, ctx.nthr);
+            fft_step_dispatch<true>(r, buf, nlines, pitch, f.n, L, tw, ncols, img_stride, f.mmag[s], f.bmag[s], lmag, 0,
+                                    ctx.tid, ctx.nthr);
         else
-            fft_step_dispatch<false>(r, buf, nlines, pitch, f.n, L, tw, ncols, img_stride, ctx.tid, ctx.nthr);
+            fft_step_dispatch<false>(r, buf, nlines, pitch, f.n, L, tw, ncols, img_stride, f.mmag[s], f.bmag[s], lmag, pad,
+                                     ctx.tid, ctx.nthr);
         ctx.sync();
         L /= r;
     }
@@ -85,7 +88,7 @@ DFT_HD void program_i2d(const KParams& p, long long tile, float2* buf, const flo
     const int nimg = (int)((p.nunits - first) < p.G ? (p.nunits - first) : p.G);
     load_contig(ctx, (float*)buf, in + first * H * P * 2, (long long)nimg * H * P * 2);
     run_line_fft(p.col, true, buf, nimg * P, P, p.tw_col, P, H * P, ctx);
-    merge_rows(buf, nimg * H, P, M, p.tw_unt, ctx.tid, ctx.nthr);
+    merge_rows(buf, nimg * H, P, M, p.tw_unt, 0, ctx.tid, ctx.nthr);
     ctx.sync();
     run_line_fft(p.row, false, buf, nimg * H, P, p.tw_row, 0, 0, ctx);
     float2* o = (float2*)out + first * H * M;
@@ -107,19 +110,39 @@ DFT_HD void program_i2d(const KParams& p, long long tile, float2* buf, const flo
 template <class Ctx>
 DFT_HD void program_f1d(const KParams& p, long long tile, float2* buf, const float* in, float* out, Ctx& ctx)
 {
-    const int M = p.M, Mo = p.M + 1;
+    const int M = p.M, Mo = p.M + 1, P = p.P;
     const long long first = tile * p.G;
     const int nrows = (int)((p.nunits - first) < p.G ? (p.nunits - first) : p.G);
-    load_contig(ctx, (float*)buf, in + first * p.W, (long long)nrows * p.W);
-    run_line_fft(p.row, false, buf, nrows, M, p.tw_row, 0, 0, ctx);
+    if (p.pad) {
+        // power-of-two rows: skewed placement (phys), so no bulk copy; 8-byte loads when aligned
+        const float* src = in + first * p.W;
+        const unsigned mg = magic_of((unsigned)M);
+        if ((((uintptr_t)src) & 7) == 0) {
+            const float2* s2 = (const float2*)src;
+            for (int idx = ctx.tid; idx < nrows * M; idx += ctx.nthr) {
+                const int r = fdiv(idx, mg), n = idx - r * M;
+                buf[r * P + phys(n, 1)] = DFT_LDG(s2 + idx);
+            }
+        } else {
+            for (int idx = ctx.tid; idx < nrows * M; idx += ctx.nthr) {
+                const int r = fdiv(idx, mg), n = idx - r * M;
+                buf[r * P + phys(n, 1)] = float2{DFT_LDG(src + 2 * idx), DFT_LDG(src + 2 * idx + 1)};
+            }
+        }
+        ctx.sync();
+    } else {
+        load_contig(ctx, (float*)buf, in + first * p.W, (long long)nrows * p.W);
+    }
+    run_line_fft(p.row, false, buf, nrows, P, p.tw_row, 0, 0, ctx, p.pad);
     float2* o = (float2*)out + first * Mo;
     const int total = nrows * Mo;
+    const unsigned omg = magic_of((unsigned)Mo);
     for (int idx = ctx.tid; idx < total; idx += ctx.nthr) {
-        const int r = idx / Mo;
+        const int r = fdiv(idx, omg);
         const int k = idx - r * Mo;
         const int k1 = (k == M) ? 0 : k;
         const int k2 = (k == 0 || k == M) ? 0 : M - k;
-        const float2* rb = buf + r * M;
+        const float2* rb = buf + r * P;
         const float2 z1 = rb[DFT_LDG(p.perm_row + k1)];
         const float2 z2 = rb[DFT_LDG(p.perm_row + k2)];
         o[idx] = untangle(z1, z2, DFT_LDG(p.tw_unt + k));
@@ -131,18 +154,29 @@ DFT_HD void program_f1d(const KParams& p, long long tile, float2* buf, const flo
 template <class Ctx>
 DFT_HD void program_i1d(const KParams& p, long long tile, float2* buf, const float* in, float* out, Ctx& ctx)
 {
-    const int M = p.M, P = p.M + 1;
+    const int M = p.M, Mo = p.M + 1, P = p.P;
     const long long first = tile * p.G;
     const int nrows = (int)((p.nunits - first) < p.G ? (p.nunits - first) : p.G);
-    load_contig(ctx, (float*)buf, in + first * P * 2, (long long)nrows * P * 2);
-    merge_rows(buf, nrows, P, M, p.tw_unt, ctx.tid, ctx.nthr);
+    if (p.pad) {
+        const float2* src = (const float2*)in + first * Mo;
+        const unsigned mg = magic_of((unsigned)Mo);
+        for (int idx = ctx.tid; idx < nrows * Mo; idx += ctx.nthr) {
+            const int r = fdiv(idx, mg), k = idx - r * Mo;
+            buf[r * P + phys(k, 1)] = DFT_LDG(src + idx);
+        }
+        ctx.sync();
+    } else {
+        load_contig(ctx, (float*)buf, in + first * Mo * 2, (long long)nrows * Mo * 2);
+    }
+    merge_rows(buf, nrows, P, M, p.tw_unt, p.pad, ctx.tid, ctx.nthr);
     ctx.sync();
-    run_line_fft(p.row, false, buf, nrows, P, p.tw_row, 0, 0, ctx);
+    run_line_fft(p.row, false, buf, nrows, P, p.tw_row, 0, 0, ctx, p.pad);
     float2* o = (float2*)out + first * M;
     const int total = nrows * M;
     const float sc = p.scale;
+    const unsigned mg2 = magic_of((unsigned)M);
     for (int idx = ctx.tid; idx < total; idx += ctx.nthr) {
-        const int r = idx / M;
+        const int r = fdiv(idx, mg2);
         const int n = idx - r * M;
         const float2 z = buf[r * P + DFT_LDG(p.perm_row + n)];
         o[idx] = float2{z.x * sc, z.y * sc};
@@ -213,20 +247,49 @@ DFT_HD void program_cols(const KParams& p, long long tile, float2* buf, const fl
     const int ncol = (int)((p.inner - col0) < p.G ? (p.inner - col0) : p.G);
     const float2* src = (const float2*)in + o_ * N * p.inner + col0;
     const int total = N * ncol;
-    for (int idx = ctx.tid; idx < total; idx += ctx.nthr) {
-        const int n = idx / ncol;
-        const int j = idx - n * ncol;
-        buf[n * P + j] = DFT_LDG(src + (long long)n * p.inner + j);
+    // When the CTA size is a multiple of the tile width each thread keeps one column and walks
+    // down the rows: no division in the loop, and the unrolled loads are all in flight together.
+    const bool fixed_col = (ctx.nthr % ncol) == 0;
+    const int rstep = ctx.nthr / ncol;
+    const int j0 = ctx.tid % ncol, n0 = ctx.tid / ncol;
+    if (fixed_col) {
+        const float2* s0 = src + (long long)n0 * p.inner + j0;
+        float2* d0 = buf + n0 * P + j0;
+        const long long sstep = (long long)rstep * p.inner;
+        const int dstep = rstep * P;
+        int n = n0;
+#if defined(__CUDA_ARCH__)
+#pragma unroll 8
+#endif
+        for (; n < N; n += rstep, s0 += sstep, d0 += dstep) *d0 = DFT_LDG(s0);
+    } else {
+        for (int idx = ctx.tid; idx < total; idx += ctx.nthr) {
+            const int n = idx / ncol;
+            const int j = idx - n * ncol;
+            buf[n * P + j] = DFT_LDG(src + (long long)n * p.inner + j);
+        }
     }
     ctx.sync();
     run_line_fft(p.col, true, buf, ncol, P, p.tw_col, ncol, 0, ctx);
     float2* dst = (float2*)out + o_ * N * p.inner + col0;
     const float sc = p.scale;
-    for (int idx = ctx.tid; idx < total; idx += ctx.nthr) {
-        const int q = idx / ncol;
-        const int j = idx - q * ncol;
-        const float2 z = buf[DFT_LDG(p.perm_col + q) * P + j];
-        dst[(long long)q * p.inner + j] = float2{z.x * sc, z.y * sc};
+    if (fixed_col) {
+        float2* d0 = dst + (long long)n0 * p.inner + j0;
+        const long long dstep2 = (long long)rstep * p.inner;
+#if defined(__CUDA_ARCH__)
+#pragma unroll 4
+#endif
+        for (int q = n0; q < N; q += rstep, d0 += dstep2) {
+            const float2 z = buf[DFT_LDG(p.perm_col + q) * P + j0];
+            *d0 = float2{z.x * sc, z.y * sc};
+        }
+    } else {
+        for (int idx = ctx.tid; idx < total; idx += ctx.nthr) {
+            const int q = idx / ncol;
+            const int j = idx - q * ncol;
+            const float2 z = buf[DFT_LDG(p.perm_col + q) * P + j];
+            dst[(long long)q * p.inner + j] = float2{z.x * sc, z.y * sc};
+        }
     }
     ctx.sync();
 }

@@ -21,6 +21,10 @@ struct LineFFT {
     int n;
     int nsteps;
     int radix[kMaxSteps];
+    // ceil(2^32 / d) for the two per-step divisors (d = L_i/r_i and d = n/r_i); 0 encodes d == 1.
+    // floor(x / d) == umulhi(x, magic) exactly whenever x * d < 2^32 (tile-local indices are < 2^16).
+    unsigned mmag[kMaxSteps];
+    unsigned bmag[kMaxSteps];
 };
 
 enum Mode : int {
@@ -59,6 +63,8 @@ struct KParams {
     long long inner;         // cols mode: contiguous inner extent (complex elements)
     long long outer;         // cols mode: number of [N][inner] slabs
     long long chunks;        // cols mode: column chunks per slab = ceil(inner / G)
+    int pad;                 // rows modes: 1 = power-of-two rows stored skewed in shared memory,
+                             // physical index p + p/16 + p/256 (kills the 16-way bank conflicts)
     int in_place_ok;         // informational
     int io_align;            // 16 if in/out base pointers and unit strides allow 16-byte bulk copies
 };

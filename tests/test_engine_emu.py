@@ -56,7 +56,7 @@ SHAPES = [
     ((4, 32, 64), 1), ((2, 3, 128, 128), 2), ((5, 90, 180), 2),
     # 1-D: even, odd, mixed radix, primes in and out of the radix set
     ((3, 2), 1), ((3, 6), 1), ((5, 30), 1), ((2, 9), 1), ((2, 15), 1), ((3, 1), 1), ((2, 360), 1),
-    ((2, 1024), 1), ((2, 2 * 7 * 11 * 13), 1), ((2, 34), 1), ((3, 19), 1), ((1, 4096), 1),
+    ((2, 1024), 1), ((2, 64), 1), ((3, 128), 1), ((1, 16384), 1), ((2, 1440), 1), ((2, 2 * 7 * 11 * 13), 1), ((2, 34), 1), ((3, 19), 1), ((1, 4096), 1),
     # 2-D: fused, multi-image tiles, odd widths, unsupported primes (naive), H == 1
     ((7, 8, 8), 2), ((3, 6, 10), 2), ((2, 5, 7), 2), ((2, 12, 18), 2), ((2, 17, 6), 2), ((2, 6, 38), 2),
     ((700, 4, 4), 2), ((1, 1, 16), 2), ((2, 16, 1), 2), ((2, 3, 3), 2),
