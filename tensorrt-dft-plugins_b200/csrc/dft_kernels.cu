@@ -84,7 +84,7 @@ struct CtaCtx {
 };
 
 template <int MODE, int NT>
-__global__ void __launch_bounds__(NT) tile_kernel(const __grid_constant__ KParams p, const float* __restrict__ in,
+__global__ void __launch_bounds__(NT, NT == 512 ? 2 : 1) tile_kernel(const __grid_constant__ KParams p, const float* __restrict__ in,
                                                               float* __restrict__ out)
 {
     extern __shared__ __align__(128) unsigned char smem_raw[];
@@ -111,6 +111,182 @@ __global__ void __launch_bounds__(NT) tile_kernel(const __grid_constant__ KParam
         if constexpr (MODE == dft::MODE_F1D_ODD) dft::program_f1d_odd(p, tile, buf, in, out, ctx);
         if constexpr (MODE == dft::MODE_I1D_ODD) dft::program_i1d_odd(p, tile, buf, in, out, ctx);
         if constexpr (MODE == dft::MODE_C2C_COLS) dft::program_cols(p, tile, buf, in, out, ctx);
+    }
+}
+
+// ---- persistent pipelined variant of the generic engine -----------------------------------------
+// One CTA per SM: 2 producer warps stream tiles into a ring of `ns` shared-memory stages (cp.async /
+// LDGSTS element copies, or one TMA bulk copy when the tile is contiguous and 16-byte clean), `ng`
+// compute groups run the ordinary tile programs (LOAD = false) on their stage and hand it back.
+// Used for the row and strided-axis passes of images too large to fuse (BASELINE cfg4 / cfg5).
+constexpr int kPipeCompute = 768, kPipeProducers = 64, kPipeThreads = kPipeCompute + kPipeProducers;
+
+struct GroupCtx {
+    int tid, nthr, bar_id;
+    __host__ __device__ __forceinline__ void sync()
+    {
+#if defined(__CUDA_ARCH__)
+        asm volatile("bar.sync %0, %1;" ::"r"(bar_id), "r"(nthr) : "memory");
+#endif
+    }
+    __host__ __device__ __forceinline__ bool bulk_load(void*, const void*, long long) { return false; }
+};
+
+__device__ __forceinline__ void cp_async8(void* dst, const void* src)
+{
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(smem_u32(dst)), "l"(src) : "memory");
+}
+__device__ __forceinline__ void cp_async4(void* dst, const void* src)
+{
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(smem_u32(dst)), "l"(src) : "memory");
+}
+__device__ __forceinline__ void gp_wait(unsigned bar, unsigned parity)
+{
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "GP_WAIT:\n"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+        "@p bra GP_DONE;\n"
+        "bra GP_WAIT;\n"
+        "GP_DONE:\n"
+        "}\n" ::"r"(bar),
+        "r"(parity)
+        : "memory");
+}
+
+// producer side: start the copies of one tile; returns the byte count of a bulk copy issued by
+// thread 0 (0 = element copies only)
+template <int MODE>
+__device__ __forceinline__ unsigned produce_tile(const KParams& p, long long tile, float2* buf, const float* in, int pt,
+                                                 unsigned full_bar)
+{
+    constexpr int NP = kPipeProducers;
+    if (MODE == dft::MODE_C2C_COLS) {
+        const int N = p.H, P = p.P;
+        const long long o_ = tile / p.chunks, c_ = tile - o_ * p.chunks, col0 = c_ * p.G;
+        const int ncol = (int)((p.inner - col0) < p.G ? (p.inner - col0) : p.G);
+        const float2* src = (const float2*)in + o_ * N * p.inner + col0;
+        if (NP % ncol == 0) {
+            const int rstep = NP / ncol, j0 = pt % ncol, n0 = pt / ncol;
+            const float2* s0 = src + (long long)n0 * p.inner + j0;
+            float2* d0 = buf + n0 * P + j0;
+            const long long sstep = (long long)rstep * p.inner;
+            const int dstep = rstep * P;
+#pragma unroll 4
+            for (int n = n0; n < N; n += rstep, s0 += sstep, d0 += dstep) cp_async8(d0, s0);
+        } else {
+            for (int idx = pt; idx < N * ncol; idx += NP) {
+                const int n = idx / ncol, j = idx - n * ncol;
+                cp_async8(buf + n * P + j, src + (long long)n * p.inner + j);
+            }
+        }
+        return 0;
+    } else {
+        // rows: F1D reads nrows*M packed-complex (= real pairs), I1D reads nrows*(M+1) complex
+        const int M = p.M, P = p.P;
+        const int per_row = (MODE == dft::MODE_F1D) ? M : M + 1;
+        const long long first = tile * p.G;
+        const int nrows = (int)((p.nunits - first) < p.G ? (p.nunits - first) : p.G);
+        const float* src = in + first * per_row * 2;
+        const long long nbytes = (long long)nrows * per_row * 8;
+        if (!p.pad && P == per_row && (((uintptr_t)src) & 15) == 0 && (nbytes & 15) == 0 && nbytes < (1 << 20)) {
+            if (pt == 0) {
+                asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(full_bar), "r"((unsigned)nbytes) : "memory");
+                asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+                                 smem_u32(buf)),
+                             "l"(src), "r"((unsigned)nbytes), "r"(full_bar)
+                             : "memory");
+            }
+            return (unsigned)nbytes;
+        }
+        const unsigned mg = dft::magic_of((unsigned)per_row);
+        const int total = nrows * per_row;
+        if ((((uintptr_t)src) & 7) == 0) {
+            const float2* s2 = (const float2*)src;
+            for (int idx = pt; idx < total; idx += NP) {
+                const int r = dft::fdiv(idx, mg), k = idx - r * per_row;
+                cp_async8(buf + r * P + dft::phys(k, p.pad), s2 + idx);
+            }
+        } else {   // real rows that are only 4-byte aligned
+            for (int idx = pt; idx < total; idx += NP) {
+                const int r = dft::fdiv(idx, mg), k = idx - r * per_row;
+                float* d = (float*)(buf + r * P + dft::phys(k, p.pad));
+                cp_async4(d, src + 2 * idx);
+                cp_async4(d + 1, src + 2 * idx + 1);
+            }
+        }
+        return 0;
+    }
+}
+
+template <int MODE>
+__global__ void __launch_bounds__(kPipeThreads, 1)
+    pipe_tile_kernel(const __grid_constant__ KParams p, const float* __restrict__ in, float* __restrict__ out, int ns, int ng,
+                     int stage_bytes)
+{
+    extern __shared__ __align__(128) unsigned char smem_raw[];
+    const unsigned full0 = smem_u32(smem_raw + (size_t)ns * stage_bytes);
+    const unsigned empty0 = full0 + 8 * ns;
+    const int tid = threadIdx.x;
+    const int gt = kPipeCompute / ng;
+    if (tid == 0) {
+        for (int s = 0; s < ns; ++s) {
+            asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(full0 + 8 * s), "r"(kPipeProducers) : "memory");
+            asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(empty0 + 8 * s), "r"(gt / 32) : "memory");
+        }
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+    }
+    __syncthreads();
+
+    if (tid >= kPipeCompute) {
+        const int pt = tid - kPipeCompute;
+        long long it = 0;
+        for (long long tile = blockIdx.x; tile < p.ntiles; tile += gridDim.x, ++it) {
+            const int s = (int)(it % ns);
+            if (it >= ns) gp_wait(empty0 + 8 * s, (unsigned)(((it / ns) - 1) & 1));
+            asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+            float2* buf = reinterpret_cast<float2*>(smem_raw + (size_t)s * stage_bytes);
+            const unsigned bar = full0 + 8 * s;
+            const unsigned bulk = produce_tile<MODE>(p, tile, buf, in, pt, bar);
+            if (bulk) {
+                if (pt != 0) asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
+            } else {
+                asm volatile("cp.async.mbarrier.arrive.noinc.shared::cta.b64 [%0];" ::"r"(bar) : "memory");
+            }
+        }
+        asm volatile("cp.async.wait_all;" ::: "memory");
+        return;
+    }
+    GroupCtx ctx;
+    const int g = tid / gt;
+    ctx.tid = tid - g * gt;
+    ctx.nthr = gt;
+    ctx.bar_id = 1 + g;
+    long long it = g;
+    for (long long tile = blockIdx.x + (long long)g * gridDim.x; tile < p.ntiles; tile += (long long)ng * gridDim.x, it += ng) {
+        const int s = (int)(it % ns);
+        float2* buf = reinterpret_cast<float2*>(smem_raw + (size_t)s * stage_bytes);
+        gp_wait(full0 + 8 * s, (unsigned)((it / ns) & 1));
+        if constexpr (MODE == dft::MODE_F1D) dft::program_f1d<GroupCtx, false>(p, tile, buf, in, out, ctx);
+        if constexpr (MODE == dft::MODE_I1D) dft::program_i1d<GroupCtx, false>(p, tile, buf, in, out, ctx);
+        if constexpr (MODE == dft::MODE_C2C_COLS) dft::program_cols<GroupCtx, false>(p, tile, buf, in, out, ctx);
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+        __syncwarp();
+        if ((tid & 31) == 0) asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(empty0 + 8 * s) : "memory");
+    }
+}
+
+typedef void (*pipe_fn)(const KParams, const float*, float*, int, int, int);
+
+pipe_fn pipe_kernel_for(int mode)
+{
+    switch (mode) {
+        case dft::MODE_F1D: return pipe_tile_kernel<dft::MODE_F1D>;
+        case dft::MODE_I1D: return pipe_tile_kernel<dft::MODE_I1D>;
+        case dft::MODE_C2C_COLS: return pipe_tile_kernel<dft::MODE_C2C_COLS>;
+        default: return nullptr;
     }
 }
 
@@ -227,6 +403,8 @@ struct ResolvedLaunch {
     const float2* spec_tab = nullptr;
     int spec_smem = 0, spec_nt = 0, spec_grid = 0;
     bool spec_needs_align16 = false; // pipelined kernels move whole images with TMA bulk copies only
+    pipe_fn gpipe = nullptr;         // non-null: persistent pipelined generic kernel instead of fn
+    int gp_ns = 0, gp_ng = 0, gp_stage = 0, gp_smem = 0, gp_grid = 0;
 };
 
 }  // namespace
@@ -425,6 +603,23 @@ static int realize_plan(trt_dft_plan_s* pl, trt_dft_plan_t* plan_out)
                 return TRT_DFT_ERR_CUDA;
             }
             r.grid = (int)std::min<long long>(r.kp.ntiles, (long long)num_sms * occ);
+            // persistent pipelined variant for the big row / strided-axis passes
+            pipe_fn pf = pipe_kernel_for(r.kp.mode);
+            const int stage = (r.kp.smem_bytes - dft::kBarrierBytes + 127) / 128 * 128;
+            const int ns = std::min(4, (dft::kSmemMax - 256) / std::max(stage, 1));
+            if (pf && !getenv("TRT_DFT_NO_GPIPE") && stage >= 8 * 1024 && ns >= 2 && r.kp.ntiles >= num_sms) {
+                const int smem = ns * stage + 2 * ns * 8 + 64;
+                if (cudaFuncSetAttribute((const void*)pf, cudaFuncAttributeMaxDynamicSharedMemorySize, dft::kSmemMax) == cudaSuccess) {
+                    r.gpipe = pf;
+                    r.gp_ns = ns;
+                    r.gp_ng = ns >= 3 ? 2 : 1;
+                    r.gp_stage = stage;
+                    r.gp_smem = smem;
+                    r.gp_grid = (int)std::min<long long>(r.kp.ntiles, num_sms);
+                } else {
+                    cudaGetLastError();
+                }
+            }
         }
         if (r.grid < 1) r.grid = 1;
         pl->launches.push_back(r);
@@ -458,10 +653,14 @@ int trt_dft_plan_describe(trt_dft_plan_t plan, char* buf, size_t len)
     if (buf && len) {
         std::string d = plan->pd.description;
         for (size_t i = 0; i < plan->launches.size(); ++i) {
-            char t[64];
+            char t[128];
             const auto& rl = plan->launches[i];
-            snprintf(t, sizeof t, "%s[%d]grid=%dx%d", i ? "," : " ", (int)i, rl.spec ? rl.spec_grid : rl.grid,
-                     rl.spec ? rl.spec_nt : rl.kp.threads);
+            if (rl.gpipe && !rl.spec)
+                snprintf(t, sizeof t, "%s[%d]pipelined grid=%dx%d stages=%d groups=%d", i ? "," : " ", (int)i, rl.gp_grid,
+                         kPipeThreads, rl.gp_ns, rl.gp_ng);
+            else
+                snprintf(t, sizeof t, "%s[%d]grid=%dx%d", i ? "," : " ", (int)i, rl.spec ? rl.spec_grid : rl.grid,
+                         rl.spec ? rl.spec_nt : rl.kp.threads);
             d += t;
         }
         strncpy(buf, d.c_str(), len - 1);
@@ -497,6 +696,8 @@ int trt_dft_exec(trt_dft_plan_t plan, const void* in, void* out, void* workspace
         if ((r.kp.mode == dft::MODE_I1D || r.kp.mode == dft::MODE_I2D) && ((uintptr_t)dst & 7)) return TRT_DFT_ERR_INVALID_ARG;
         if (r.spec && !(r.spec_needs_align16 && ((((uintptr_t)src) | ((uintptr_t)dst)) & 15)))
             r.spec<<<r.spec_grid, r.spec_nt, r.spec_smem, st>>>(src, dst, r.kp.nunits, r.spec_tab, r.kp.scale);
+        else if (r.gpipe)
+            r.gpipe<<<r.gp_grid, kPipeThreads, r.gp_smem, st>>>(r.kp, src, dst, r.gp_ns, r.gp_ng, r.gp_stage);
         else
             r.fn<<<r.grid, r.kp.threads, r.kp.smem_bytes, st>>>(r.kp, src, dst);
         if (cudaPeekAtLastError() != cudaSuccess) {

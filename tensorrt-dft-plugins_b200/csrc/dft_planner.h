@@ -8,6 +8,7 @@
 #include <math.h>
 #include <stdint.h>
 #include <stdio.h>
+#include <stdlib.h>
 #include <string.h>
 
 #include <algorithm>
@@ -213,7 +214,7 @@ struct Planner {
         k.pad = (even && is_pow2(M) && M >= 32) ? 1 : 0;
         k.P = k.pad ? phys_index(M, true) + 1 : ((inverse && even) ? M + 1 : M);
         k.nunits = nrows;
-        k.G = pick_group(nrows, (long long)k.P * 8, 32 * 1024);
+        k.G = pick_group(nrows, (long long)k.P * 8, 48 * 1024);
         k.ntiles = (nrows + k.G - 1) / k.G;
         k.smem_bytes = k.G * k.P * 8 + kBarrierBytes;
         k.scale = scale;
@@ -240,6 +241,13 @@ struct Planner {
         make_line_fft(N, false, &k.col);
         const long long maxfit = std::max<long long>(1, (long long)(kSmemMax - kBarrierBytes) / ((long long)N * 8));
         long long tm = std::max(std::min<long long>(16, maxfit), std::min<long long>(32, (64 * 1024) / ((long long)N * 8)));
+        // prefer a tile that leaves room for two pipeline stages, as long as rows stay >= 32 bytes wide
+        {
+            long long t2 = 16;
+            while (t2 > 1 && t2 * N * 8 > (kSmemMax - 1024) / 2) t2 /= 2;
+            if (t2 >= 4) tm = t2;
+        }
+        if (const char* e = getenv("TRT_DFT_TM")) tm = atoll(e);          // tuning override (benchmarks only)
         tm = std::max<long long>(1, std::min(tm, std::min(inner, maxfit)));
         k.G = (int)tm;
         k.P = (int)tm;
@@ -251,6 +259,7 @@ struct Planner {
         k.smem_bytes = N * k.P * 8 + kBarrierBytes;
         k.scale = scale;
         k.threads = ((long long)N * tm >= 8192) ? 512 : 256;   // big tiles: more warps to hide the strided loads
+        if (const char* e = getenv("TRT_DFT_COLS_THREADS")) k.threads = atoi(e) == 512 ? 512 : 256;
         Launch l;
         l.kp = k;
         l.src = src;

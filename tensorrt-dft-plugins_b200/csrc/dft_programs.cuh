@@ -107,13 +107,15 @@ DFT_HD void program_i2d(const KParams& p, long long tile, float2* buf, const flo
 }
 
 // ---- MODE_F1D: G rows per tile, W = 2M --------------------------------------------------------
-template <class Ctx>
+// LOAD = false: the tile is already in `buf` (the pipelined kernel's producer warps put it there).
+template <class Ctx, bool LOAD = true>
 DFT_HD void program_f1d(const KParams& p, long long tile, float2* buf, const float* in, float* out, Ctx& ctx)
 {
     const int M = p.M, Mo = p.M + 1, P = p.P;
     const long long first = tile * p.G;
     const int nrows = (int)((p.nunits - first) < p.G ? (p.nunits - first) : p.G);
-    if (p.pad) {
+    if (!LOAD) {
+    } else if (p.pad) {
         // power-of-two rows: skewed placement (phys), so no bulk copy; 8-byte loads when aligned
         const float* src = in + first * p.W;
         const unsigned mg = magic_of((unsigned)M);
@@ -151,13 +153,14 @@ DFT_HD void program_f1d(const KParams& p, long long tile, float2* buf, const flo
 }
 
 // ---- MODE_I1D ------------------------------------------------------------------------------------
-template <class Ctx>
+template <class Ctx, bool LOAD = true>
 DFT_HD void program_i1d(const KParams& p, long long tile, float2* buf, const float* in, float* out, Ctx& ctx)
 {
     const int M = p.M, Mo = p.M + 1, P = p.P;
     const long long first = tile * p.G;
     const int nrows = (int)((p.nunits - first) < p.G ? (p.nunits - first) : p.G);
-    if (p.pad) {
+    if (!LOAD) {
+    } else if (p.pad) {
         const float2* src = (const float2*)in + first * Mo;
         const unsigned mg = magic_of((unsigned)Mo);
         for (int idx = ctx.tid; idx < nrows * Mo; idx += ctx.nthr) {
@@ -237,7 +240,7 @@ DFT_HD void program_i1d_odd(const KParams& p, long long tile, float2* buf, const
 }
 
 // ---- MODE_C2C_COLS: data[outer][N][inner]; tile = (slab o, chunk c of G columns) ------------------
-template <class Ctx>
+template <class Ctx, bool LOAD = true>
 DFT_HD void program_cols(const KParams& p, long long tile, float2* buf, const float* in, float* out, Ctx& ctx)
 {
     const int N = p.H, P = p.P;
@@ -252,7 +255,8 @@ DFT_HD void program_cols(const KParams& p, long long tile, float2* buf, const fl
     const bool fixed_col = (ctx.nthr % ncol) == 0;
     const int rstep = ctx.nthr / ncol;
     const int j0 = ctx.tid % ncol, n0 = ctx.tid / ncol;
-    if (fixed_col) {
+    if (!LOAD) {
+    } else if (fixed_col) {
         const float2* s0 = src + (long long)n0 * p.inner + j0;
         float2* d0 = buf + n0 * P + j0;
         const long long sstep = (long long)rstep * p.inner;
@@ -269,7 +273,7 @@ DFT_HD void program_cols(const KParams& p, long long tile, float2* buf, const fl
             buf[n * P + j] = DFT_LDG(src + (long long)n * p.inner + j);
         }
     }
-    ctx.sync();
+    if (LOAD) ctx.sync();
     run_line_fft(p.col, true, buf, ncol, P, p.tw_col, ncol, 0, ctx);
     float2* dst = (float2*)out + o_ * N * p.inner + col0;
     const float sc = p.scale;
