@@ -222,14 +222,33 @@ __device__ __forceinline__ unsigned produce_tile(const KParams& p, long long til
 
 template <int MODE>
 __global__ void __launch_bounds__(kPipeThreads, 1)
-    pipe_tile_kernel(const __grid_constant__ KParams p, const float* __restrict__ in, float* __restrict__ out, int ns, int ng,
-                     int stage_bytes)
+    pipe_tile_kernel(const __grid_constant__ KParams p_in, const float* __restrict__ in, float* __restrict__ out, int ns, int ng,
+                     int stage_bytes, int tables_in_smem)
 {
     extern __shared__ __align__(128) unsigned char smem_raw[];
     const unsigned full0 = smem_u32(smem_raw + (size_t)ns * stage_bytes);
     const unsigned empty0 = full0 + 8 * ns;
     const int tid = threadIdx.x;
     const int gt = kPipeCompute / ng;
+    KParams p = p_in;
+    if (tables_in_smem) {
+        // twiddle / permutation tables move into shared memory once per (persistent) CTA
+        unsigned char* tb = smem_raw + (size_t)ns * stage_bytes + 2 * ns * 8 + 64;
+        auto stash = [&](const void* src, int bytes) -> void* {
+            void* dst = tb;
+            for (int i = tid * 4; i < bytes; i += kPipeThreads * 4) *(int*)(tb + i) = __ldg((const int*)((const unsigned char*)src + i));
+            tb += (bytes + 15) / 16 * 16;
+            return dst;
+        };
+        if (MODE == dft::MODE_C2C_COLS) {
+            p.tw_col = (const float2*)stash(p_in.tw_col, p_in.col.n * 8);
+            p.perm_col = (const int*)stash(p_in.perm_col, p_in.col.n * 4);
+        } else {
+            p.tw_row = (const float2*)stash(p_in.tw_row, p_in.row.n * 8);
+            p.perm_row = (const int*)stash(p_in.perm_row, p_in.row.n * 4);
+            p.tw_unt = (const float2*)stash(p_in.tw_unt, (p_in.M + 1) * 8);
+        }
+    }
     if (tid == 0) {
         for (int s = 0; s < ns; ++s) {
             asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(full0 + 8 * s), "r"(kPipeProducers) : "memory");
@@ -278,7 +297,7 @@ __global__ void __launch_bounds__(kPipeThreads, 1)
     }
 }
 
-typedef void (*pipe_fn)(const KParams, const float*, float*, int, int, int);
+typedef void (*pipe_fn)(const KParams, const float*, float*, int, int, int, int);
 
 pipe_fn pipe_kernel_for(int mode)
 {
@@ -404,7 +423,7 @@ struct ResolvedLaunch {
     int spec_smem = 0, spec_nt = 0, spec_grid = 0;
     bool spec_needs_align16 = false; // pipelined kernels move whole images with TMA bulk copies only
     pipe_fn gpipe = nullptr;         // non-null: persistent pipelined generic kernel instead of fn
-    int gp_ns = 0, gp_ng = 0, gp_stage = 0, gp_smem = 0, gp_grid = 0;
+    int gp_ns = 0, gp_ng = 0, gp_stage = 0, gp_smem = 0, gp_grid = 0, gp_tables = 0;
 };
 
 }  // namespace
@@ -606,9 +625,22 @@ static int realize_plan(trt_dft_plan_s* pl, trt_dft_plan_t* plan_out)
             // persistent pipelined variant for the big row / strided-axis passes
             pipe_fn pf = pipe_kernel_for(r.kp.mode);
             const int stage = (r.kp.smem_bytes - dft::kBarrierBytes + 127) / 128 * 128;
-            const int ns = std::min(4, (dft::kSmemMax - 256) / std::max(stage, 1));
+            int ns = std::min(4, (dft::kSmemMax - 256) / std::max(stage, 1));
+            // tables (twiddles, permutation) ride in shared memory when they fit beside >= 2 stages
+            const int tab_bytes = r.kp.mode == dft::MODE_C2C_COLS
+                                      ? r.kp.col.n * 12 + 64
+                                      : r.kp.row.n * 12 + (r.kp.M + 1) * 8 + 64;
+            int tables = 0;
+            if (ns >= 2) {
+                int ns_t = std::min(4, (dft::kSmemMax - 256 - tab_bytes) / std::max(stage, 1));
+                if (ns_t >= 2 && (ns_t >= 3 || ns < 3)) {
+                    ns = ns_t;
+                    tables = 1;
+                }
+            }
             if (pf && !getenv("TRT_DFT_NO_GPIPE") && stage >= 8 * 1024 && ns >= 2 && r.kp.ntiles >= num_sms) {
-                const int smem = ns * stage + 2 * ns * 8 + 64;
+                const int smem = ns * stage + 2 * ns * 8 + 64 + (tables ? tab_bytes : 0);
+                r.gp_tables = tables;
                 if (cudaFuncSetAttribute((const void*)pf, cudaFuncAttributeMaxDynamicSharedMemorySize, dft::kSmemMax) == cudaSuccess) {
                     r.gpipe = pf;
                     r.gp_ns = ns;
@@ -697,7 +729,7 @@ int trt_dft_exec(trt_dft_plan_t plan, const void* in, void* out, void* workspace
         if (r.spec && !(r.spec_needs_align16 && ((((uintptr_t)src) | ((uintptr_t)dst)) & 15)))
             r.spec<<<r.spec_grid, r.spec_nt, r.spec_smem, st>>>(src, dst, r.kp.nunits, r.spec_tab, r.kp.scale);
         else if (r.gpipe)
-            r.gpipe<<<r.gp_grid, kPipeThreads, r.gp_smem, st>>>(r.kp, src, dst, r.gp_ns, r.gp_ng, r.gp_stage);
+            r.gpipe<<<r.gp_grid, kPipeThreads, r.gp_smem, st>>>(r.kp, src, dst, r.gp_ns, r.gp_ng, r.gp_stage, r.gp_tables);
         else
             r.fn<<<r.grid, r.kp.threads, r.kp.smem_bytes, st>>>(r.kp, src, dst);
         if (cudaPeekAtLastError() != cudaSuccess) {

@@ -16,10 +16,11 @@
 #include "dft_types.h"
 
 #if defined(__CUDA_ARCH__)
-#define DFT_LDG(ptr) __ldg(ptr)
+#define DFT_LDG(ptr) __ldg(ptr)     // tensor data: always global memory
 #else
 #define DFT_LDG(ptr) (*(ptr))
 #endif
+#define DFT_LDT(ptr) (*(ptr))       // twiddle / permutation tables: global or shared memory (generic load)
 
 namespace dft {
 
@@ -96,7 +97,7 @@ DFT_HD void fft_step(float2* buf, int nlines, int pitch, int N, int L, const flo
             const int tstep = b * tws;
             static_for<1, R>([&](auto cc) {
                 constexpr int c = decltype(cc)::value;
-                const float2 w = DFT_LDG(twb + (c - 1) * tstep);
+                const float2 w = DFT_LDT(twb + (c - 1) * tstep);
                 v[c] = cmul(v[c], w);
             });
         }
@@ -172,7 +173,7 @@ DFT_HD void merge_rows(float2* buf, int nrows, int pitch, int M, const float2* t
         const int k2 = M - k;
         const int pk = phys(k, pad), pk2 = phys(k2, pad);
         const float2 a = row[pk], b = row[pk2];
-        const float2 w = DFT_LDG(tw_unt + k);  // (c, s) = exp(-2 pi i k / W)
+        const float2 w = DFT_LDT(tw_unt + k);  // (c, s) = exp(-2 pi i k / W)
         // Z'[k]   = (a + conj b) + i*conj(w)*(a - conj b)
         // Z'[M-k] = (b + conj a) - i*w*(b - conj a)
         const float sx = a.x + b.x, sy = a.y - b.y;   // a + conj b

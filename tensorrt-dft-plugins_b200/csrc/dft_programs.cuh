@@ -72,9 +72,9 @@ DFT_HD void program_f2d(const KParams& p, long long tile, float2* buf, const flo
         const int k2 = (k == 0 || k == M) ? 0 : M - k;
         const int q2 = (q == 0) ? 0 : H - q;
         const float2* ib = buf + img * H * M;
-        const float2 z1 = ib[DFT_LDG(p.perm_col + q) * M + DFT_LDG(p.perm_row + k1)];
-        const float2 z2 = ib[DFT_LDG(p.perm_col + q2) * M + DFT_LDG(p.perm_row + k2)];
-        o[idx] = untangle(z1, z2, DFT_LDG(p.tw_unt + k));
+        const float2 z1 = ib[DFT_LDT(p.perm_col + q) * M + DFT_LDT(p.perm_row + k1)];
+        const float2 z2 = ib[DFT_LDT(p.perm_col + q2) * M + DFT_LDT(p.perm_row + k2)];
+        o[idx] = untangle(z1, z2, DFT_LDT(p.tw_unt + k));
     }
     ctx.sync();
 }
@@ -100,7 +100,7 @@ DFT_HD void program_i2d(const KParams& p, long long tile, float2* buf, const flo
         const int rem = idx - img * per_img;
         const int r = rem / M;
         const int n = rem - r * M;
-        const float2 z = buf[(img * H + DFT_LDG(p.perm_col + r)) * P + DFT_LDG(p.perm_row + n)];
+        const float2 z = buf[(img * H + DFT_LDT(p.perm_col + r)) * P + DFT_LDT(p.perm_row + n)];
         o[idx] = float2{z.x * sc, z.y * sc};
     }
     ctx.sync();
@@ -136,18 +136,25 @@ DFT_HD void program_f1d(const KParams& p, long long tile, float2* buf, const flo
         load_contig(ctx, (float*)buf, in + first * p.W, (long long)nrows * p.W);
     }
     run_line_fft(p.row, false, buf, nrows, P, p.tw_row, 0, 0, ctx, p.pad);
+    // real-FFT split, two outputs per item: X[k] and X[M-k] come from the same pair Z[k], Z[M-k]
     float2* o = (float2*)out + first * Mo;
-    const int total = nrows * Mo;
-    const unsigned omg = magic_of((unsigned)Mo);
+    const int per_row = M / 2 + 1;
+    const int total = nrows * per_row;
+    const unsigned omg = magic_of((unsigned)per_row);
     for (int idx = ctx.tid; idx < total; idx += ctx.nthr) {
         const int r = fdiv(idx, omg);
-        const int k = idx - r * Mo;
-        const int k1 = (k == M) ? 0 : k;
-        const int k2 = (k == 0 || k == M) ? 0 : M - k;
+        const int k = idx - r * per_row;
+        const int kk = M - k;
         const float2* rb = buf + r * P;
-        const float2 z1 = rb[DFT_LDG(p.perm_row + k1)];
-        const float2 z2 = rb[DFT_LDG(p.perm_row + k2)];
-        o[idx] = untangle(z1, z2, DFT_LDG(p.tw_unt + k));
+        const float2 z1 = rb[DFT_LDT(p.perm_row + k)];
+        const float2 z2 = rb[DFT_LDT(p.perm_row + (k == 0 ? 0 : kk))];
+        const float2 w = DFT_LDT(p.tw_unt + k);
+        const float sx = z1.x + z2.x, sy = z1.y - z2.y;   // z1 + conj z2
+        const float dx = z1.x - z2.x, dy = z1.y + z2.y;   // z1 - conj z2
+        const float tx = 0.5f * (w.x * dx - w.y * dy), ty = 0.5f * (w.x * dy + w.y * dx);
+        float2* orow = o + (long long)r * Mo;
+        orow[k] = float2{0.5f * sx + ty, 0.5f * sy - tx};
+        if (kk != k) orow[kk] = float2{0.5f * sx - ty, -0.5f * sy - tx};
     }
     ctx.sync();
 }
@@ -181,7 +188,7 @@ DFT_HD void program_i1d(const KParams& p, long long tile, float2* buf, const flo
     for (int idx = ctx.tid; idx < total; idx += ctx.nthr) {
         const int r = fdiv(idx, mg2);
         const int n = idx - r * M;
-        const float2 z = buf[r * P + DFT_LDG(p.perm_row + n)];
+        const float2 z = buf[r * P + DFT_LDT(p.perm_row + n)];
         o[idx] = float2{z.x * sc, z.y * sc};
     }
     ctx.sync();
@@ -202,7 +209,7 @@ DFT_HD void program_f1d_odd(const KParams& p, long long tile, float2* buf, const
     for (int idx = ctx.tid; idx < nrows * Mo; idx += ctx.nthr) {
         const int r = idx / Mo;
         const int k = idx - r * Mo;
-        o[idx] = buf[r * W + DFT_LDG(p.perm_row + k)];
+        o[idx] = buf[r * W + DFT_LDT(p.perm_row + k)];
     }
     ctx.sync();
 }
@@ -234,7 +241,7 @@ DFT_HD void program_i1d_odd(const KParams& p, long long tile, float2* buf, const
     for (int idx = ctx.tid; idx < nrows * W; idx += ctx.nthr) {
         const int r = idx / W;
         const int n = idx - r * W;
-        o[idx] = buf[r * W + DFT_LDG(p.perm_row + n)].x * sc;
+        o[idx] = buf[r * W + DFT_LDT(p.perm_row + n)].x * sc;
     }
     ctx.sync();
 }
@@ -284,14 +291,14 @@ DFT_HD void program_cols(const KParams& p, long long tile, float2* buf, const fl
 #pragma unroll 4
 #endif
         for (int q = n0; q < N; q += rstep, d0 += dstep2) {
-            const float2 z = buf[DFT_LDG(p.perm_col + q) * P + j0];
+            const float2 z = buf[DFT_LDT(p.perm_col + q) * P + j0];
             *d0 = float2{z.x * sc, z.y * sc};
         }
     } else {
         for (int idx = ctx.tid; idx < total; idx += ctx.nthr) {
             const int q = idx / ncol;
             const int j = idx - q * ncol;
-            const float2 z = buf[DFT_LDG(p.perm_col + q) * P + j];
+            const float2 z = buf[DFT_LDT(p.perm_col + q) * P + j];
             dst[(long long)q * p.inner + j] = float2{z.x * sc, z.y * sc};
         }
     }
@@ -324,7 +331,7 @@ DFT_HD void naive_rows_r2c_elem(const KParams& p, long long idx, const float* in
     const float* x = in + r * W;
     double sr = 0.0, si = 0.0;
     for (int n = 0; n < W; ++n) {
-        const float2 w = DFT_LDG(p.tw_row + (int)(((long long)n * k) % W));
+        const float2 w = DFT_LDT(p.tw_row + (int)(((long long)n * k) % W));
         const double v = (double)DFT_LDG(x + n);
         sr += v * w.x;
         si += v * w.y;
@@ -340,7 +347,7 @@ DFT_HD void naive_rows_c2r_elem(const KParams& p, long long idx, const float* in
     const float2* X = (const float2*)in + r * Mo;
     double s = (double)DFT_LDG(X).x;
     for (int k = 1; k < Mo; ++k) {
-        const float2 w = DFT_LDG(p.tw_row + (int)(((long long)n * k) % W));  // (c, -s); inverse uses conj
+        const float2 w = DFT_LDT(p.tw_row + (int)(((long long)n * k) % W));  // (c, -s); inverse uses conj
         const float2 v = DFT_LDG(X + k);
         if (2 * k == W)
             s += (double)v.x * w.x;
@@ -363,7 +370,7 @@ DFT_HD void naive_cols_elem(const KParams& p, long long idx, const float* in, fl
     const double sg = p.W ? -1.0 : 1.0;
     double sr = 0.0, si = 0.0;
     for (int n = 0; n < N; ++n) {
-        const float2 w = DFT_LDG(p.tw_col + (int)(((long long)n * q) % N));
+        const float2 w = DFT_LDT(p.tw_col + (int)(((long long)n * q) % N));
         const float2 v = DFT_LDG(src + (long long)n * p.inner);
         const double wy = sg * w.y;
         sr += (double)v.x * w.x - (double)v.y * wy;
