@@ -119,7 +119,7 @@ __global__ void __launch_bounds__(NT, NT == 512 ? 2 : 1) tile_kernel(const __gri
 // LDGSTS element copies, or one TMA bulk copy when the tile is contiguous and 16-byte clean), `ng`
 // compute groups run the ordinary tile programs (LOAD = false) on their stage and hand it back.
 // Used for the row and strided-axis passes of images too large to fuse (BASELINE cfg4 / cfg5).
-constexpr int kPipeCompute = 768, kPipeProducers = 64, kPipeThreads = kPipeCompute + kPipeProducers;
+constexpr int kPipeCompute = 512, kPipeProducers = 64, kPipeThreads = kPipeCompute + kPipeProducers;
 
 struct GroupCtx {
     int tid, nthr, bar_id;
@@ -220,7 +220,38 @@ __device__ __forceinline__ unsigned produce_tile(const KParams& p, long long til
     }
 }
 
-template <int MODE>
+// Compile-time radix schedule of the transformed axis.  Injected into the kernel's private copy of
+// KParams, it lets the compiler fold the generic tile programs (radix switch, strides, magic divisors,
+// skew) down to immediates for registered lengths; GeoNone keeps everything run-time.
+struct GeoNone {
+    static constexpr bool kStatic = false;
+};
+template <int N_, int R0, int R1 = 1, int R2 = 1, int R3 = 1>
+struct GeoLine {
+    static constexpr bool kStatic = true;
+    static constexpr int N = N_;
+    static constexpr int nsteps = (R0 > 1) + (R1 > 1) + (R2 > 1) + (R3 > 1);
+    static_assert(R0 * R1 * R2 * R3 == N_, "schedule must multiply to N");
+    static constexpr bool pow2 = (N_ & (N_ - 1)) == 0;
+    __device__ static void apply(dft::LineFFT& f)
+    {
+        constexpr int r[4] = {R0, R1, R2, R3};
+        f.n = N_;
+        f.nsteps = nsteps;
+        int L = N_;
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            if (i >= nsteps) break;
+            f.radix[i] = r[i];
+            const unsigned m = (unsigned)(L / r[i]), bpl = (unsigned)(N_ / r[i]);
+            f.mmag[i] = m <= 1 ? 0u : (unsigned)(((1ull << 32) + m - 1) / m);
+            f.bmag[i] = bpl <= 1 ? 0u : (unsigned)(((1ull << 32) + bpl - 1) / bpl);
+            L /= r[i];
+        }
+    }
+};
+
+template <int MODE, class Geo = GeoNone>
 __global__ void __launch_bounds__(kPipeThreads, 1)
     pipe_tile_kernel(const __grid_constant__ KParams p_in, const float* __restrict__ in, float* __restrict__ out, int ns, int ng,
                      int stage_bytes, int tables_in_smem)
@@ -231,6 +262,19 @@ __global__ void __launch_bounds__(kPipeThreads, 1)
     const int tid = threadIdx.x;
     const int gt = kPipeCompute / ng;
     KParams p = p_in;
+    if constexpr (Geo::kStatic) {
+        if (MODE == dft::MODE_C2C_COLS) {
+            Geo::apply(p.col);
+            p.H = Geo::N;
+        } else {
+            Geo::apply(p.row);
+            p.M = Geo::N;
+            p.W = 2 * Geo::N;
+            p.pad = (Geo::pow2 && Geo::N >= 32) ? 1 : 0;
+            constexpr int PP = Geo::N + (Geo::N >> 4) + (Geo::N >> 8) + 1;
+            p.P = (Geo::pow2 && Geo::N >= 32) ? PP : (MODE == dft::MODE_I1D ? Geo::N + 1 : Geo::N);
+        }
+    }
     if (tables_in_smem) {
         // twiddle / permutation tables move into shared memory once per (persistent) CTA
         unsigned char* tb = smem_raw + (size_t)ns * stage_bytes + 2 * ns * 8 + 64;
@@ -298,6 +342,29 @@ __global__ void __launch_bounds__(kPipeThreads, 1)
 }
 
 typedef void (*pipe_fn)(const KParams, const float*, float*, int, int, int, int);
+
+// registered lengths: (N, radix schedule) must equal what the planner chose for that axis
+#define DFT_GEO_LIST(X)          \
+    X(720, 16, 9, 5, 1)          \
+    X(720, 10, 9, 8, 1)          \
+    X(4096, 16, 16, 16, 1)       \
+    X(512, 2, 16, 16, 1)         \
+    X(1024, 4, 16, 16, 1)        \
+    X(2048, 8, 16, 16, 1)
+
+pipe_fn pipe_kernel_for_geo(int mode, const dft::LineFFT& f)
+{
+#define DFT_GEO_TRY(N_, A, B, C, D)                                                                                   \
+    if (f.n == N_ && f.nsteps == ((A > 1) + (B > 1) + (C > 1) + (D > 1)) && f.radix[0] == A && (B == 1 || f.radix[1] == B) && \
+        (C == 1 || f.radix[2] == C) && (D == 1 || f.radix[3] == D)) {                                              \
+        if (mode == dft::MODE_F1D) return pipe_tile_kernel<dft::MODE_F1D, GeoLine<N_, A, B, C, D>>;                 \
+        if (mode == dft::MODE_I1D) return pipe_tile_kernel<dft::MODE_I1D, GeoLine<N_, A, B, C, D>>;                 \
+        if (mode == dft::MODE_C2C_COLS) return pipe_tile_kernel<dft::MODE_C2C_COLS, GeoLine<N_, A, B, C, D>>;       \
+    }
+    DFT_GEO_LIST(DFT_GEO_TRY)
+#undef DFT_GEO_TRY
+    return nullptr;
+}
 
 pipe_fn pipe_kernel_for(int mode)
 {
@@ -624,6 +691,10 @@ static int realize_plan(trt_dft_plan_s* pl, trt_dft_plan_t* plan_out)
             r.grid = (int)std::min<long long>(r.kp.ntiles, (long long)num_sms * occ);
             // persistent pipelined variant for the big row / strided-axis passes
             pipe_fn pf = pipe_kernel_for(r.kp.mode);
+            if (pf && !getenv("TRT_DFT_NO_GEO")) {
+                pipe_fn pg = pipe_kernel_for_geo(r.kp.mode, r.kp.mode == dft::MODE_C2C_COLS ? r.kp.col : r.kp.row);
+                if (pg) pf = pg;
+            }
             const int stage = (r.kp.smem_bytes - dft::kBarrierBytes + 127) / 128 * 128;
             int ns = std::min(4, (dft::kSmemMax - 256) / std::max(stage, 1));
             // tables (twiddles, permutation) ride in shared memory when they fit beside >= 2 stages

@@ -17,7 +17,11 @@ DFT_HD void run_line_fft(const LineFFT& f, bool cols, float2* buf, int nlines, i
 {
     int L = f.n;
     const unsigned lmag = cols ? magic_of((unsigned)nlines) : 0u;   // nlines differs on the last, partial tile
-    for (int s = 0; s < f.nsteps; ++s) {
+#if defined(__CUDA_ARCH__)
+#pragma unroll
+#endif
+    for (int s = 0; s < kMaxSteps; ++s) {
+        if (s >= f.nsteps) break;
         const int r = f.radix[s];
         if (cols)
             fft_step_dispatch<true>(r, buf, nlines, pitch, f.n, L, tw, ncols, img_stride, f.mmag[s], f.bmag[s], lmag, 0,
