@@ -416,6 +416,7 @@ struct SpecEntry {
     int smem_f, smem_i;
     spec_fn fwd, inv;
     bool pipelined;      // dft_pipe2d.cuh: one persistent CTA per SM, needs 16-byte aligned in/out
+    int NT_inv = 0;      // threads of the inverse kernel when they differ from NT
 };
 
 template <class C>
@@ -425,18 +426,22 @@ SpecEntry make_spec()
                      dft::fused_rfft2_kernel<C>, dft::fused_irfft2_kernel<C>, false};
 }
 
-template <class C>
+template <class CF, class CI>
 SpecEntry make_pipe()
 {
-    return SpecEntry{C::H, C::W, C::RA, C::RB, C::CA, C::CB, C::THREADS, C::SMEM, C::SMEM,
-                     dft::pipe_rfft2_kernel<C>, dft::pipe_irfft2_kernel<C>, true};
+    static_assert(CF::H == CI::H && CF::W == CI::W && CF::RA == CI::RA && CF::RB == CI::RB && CF::CA == CI::CA && CF::CB == CI::CB, "");
+    SpecEntry e{CF::H, CF::W, CF::RA, CF::RB, CF::CA, CF::CB, CF::THREADS, CF::SMEM, CI::SMEM,
+                dft::pipe_rfft2_kernel<CF>, dft::pipe_irfft2_kernel<CI>, true};
+    e.NT_inv = CI::THREADS;
+    return e;
 }
 
 const SpecEntry* find_spec(int H, int W)
 {
     static const SpecEntry table[] = {
         //                     H    W   RA  RB  CA  CB  group threads, groups, stages
-        make_pipe<dft::PipeCfg<90, 180, 9, 10, 10, 9, 480, 2, 3>>(),   // FourCastNet AFNO (BASELINE cfg3)
+        make_pipe<dft::PipeCfg<90, 180, 9, 10, 10, 9, 320, 2, 3>,      // forward: 2 x 320 threads, 96 registers
+                  dft::PipeCfg<90, 180, 9, 10, 10, 9, 480, 2, 3>>(),    // inverse: 2 x 480 (one-round merge)   (BASELINE cfg3)
         //                      H    W   RA  RB  CA  CB   NT  min CTAs/SM
         make_spec<dft::FusedCfg<128, 128, 8, 8, 16, 8, 256, 3>>(),     // FNO (BASELINE cfg2)
         make_spec<dft::FusedCfg<64, 64, 8, 4, 8, 8, 256, 4>>(),
@@ -651,7 +656,7 @@ static int realize_plan(trt_dft_plan_s* pl, trt_dft_plan_t* plan_out)
             const bool invm = r.kp.mode == dft::MODE_I2D;
             r.spec = invm ? e->inv : e->fwd;
             r.spec_smem = invm ? e->smem_i : e->smem_f;
-            r.spec_nt = e->NT;
+            r.spec_nt = (invm && e->NT_inv) ? e->NT_inv : e->NT;
             r.spec_tab = (const float2*)(base + tw_off[spec_tab_id[li]]);
             int occ = 0;
             if (cudaFuncSetAttribute((const void*)r.spec, cudaFuncAttributeMaxDynamicSharedMemorySize, r.spec_smem) != cudaSuccess ||

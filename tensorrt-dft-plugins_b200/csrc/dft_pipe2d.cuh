@@ -35,7 +35,8 @@ struct PipeCfg {
     static_assert(RB_ % 2 == 0, "row chunks are accessed 128 bits at a time");
     static constexpr int PI = M + 1;
     static constexpr int KH = M / 2 + 1;
-    static_assert(CA_ * KH <= GT_ && (KH + 31) / 32 * 32 + (CA_ - 1) * KH <= GT_, "the pair step must fit one round of a group");
+    // the inverse kernel's merge step needs every (k, M-k) item in one round of a group
+    static constexpr bool kInverseOk = CA_ * KH <= GT_;
     static constexpr int TILE_F = H * M * 8;       // bytes: real image == packed complex image
     static constexpr int TILE_I = H * PI * 8;      // bytes: one-sided spectrum
     static_assert(TILE_F % 16 == 0 && TILE_I % 16 == 0, "bulk copies need 16-byte multiples");
@@ -241,12 +242,15 @@ __global__ void __launch_bounds__(C::THREADS, 1)
         {
             constexpr int KHP = (KH + 31) / 32 * 32;
             float2* oimg = reinterpret_cast<float2*>(out) + tile * (long long)(H * MO);
-            if (gt < KHP) {
-                if (gt < KH) split_store<C, true>(buf, twU, oimg, 0, gt);
-            } else {
-                const int u = gt - KHP;
-                const int q1 = 1 + u / KH, k = u - (q1 - 1) * KH;
-                if (q1 < CA) split_store<C, false>(buf, twU, oimg, q1, k);
+#pragma unroll 1
+            for (int t = gt; t < KHP + (CA - 1) * KH; t += GT) {
+                if (t < KHP) {
+                    if (t < KH) split_store<C, true>(buf, twU, oimg, 0, t);
+                } else {
+                    const int u = t - KHP;
+                    const int q1 = 1 + u / KH, k = u - (q1 - 1) * KH;
+                    split_store<C, false>(buf, twU, oimg, q1, k);
+                }
             }
         }
         // release: every warp hands the stage back on its own (no group barrier at the tile end)
@@ -262,6 +266,7 @@ __global__ void __launch_bounds__(C::THREADS, 1)
     pipe_irfft2_kernel(const float* __restrict__ in, float* __restrict__ out, long long nimg,
                        const float2* __restrict__ tables, float scale)
 {
+    static_assert(C::kInverseOk, "inverse kernel: group too small for the one-round merge step");
     constexpr int H = C::H, M = C::M, RA = C::RA, RB = C::RB, CA = C::CA, CB = C::CB, GT = C::GT, NG = C::NG, NS = C::NS;
     constexpr int KH = C::KH, PI = C::PI;
     extern __shared__ __align__(128) unsigned char smem_raw[];
