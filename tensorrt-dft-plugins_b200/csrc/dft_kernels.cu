@@ -183,11 +183,16 @@ __device__ __forceinline__ unsigned produce_tile(const KParams& p, long long til
         }
         return 0;
     } else {
-        // rows: F1D reads nrows*M packed-complex (= real pairs), I1D reads nrows*(M+1) complex
-        const int M = p.M, P = p.P;
-        const int per_row = (MODE == dft::MODE_F1D) ? M : M + 1;
-        const long long first = tile * p.G;
-        const int nrows = (int)((p.nunits - first) < p.G ? (p.nunits - first) : p.G);
+        // contiguous tiles.  rows: F1D reads nrows*M packed-complex (= real pairs), I1D nrows*(M+1) complex;
+        // fused 2-D: the same per image row, H rows per image, G images per tile (pitch == row length)
+        const int M = p.M;
+        const bool fwd_side = (MODE == dft::MODE_F1D || MODE == dft::MODE_F2D);
+        const bool two_d = (MODE == dft::MODE_F2D || MODE == dft::MODE_I2D);
+        const int per_row = fwd_side ? M : M + 1;
+        const int P = two_d ? per_row : p.P;
+        const long long first = tile * p.G * (two_d ? p.H : 1);
+        const long long units_left = (p.nunits - tile * p.G) < p.G ? (p.nunits - tile * p.G) : p.G;
+        const int nrows = (int)(units_left * (two_d ? p.H : 1));
         const float* src = in + first * per_row * 2;
         const long long nbytes = (long long)nrows * per_row * 8;
         if (!p.pad && P == per_row && (((uintptr_t)src) & 15) == 0 && (nbytes & 15) == 0 && nbytes < (1 << 20)) {
@@ -284,10 +289,11 @@ __global__ void __launch_bounds__(kPipeThreads, 1)
             tb += (bytes + 15) / 16 * 16;
             return dst;
         };
-        if (MODE == dft::MODE_C2C_COLS) {
+        if (MODE == dft::MODE_C2C_COLS || MODE == dft::MODE_F2D || MODE == dft::MODE_I2D) {
             p.tw_col = (const float2*)stash(p_in.tw_col, p_in.col.n * 8);
             p.perm_col = (const int*)stash(p_in.perm_col, p_in.col.n * 4);
-        } else {
+        }
+        if (MODE != dft::MODE_C2C_COLS) {
             p.tw_row = (const float2*)stash(p_in.tw_row, p_in.row.n * 8);
             p.perm_row = (const int*)stash(p_in.perm_row, p_in.row.n * 4);
             p.tw_unt = (const float2*)stash(p_in.tw_unt, (p_in.M + 1) * 8);
@@ -332,6 +338,8 @@ __global__ void __launch_bounds__(kPipeThreads, 1)
         const int s = (int)(it % ns);
         float2* buf = reinterpret_cast<float2*>(smem_raw + (size_t)s * stage_bytes);
         gp_wait(full0 + 8 * s, (unsigned)((it / ns) & 1));
+        if constexpr (MODE == dft::MODE_F2D) dft::program_f2d<GroupCtx, false>(p, tile, buf, in, out, ctx);
+        if constexpr (MODE == dft::MODE_I2D) dft::program_i2d<GroupCtx, false>(p, tile, buf, in, out, ctx);
         if constexpr (MODE == dft::MODE_F1D) dft::program_f1d<GroupCtx, false>(p, tile, buf, in, out, ctx);
         if constexpr (MODE == dft::MODE_I1D) dft::program_i1d<GroupCtx, false>(p, tile, buf, in, out, ctx);
         if constexpr (MODE == dft::MODE_C2C_COLS) dft::program_cols<GroupCtx, false>(p, tile, buf, in, out, ctx);
@@ -369,6 +377,8 @@ pipe_fn pipe_kernel_for_geo(int mode, const dft::LineFFT& f)
 pipe_fn pipe_kernel_for(int mode)
 {
     switch (mode) {
+        case dft::MODE_F2D: return pipe_tile_kernel<dft::MODE_F2D>;
+        case dft::MODE_I2D: return pipe_tile_kernel<dft::MODE_I2D>;
         case dft::MODE_F1D: return pipe_tile_kernel<dft::MODE_F1D>;
         case dft::MODE_I1D: return pipe_tile_kernel<dft::MODE_I1D>;
         case dft::MODE_C2C_COLS: return pipe_tile_kernel<dft::MODE_C2C_COLS>;
@@ -703,9 +713,10 @@ static int realize_plan(trt_dft_plan_s* pl, trt_dft_plan_t* plan_out)
             const int stage = (r.kp.smem_bytes - dft::kBarrierBytes + 127) / 128 * 128;
             int ns = std::min(4, (dft::kSmemMax - 256) / std::max(stage, 1));
             // tables (twiddles, permutation) ride in shared memory when they fit beside >= 2 stages
+            const bool m2d = r.kp.mode == dft::MODE_F2D || r.kp.mode == dft::MODE_I2D;
             const int tab_bytes = r.kp.mode == dft::MODE_C2C_COLS
                                       ? r.kp.col.n * 12 + 64
-                                      : r.kp.row.n * 12 + (r.kp.M + 1) * 8 + 64;
+                                      : r.kp.row.n * 12 + (r.kp.M + 1) * 8 + 64 + (m2d ? r.kp.col.n * 12 + 64 : 0);
             int tables = 0;
             if (ns >= 2) {
                 int ns_t = std::min(4, (dft::kSmemMax - 256 - tab_bytes) / std::max(stage, 1));

@@ -55,42 +55,51 @@ DFT_HD void load_contig(Ctx& ctx, float* dst, const float* src, long long nfloat
 }
 
 // ---- MODE_F2D: fused rfft2 of G images per tile ---------------------------------------------
-template <class Ctx>
+template <class Ctx, bool LOAD = true>
 DFT_HD void program_f2d(const KParams& p, long long tile, float2* buf, const float* in, float* out, Ctx& ctx)
 {
     const int H = p.H, M = p.M, Mo = p.M + 1;
     const long long first = tile * p.G;
     const int nimg = (int)((p.nunits - first) < p.G ? (p.nunits - first) : p.G);
-    load_contig(ctx, (float*)buf, in + first * H * p.W, (long long)nimg * H * p.W);
+    if (LOAD) load_contig(ctx, (float*)buf, in + first * H * p.W, (long long)nimg * H * p.W);
     run_line_fft(p.row, false, buf, nimg * H, M, p.tw_row, 0, 0, ctx);
     run_line_fft(p.col, true, buf, nimg * M, M, p.tw_col, M, H * M, ctx);
+    // 2-D real-FFT split, two outputs per item: X[q][k] and X[(H-q)%H][M-k] share the pair
+    // Y[q][k], Y[(H-q)%H][(M-k)%M].  k = M/2 (M even) is produced twice with identical values.
     float2* o = (float2*)out + first * H * Mo;
-    const int per_img = H * Mo;
+    const int KH = M / 2 + 1;
+    const int per_img = H * KH;
     const int total = nimg * per_img;
+    const unsigned imag = magic_of((unsigned)per_img), kmag = magic_of((unsigned)KH);
     for (int idx = ctx.tid; idx < total; idx += ctx.nthr) {
-        const int img = idx / per_img;
+        const int img = fdiv(idx, imag);
         const int rem = idx - img * per_img;
-        const int q = rem / Mo;
-        const int k = rem - q * Mo;
-        const int k1 = (k == M) ? 0 : k;
-        const int k2 = (k == 0 || k == M) ? 0 : M - k;
+        const int q = fdiv(rem, kmag);
+        const int k = rem - q * KH;
+        const int kk = M - k;
         const int q2 = (q == 0) ? 0 : H - q;
         const float2* ib = buf + img * H * M;
-        const float2 z1 = ib[DFT_LDT(p.perm_col + q) * M + DFT_LDT(p.perm_row + k1)];
-        const float2 z2 = ib[DFT_LDT(p.perm_col + q2) * M + DFT_LDT(p.perm_row + k2)];
-        o[idx] = untangle(z1, z2, DFT_LDT(p.tw_unt + k));
+        const float2 z1 = ib[DFT_LDT(p.perm_col + q) * M + DFT_LDT(p.perm_row + k)];
+        const float2 z2 = ib[DFT_LDT(p.perm_col + q2) * M + DFT_LDT(p.perm_row + (k == 0 ? 0 : kk))];
+        const float2 w = DFT_LDT(p.tw_unt + k);
+        const float sx = z1.x + z2.x, sy = z1.y - z2.y;
+        const float dx = z1.x - z2.x, dy = z1.y + z2.y;
+        const float tx = 0.5f * (w.x * dx - w.y * dy), ty = 0.5f * (w.x * dy + w.y * dx);
+        float2* oi = o + (long long)img * H * Mo;
+        oi[q * Mo + k] = float2{0.5f * sx + ty, 0.5f * sy - tx};
+        oi[q2 * Mo + kk] = float2{0.5f * sx - ty, -0.5f * sy - tx};
     }
     ctx.sync();
 }
 
 // ---- MODE_I2D: fused irfft2 --------------------------------------------------------------------
-template <class Ctx>
+template <class Ctx, bool LOAD = true>
 DFT_HD void program_i2d(const KParams& p, long long tile, float2* buf, const float* in, float* out, Ctx& ctx)
 {
     const int H = p.H, M = p.M, P = p.M + 1;
     const long long first = tile * p.G;
     const int nimg = (int)((p.nunits - first) < p.G ? (p.nunits - first) : p.G);
-    load_contig(ctx, (float*)buf, in + first * H * P * 2, (long long)nimg * H * P * 2);
+    if (LOAD) load_contig(ctx, (float*)buf, in + first * H * P * 2, (long long)nimg * H * P * 2);
     run_line_fft(p.col, true, buf, nimg * P, P, p.tw_col, P, H * P, ctx);
     merge_rows(buf, nimg * H, P, M, p.tw_unt, 0, ctx.tid, ctx.nthr);
     ctx.sync();
@@ -99,10 +108,11 @@ DFT_HD void program_i2d(const KParams& p, long long tile, float2* buf, const flo
     const int per_img = H * M;
     const int total = nimg * per_img;
     const float sc = p.scale;
+    const unsigned imag = magic_of((unsigned)per_img), mmag = magic_of((unsigned)M);
     for (int idx = ctx.tid; idx < total; idx += ctx.nthr) {
-        const int img = idx / per_img;
+        const int img = fdiv(idx, imag);
         const int rem = idx - img * per_img;
-        const int r = rem / M;
+        const int r = fdiv(rem, mmag);
         const int n = rem - r * M;
         const float2 z = buf[(img * H + DFT_LDT(p.perm_col + r)) * P + DFT_LDT(p.perm_row + n)];
         o[idx] = float2{z.x * sc, z.y * sc};
