@@ -203,7 +203,7 @@ __global__ void __launch_bounds__(C::THREADS, 1)
         pipe::mbar_wait(full0 + 8 * s, (unsigned)((it / NS) & 1));
 
         // rows, DIF step RA: elements b + a*RB
-#pragma unroll 1
+#pragma unroll 2
         for (int t = gt; t < H * RB; t += GT) {
             const int row = t / RB, b = t - row * RB;
             float2* p = buf + row * M + b;
@@ -215,7 +215,7 @@ __global__ void __launch_bounds__(C::THREADS, 1)
         }
         pipe::group_sync(bar_id, GT);
         // rows, DIF step RB: contiguous chunk; frequency k = k1 + RA*k2 stays at k1*RB + k2
-#pragma unroll 1
+#pragma unroll 2
         for (int t = gt; t < H * RA; t += GT) {
             float2* p = buf + t * RB;
             float2 v[RB];
@@ -225,7 +225,7 @@ __global__ void __launch_bounds__(C::THREADS, 1)
         }
         pipe::group_sync(bar_id, GT);
         // columns, DIF step CA: rows b + a*CB; threads run along the row
-#pragma unroll 1
+#pragma unroll 2
         for (int t = gt; t < CB * M; t += GT) {
             const int b = t / M;
             float2* p = buf + t;
