@@ -69,6 +69,17 @@ int trt_dft_plan_create(trt_dft_plan_t* plan, int direction, int rank, const int
  */
 int trt_dft_plan_create_c2c(trt_dft_plan_t* plan, int direction, int64_t n, int64_t outer, int64_t inner, float scale);
 
+/*
+ * Pencil decomposition helper (no counterpart in the single-GPU reference, dft_plugins.cpp:341 "assuming
+ * single GPU"): makes a rank-1 FORWARD plan over `batch` rows write its result split by columns, ready to
+ * be the send buffer of an all-to-all.  Rows are taken in images of `rows_per_image`; inside each image the
+ * columns [col_starts[j], col_starts[j+1]) of all its rows form one contiguous block (block j goes to rank
+ * j), blocks in rank order.  col_starts has nparts+1 entries, col_starts[0] = 0, col_starts[nparts] =
+ * dims[0]/2+1; nparts <= 8; nparts = 0 restores the ordinary layout.  Total output size is unchanged.
+ * Call before trt_dft_exec, not concurrently with it.
+ */
+int trt_dft_plan_set_column_split(trt_dft_plan_t plan, int nparts, const int64_t* col_starts, int64_t rows_per_image);
+
 /* Replaces the workSize out-parameter of cufftXtMakePlanMany (dft_plugins.cpp:175) that
  * getWorkspaceSize reports (:114-129).  0 for every single-kernel plan. */
 size_t trt_dft_workspace_bytes(trt_dft_plan_t plan);

@@ -747,6 +747,24 @@ static int realize_plan(trt_dft_plan_s* pl, trt_dft_plan_t* plan_out)
     return TRT_DFT_OK;
 }
 
+int trt_dft_plan_set_column_split(trt_dft_plan_t plan, int nparts, const int64_t* col_starts, int64_t rows_per_image)
+{
+    if (!plan || nparts < 0 || nparts > 8 || (nparts > 0 && (!col_starts || rows_per_image < 1))) return TRT_DFT_ERR_INVALID_ARG;
+    if (plan->launches.size() != 1 || plan->launches[0].kp.mode != dft::MODE_F1D) return TRT_DFT_ERR_UNSUPPORTED;
+    KParams& k = plan->launches[0].kp;
+    const int Mo = k.M + 1;
+    if (nparts > 0) {
+        if (col_starts[0] != 0 || col_starts[nparts] != Mo || k.nunits % rows_per_image != 0 || k.nunits > (1LL << 30))
+            return TRT_DFT_ERR_INVALID_ARG;
+        for (int j = 0; j < nparts; ++j)
+            if (col_starts[j + 1] < col_starts[j]) return TRT_DFT_ERR_INVALID_ARG;
+    }
+    k.pack_n = nparts;
+    for (int j = 0; j <= nparts; ++j) k.pack_c0[j] = (int)col_starts[j];
+    k.pack_hn = (int)rows_per_image;
+    return TRT_DFT_OK;
+}
+
 size_t trt_dft_workspace_bytes(trt_dft_plan_t plan)
 {
     return plan ? plan->pd.ws_bytes : 0;

@@ -120,6 +120,16 @@ DFT_HD void program_i2d(const KParams& p, long long tile, float2* buf, const flo
     ctx.sync();
 }
 
+// Column-split ("packed for all-to-all") position of element (global row R, column k); see KParams::pack_n.
+DFT_HD long long packed_index(const KParams& p, int R, int k, int Mo)
+{
+    const int b = R / p.pack_hn, rl = R - b * p.pack_hn;
+    int j = 0;
+    for (int t = 1; t < p.pack_n; ++t) j += (k >= p.pack_c0[t]) ? 1 : 0;
+    const int c0 = p.pack_c0[j], cn = p.pack_c0[j + 1] - c0;
+    return (long long)b * p.pack_hn * Mo + (long long)p.pack_hn * c0 + (long long)rl * cn + (k - c0);
+}
+
 // ---- MODE_F1D: G rows per tile, W = 2M --------------------------------------------------------
 // LOAD = false: the tile is already in `buf` (the pipelined kernel's producer warps put it there).
 template <class Ctx, bool LOAD = true>
@@ -166,9 +176,18 @@ DFT_HD void program_f1d(const KParams& p, long long tile, float2* buf, const flo
         const float sx = z1.x + z2.x, sy = z1.y - z2.y;   // z1 + conj z2
         const float dx = z1.x - z2.x, dy = z1.y + z2.y;   // z1 - conj z2
         const float tx = 0.5f * (w.x * dx - w.y * dy), ty = 0.5f * (w.x * dy + w.y * dx);
-        float2* orow = o + (long long)r * Mo;
-        orow[k] = float2{0.5f * sx + ty, 0.5f * sy - tx};
-        if (kk != k) orow[kk] = float2{0.5f * sx - ty, -0.5f * sy - tx};
+        const float2 x1 = float2{0.5f * sx + ty, 0.5f * sy - tx};
+        const float2 x2 = float2{0.5f * sx - ty, -0.5f * sy - tx};
+        if (p.pack_n == 0) {
+            float2* orow = o + (long long)r * Mo;
+            orow[k] = x1;
+            if (kk != k) orow[kk] = x2;
+        } else {
+            float2* ob = (float2*)out;
+            const int R = (int)first + r;
+            ob[packed_index(p, R, k, Mo)] = x1;
+            if (kk != k) ob[packed_index(p, R, kk, Mo)] = x2;
+        }
     }
     ctx.sync();
 }

@@ -65,6 +65,12 @@ struct KParams {
     long long chunks;        // cols mode: column chunks per slab = ceil(inner / G)
     int pad;                 // rows modes: 1 = power-of-two rows stored skewed in shared memory,
                              // physical index p + p/16 + p/256 (kills the 16-way bank conflicts)
+    // MODE_F1D only: write the result column-split for an all-to-all (pencil decomposition).  Rows come in
+    // images of pack_hn rows; within an image, columns [pack_c0[j], pack_c0[j+1]) of all its rows form the
+    // contiguous block destined for rank j.  pack_n == 0: ordinary [rows][M+1] output.
+    int pack_n;
+    int pack_c0[9];
+    int pack_hn;
     int in_place_ok;         // informational
     int io_align;            // 16 if in/out base pointers and unit strides allow 16-byte bulk copies
 };

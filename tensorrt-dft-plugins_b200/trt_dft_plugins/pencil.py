@@ -81,4 +81,50 @@ class PencilRfft2:
     def forward(self, x_local):
         """x_local: this rank's row band [B, H_r, W] (fp32).  Returns its column band [B, H, C_r, 2]."""
         assert tuple(x_local.shape) == (self.B, self.hn, self.W)
-        return self.col_pass(self.transpose(self.row_pass(x_local)))
+        if self._row_fft is not None or self._col_fft is not None or not x_local.is_cuda or self.world == 1:
+            return self.col_pass(self.transpose(self.row_pass(x_local)))
+        return self._forward_fused(x_local)
+
+    # ---- GPU path: pack fused into the row pass, one all-to-all per image straight into place ----------
+    def _fused_plans(self):
+        if getattr(self, "_fplans", None) is None:
+            from . import capi
+            import ctypes
+            rows = capi.Plan(capi.FORWARD, (self.W,), self.hn)                   # one image's row band per launch
+            L = capi.lib()
+            L.trt_dft_plan_set_column_split.restype = ctypes.c_int
+            L.trt_dft_plan_set_column_split.argtypes = [ctypes.c_void_p, ctypes.c_int, ctypes.POINTER(ctypes.c_int64), ctypes.c_int64]
+            starts = [c0 for (c0, _) in self.col_spans] + [self.Mo]
+            arr = (ctypes.c_int64 * len(starts))(*starts)
+            rc = L.trt_dft_plan_set_column_split(rows.handle, self.world, arr, self.hn)
+            if rc != 0:
+                raise capi.DftError(f"trt_dft_plan_set_column_split failed with status {rc}")
+            cols = capi.C2CPlan(capi.FORWARD, self.H, 1, self.cn)               # one image's column band per launch
+            self._fplans = (rows, cols)
+        return self._fplans
+
+    def _forward_fused(self, x_local):
+        """Row pass of image b writes its spectrum already split by destination rank (the send buffer of the
+        all-to-all); the all-to-all of image b lands directly in z[b] = [H, C_r] (blocks arrive in source-rank
+        order = row order), so there is no pack or unpack copy, and it overlaps the row pass of image b+1 and
+        the column pass of image b-1."""
+        rows, cols = self._fused_plans()
+        B, dev = self.B, x_local.device
+        send = torch.empty(B, self.hn * self.Mo, 2, dtype=torch.float32, device=dev)
+        z = torch.empty(B, self.H, self.cn, 2, dtype=torch.float32, device=dev)
+        in_splits = [self.hn * cn * 2 for (_, cn) in self.col_spans]
+        out_splits = [hn_s * self.cn * 2 for (_, hn_s) in self.row_spans]
+        works = []
+        for b in range(B):
+            rows.exec(x_local[b], send[b])
+            if self.world == 1:
+                z[b].view(-1).copy_(send[b].view(-1))
+                works.append(None)
+            else:
+                works.append(dist.all_to_all_single(z[b].view(-1), send[b].view(-1), output_split_sizes=out_splits,
+                                                    input_split_sizes=in_splits, group=self.group, async_op=True))
+        for b in range(B):
+            if works[b] is not None:
+                works[b].wait()
+            cols.exec(z[b], z[b])
+        return z
