@@ -166,19 +166,26 @@ __device__ __forceinline__ unsigned produce_tile(const KParams& p, long long til
         const int N = p.H, P = p.P;
         const long long o_ = tile / p.chunks, c_ = tile - o_ * p.chunks, col0 = c_ * p.G;
         const int ncol = (int)((p.inner - col0) < p.G ? (p.inner - col0) : p.G);
-        const float2* src = (const float2*)in + o_ * N * p.inner + col0;
+        const int n1s = p.n1split > 1 ? p.n1split : 1;   // four-step first pass: rows n1 + n1split*n2 of image o_hi
+        const long long o_hi = o_ / n1s;
+        const int n1 = (int)(o_ - o_hi * n1s);
+        const long long ntot = (long long)n1s * N;
+        const float2* img = (const float2*)in + o_hi * ntot * p.inner + col0;
+        auto src_row = [&](int n) -> const float2* {
+            long long row = n1 + (long long)n1s * n;
+            if (p.rev_in) row = (row == 0) ? 0 : ntot - row;
+            return img + row * p.inner;
+        };
         if (NP % ncol == 0) {
             const int rstep = NP / ncol, j0 = pt % ncol, n0 = pt / ncol;
-            const float2* s0 = src + (long long)n0 * p.inner + j0;
             float2* d0 = buf + n0 * P + j0;
-            const long long sstep = (long long)rstep * p.inner;
             const int dstep = rstep * P;
 #pragma unroll 4
-            for (int n = n0; n < N; n += rstep, s0 += sstep, d0 += dstep) cp_async8(d0, s0);
+            for (int n = n0; n < N; n += rstep, d0 += dstep) cp_async8(d0, src_row(n) + j0);
         } else {
             for (int idx = pt; idx < N * ncol; idx += NP) {
                 const int n = idx / ncol, j = idx - n * ncol;
-                cp_async8(buf + n * P + j, src + (long long)n * p.inner + j);
+                cp_async8(buf + n * P + j, src_row(n) + j);
             }
         }
         return 0;
@@ -652,6 +659,7 @@ static int realize_plan(trt_dft_plan_s* pl, trt_dft_plan_t* plan_out)
         if (l.tw_unt_id >= 0) r.kp.tw_unt = (const float2*)(base + tw_off[l.tw_unt_id]);
         if (l.perm_row_id >= 0) r.kp.perm_row = (const int*)(base + perm_off[l.perm_row_id]);
         if (l.perm_col_id >= 0) r.kp.perm_col = (const int*)(base + perm_off[l.perm_col_id]);
+        if (l.tw_four_id >= 0) r.kp.tw_four = (const float2*)(base + tw_off[l.tw_four_id]);
         if (r.kp.mode != dft::MODE_C2C_COLS) r.kp.threads = 256;
         r.fn = kernel_for(r.kp.mode, r.kp.threads);
         r.src = l.src;

@@ -30,6 +30,7 @@ struct Launch {
     int src, dst;          // BufSel
     int tw_row_id = -1, tw_col_id = -1, tw_unt_id = -1;
     int perm_row_id = -1, perm_col_id = -1;
+    int tw_four_id = -1;   // four-step first pass: w_Ntot^j table
     std::string name;
 };
 
@@ -232,10 +233,47 @@ struct Planner {
         pd->launches.push_back(l);
     }
 
+    // Long strided axes (a column tile of >= 4 x 8 bytes no longer fits twice in shared memory) run as a
+    // four-step FFT, N = N1*N2: pass 1 gathers rows n1 + N1*n2, transforms over n2 (length N2), multiplies
+    // by w_N^(n1*k2) and stores them as the contiguous rows n1*N2 + k2 of the workspace; pass 2 transforms
+    // over n1 (length N1, row stride N2) and leaves natural order.  Both passes use full-width coalesced
+    // tiles.  The inverse reads pass 1's rows index-reversed instead of using reversed output tables.
+    bool add_cols_four_step(bool inverse, long long outer, int N, long long inner, int src, int dst, float scale)
+    {
+        if (src == BUF_WS || getenv("TRT_DFT_NO_FOURSTEP")) return false;
+        if ((long long)N * 8 * 4 * 2 <= kSmemMax - 1024) return false;     // a 4-wide tile still fits twice: one pass is fine
+        int best1 = 0;
+        for (int n2 = 2; n2 <= 2048; ++n2) {
+            if (N % n2) continue;
+            const int n1 = N / n2;
+            LineFFT f1, f2;
+            if (n1 < 2 || n1 > 2048 || !make_line_fft(n1, false, &f1) || !make_line_fft(n2, false, &f2)) continue;
+            auto bal = [](int a, int b) { return a > b ? (double)a / b : (double)b / a; };
+            if (!best1 || bal(n1, n2) < bal(best1, N / best1) || (bal(n1, n2) == bal(best1, N / best1) && n2 > N / best1)) best1 = n1;
+        }
+        if (!best1) return false;
+        const int N1 = best1, N2 = N / best1;
+        const size_t bytes = (size_t)outer * N * inner * 8;
+        pd->ws_bytes = std::max(pd->ws_bytes, bytes);
+        const size_t before = pd->launches.size();
+        add_cols(false, outer * N1, N2, inner, src, BUF_WS, 1.0f, /*allow_four_step=*/false);
+        {
+            Launch& l = pd->launches[before];
+            l.kp.n1split = N1;
+            l.kp.rev_in = inverse ? 1 : 0;
+            l.tw_four_id = add_tw(make_twiddles(N, N));
+            l.name += " [four-step pass 1 of " + std::to_string(N) + "]";
+        }
+        add_cols(false, outer, N1, (long long)N2 * inner, BUF_WS, dst, scale, false);
+        pd->launches.back().name += " [four-step pass 2]";
+        return true;
+    }
+
     // complex FFT of length N along a strided axis of data[outer][N][inner]
-    void add_cols(bool inverse, long long outer, int N, long long inner, int src, int dst, float scale)
+    void add_cols(bool inverse, long long outer, int N, long long inner, int src, int dst, float scale, bool allow_four_step = true)
     {
         if (N == 1 && src == dst && scale == 1.0f) return;   // identity
+        if (allow_four_step && add_cols_four_step(inverse, outer, N, inner, src, dst, scale)) return;
         KParams k = base(MODE_C2C_COLS);
         k.H = N;
         make_line_fft(N, false, &k.col);
@@ -245,6 +283,8 @@ struct Planner {
         {
             long long t2 = 16;
             while (t2 > 1 && t2 * N * 8 > (kSmemMax - 1024) / 2) t2 /= 2;
+            // short axes: widen the tile to ~32 KB so that per-tile overheads (barriers, pipeline handshakes) amortise
+            while (t2 < 64 && t2 * 2 * N * 8 <= 32 * 1024) t2 *= 2;
             if (t2 >= 4) tm = t2;
         }
         if (const char* e = getenv("TRT_DFT_TM")) tm = atoll(e);          // tuning override (benchmarks only)

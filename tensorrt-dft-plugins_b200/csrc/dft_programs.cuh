@@ -288,7 +288,18 @@ DFT_HD void program_cols(const KParams& p, long long tile, float2* buf, const fl
     const long long c_ = tile - o_ * p.chunks;
     const long long col0 = c_ * p.G;
     const int ncol = (int)((p.inner - col0) < p.G ? (p.inner - col0) : p.G);
-    const float2* src = (const float2*)in + o_ * N * p.inner + col0;
+    // source rows: contiguous, or (four-step first pass) every n1split-th row starting at n1, optionally
+    // index-reversed over the whole axis (inverse transform)
+    const int n1s = p.n1split > 1 ? p.n1split : 1;
+    const long long o_hi = o_ / n1s;
+    const int n1 = (int)(o_ - o_hi * n1s);
+    const long long ntot = (long long)n1s * N;
+    const float2* img = (const float2*)in + o_hi * ntot * p.inner + col0;
+    auto src_row = [&](int n) -> const float2* {
+        long long row = n1 + (long long)n1s * n;
+        if (p.rev_in) row = (row == 0) ? 0 : ntot - row;
+        return img + row * p.inner;
+    };
     const int total = N * ncol;
     // When the CTA size is a multiple of the tile width each thread keeps one column and walks
     // down the rows: no division in the loop, and the unrolled loads are all in flight together.
@@ -297,26 +308,25 @@ DFT_HD void program_cols(const KParams& p, long long tile, float2* buf, const fl
     const int j0 = ctx.tid % ncol, n0 = ctx.tid / ncol;
     if (!LOAD) {
     } else if (fixed_col) {
-        const float2* s0 = src + (long long)n0 * p.inner + j0;
         float2* d0 = buf + n0 * P + j0;
-        const long long sstep = (long long)rstep * p.inner;
         const int dstep = rstep * P;
-        int n = n0;
 #if defined(__CUDA_ARCH__)
 #pragma unroll 8
 #endif
-        for (; n < N; n += rstep, s0 += sstep, d0 += dstep) *d0 = DFT_LDG(s0);
+        for (int n = n0; n < N; n += rstep, d0 += dstep) *d0 = DFT_LDG(src_row(n) + j0);
     } else {
         for (int idx = ctx.tid; idx < total; idx += ctx.nthr) {
             const int n = idx / ncol;
             const int j = idx - n * ncol;
-            buf[n * P + j] = DFT_LDG(src + (long long)n * p.inner + j);
+            buf[n * P + j] = DFT_LDG(src_row(n) + j);
         }
     }
     if (LOAD) ctx.sync();
     run_line_fft(p.col, true, buf, ncol, P, p.tw_col, ncol, 0, ctx);
     float2* dst = (float2*)out + o_ * N * p.inner + col0;
     const float sc = p.scale;
+    const float cs = sc;
+    const bool four = p.n1split > 1;
     if (fixed_col) {
         float2* d0 = dst + (long long)n0 * p.inner + j0;
         const long long dstep2 = (long long)rstep * p.inner;
@@ -324,15 +334,17 @@ DFT_HD void program_cols(const KParams& p, long long tile, float2* buf, const fl
 #pragma unroll 4
 #endif
         for (int q = n0; q < N; q += rstep, d0 += dstep2) {
-            const float2 z = buf[DFT_LDT(p.perm_col + q) * P + j0];
-            *d0 = float2{z.x * sc, z.y * sc};
+            float2 z = buf[DFT_LDT(p.perm_col + q) * P + j0];
+            if (four) z = cmul(z, DFT_LDT(p.tw_four + (long long)n1 * q));
+            *d0 = float2{z.x * sc, z.y * cs};
         }
     } else {
         for (int idx = ctx.tid; idx < total; idx += ctx.nthr) {
             const int q = idx / ncol;
             const int j = idx - q * ncol;
-            const float2 z = buf[DFT_LDT(p.perm_col + q) * P + j];
-            dst[(long long)q * p.inner + j] = float2{z.x * sc, z.y * sc};
+            float2 z = buf[DFT_LDT(p.perm_col + q) * P + j];
+            if (four) z = cmul(z, DFT_LDT(p.tw_four + (long long)n1 * q));
+            dst[(long long)q * p.inner + j] = float2{z.x * sc, z.y * cs};
         }
     }
     ctx.sync();

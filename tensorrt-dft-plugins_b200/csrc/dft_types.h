@@ -71,6 +71,14 @@ struct KParams {
     int pack_n;
     int pack_c0[9];
     int pack_hn;
+    // MODE_C2C_COLS as the first pass of a four-step FFT of a long axis Ntot = n1split * N:
+    // slab o_ = (o_hi, n1) gathers rows n1 + n1split*n2 (n2 = 0..N-1) of image o_hi, stores them as the
+    // contiguous rows n1*N + k2 and multiplies row k2 by w_Ntot^(n1*k2) (tw_four, Ntot entries).
+    // n1split <= 1: ordinary pass.  rev_in: read the axis index-reversed, row (Ntot - n) mod Ntot for n,
+    // which turns the forward transform into the inverse one (IDFT(x)[n] = DFT(x reversed)[n]).
+    int n1split;
+    const float2* tw_four;
+    int rev_in;
     int in_place_ok;         // informational
     int io_align;            // 16 if in/out base pointers and unit strides allow 16-byte bulk copies
 };

@@ -42,6 +42,7 @@ extern "C" int dft_emu_exec(int direction, int rank, const int64_t* dims, int64_
         if (l.tw_unt_id >= 0) kp.tw_unt = pd.tw_tables[l.tw_unt_id].data();
         if (l.perm_row_id >= 0) kp.perm_row = pd.perm_tables[l.perm_row_id].data();
         if (l.perm_col_id >= 0) kp.perm_col = pd.perm_tables[l.perm_col_id].data();
+        if (l.tw_four_id >= 0) kp.tw_four = pd.tw_tables[l.tw_four_id].data();
         auto sel = [&](int s) -> float* {
             switch (s) {
                 case dft::BUF_IN: return const_cast<float*>(in);

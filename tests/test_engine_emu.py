@@ -59,7 +59,7 @@ SHAPES = [
     ((2, 1024), 1), ((2, 64), 1), ((3, 128), 1), ((1, 16384), 1), ((2, 1440), 1), ((2, 2 * 7 * 11 * 13), 1), ((2, 34), 1), ((3, 19), 1), ((1, 4096), 1),
     # 2-D: fused, multi-image tiles, odd widths, unsupported primes (naive), H == 1
     ((7, 8, 8), 2), ((3, 6, 10), 2), ((2, 5, 7), 2), ((2, 12, 18), 2), ((2, 17, 6), 2), ((2, 6, 38), 2),
-    ((700, 4, 4), 2), ((1, 1, 16), 2), ((2, 16, 1), 2), ((2, 3, 3), 2),
+    ((700, 4, 4), 2), ((1, 4096, 64), 2), ((2, 5120, 40), 2), ((1, 1, 16), 2), ((2, 16, 1), 2), ((2, 3, 3), 2),
     # 3-D
     ((2, 4, 6, 8), 3), ((2, 3, 5, 6), 3), ((1, 2, 3, 5, 7), 3), ((2, 1, 4, 4), 3), ((1, 17, 4, 6), 3),
 ]
