@@ -15,7 +15,7 @@ OUT = HERE / "trt_dft_plugins" / "libtrt_dft_plugins.so"
 
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a",
-    "-lineinfo", "-O3", "-std=c++17",
+    "-lineinfo", "-O3", "-std=c++17", "-t", "0",
     "-shared", "-Xcompiler", "-fPIC",
     "-I", str(HERE.parent / "include"),
 ]

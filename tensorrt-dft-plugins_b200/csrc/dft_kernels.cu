@@ -18,456 +18,21 @@
 #include <vector>
 
 #include "../../include/trt_dft.h"
-#include "dft_fused2d.cuh"
-#include "dft_pipe2d.cuh"
+#include "dft_spec.h"
+#include "dft_launch.h"
 #include "dft_planner.h"
 #include "dft_programs.cuh"
 
 namespace {
 
 using dft::KParams;
+using dft::kernel_fn;
+using dft::pipe_fn;
+using dft::kPipeThreads;
 
-__device__ __forceinline__ unsigned smem_u32(const void* p)
-{
-    return (unsigned)__cvta_generic_to_shared(p);
-}
-
-// CTA context for the tile programs.
-struct CtaCtx {
-    int tid, nthr;
-    unsigned bar;      // shared-memory address of the mbarrier
-    unsigned phase;    // parity of the next completion
-    bool bulk;         // this mode may use cp.async.bulk
-
-    __host__ __device__ __forceinline__ void sync()
-    {
-#if defined(__CUDA_ARCH__)
-        __syncthreads();
-#endif
-    }
-
-    // Whole-tile global->shared copy by the TMA unit (1-D bulk copy).  All threads call it with
-    // identical arguments; returns false (nothing done) when the copy is not 16-byte clean.
-    __host__ __device__ __forceinline__ bool bulk_load(void* dst, const void* src, long long bytes)
-    {
-#if defined(__CUDA_ARCH__)
-        if (!bulk || bytes <= 0 || (bytes & 15) || ((uintptr_t)src & 15) || bytes >= (1 << 20)) return false;
-        if (tid == 0) {
-            // order the previous tile's generic-proxy accesses before the async-proxy write
-            asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
-            asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"((unsigned)bytes)
-                         : "memory");
-            asm volatile(
-                "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
-                    smem_u32(dst)),
-                "l"(src), "r"((unsigned)bytes), "r"(bar)
-                : "memory");
-        }
-        asm volatile(
-            "{\n"
-            ".reg .pred p;\n"
-            "DFT_WAIT:\n"
-            "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
-            "@p bra DFT_DONE;\n"
-            "bra DFT_WAIT;\n"
-            "DFT_DONE:\n"
-            "}\n" ::"r"(bar),
-            "r"(phase)
-            : "memory");
-        phase ^= 1u;
-        return true;
-#else
-        (void)dst; (void)src; (void)bytes;
-        return false;
-#endif
-    }
-};
-
-template <int MODE, int NT>
-__global__ void __launch_bounds__(NT, NT == 512 ? 2 : 1) tile_kernel(const __grid_constant__ KParams p, const float* __restrict__ in,
-                                                              float* __restrict__ out)
-{
-    extern __shared__ __align__(128) unsigned char smem_raw[];
-    float2* buf = reinterpret_cast<float2*>(smem_raw);
-    CtaCtx ctx;
-    ctx.tid = threadIdx.x;
-    ctx.nthr = blockDim.x;
-    ctx.phase = 0;
-    ctx.bulk = (MODE == dft::MODE_F2D || MODE == dft::MODE_I2D || MODE == dft::MODE_F1D || MODE == dft::MODE_I1D);
-    ctx.bar = smem_u32(smem_raw + p.smem_bytes - dft::kBarrierBytes);
-    if (ctx.bulk) {
-        if (threadIdx.x == 0) {
-            asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(ctx.bar) : "memory");
-            asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
-            asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
-        }
-        __syncthreads();
-    }
-    for (long long tile = blockIdx.x; tile < p.ntiles; tile += gridDim.x) {
-        if constexpr (MODE == dft::MODE_F2D) dft::program_f2d(p, tile, buf, in, out, ctx);
-        if constexpr (MODE == dft::MODE_I2D) dft::program_i2d(p, tile, buf, in, out, ctx);
-        if constexpr (MODE == dft::MODE_F1D) dft::program_f1d(p, tile, buf, in, out, ctx);
-        if constexpr (MODE == dft::MODE_I1D) dft::program_i1d(p, tile, buf, in, out, ctx);
-        if constexpr (MODE == dft::MODE_F1D_ODD) dft::program_f1d_odd(p, tile, buf, in, out, ctx);
-        if constexpr (MODE == dft::MODE_I1D_ODD) dft::program_i1d_odd(p, tile, buf, in, out, ctx);
-        if constexpr (MODE == dft::MODE_C2C_COLS) dft::program_cols(p, tile, buf, in, out, ctx);
-    }
-}
-
-// ---- persistent pipelined variant of the generic engine -----------------------------------------
-// One CTA per SM: 2 producer warps stream tiles into a ring of `ns` shared-memory stages (cp.async /
-// LDGSTS element copies, or one TMA bulk copy when the tile is contiguous and 16-byte clean), `ng`
-// compute groups run the ordinary tile programs (LOAD = false) on their stage and hand it back.
-// Used for the row and strided-axis passes of images too large to fuse (BASELINE cfg4 / cfg5).
-constexpr int kPipeCompute = 512, kPipeProducers = 64, kPipeThreads = kPipeCompute + kPipeProducers;
-
-struct GroupCtx {
-    int tid, nthr, bar_id;
-    __host__ __device__ __forceinline__ void sync()
-    {
-#if defined(__CUDA_ARCH__)
-        asm volatile("bar.sync %0, %1;" ::"r"(bar_id), "r"(nthr) : "memory");
-#endif
-    }
-    __host__ __device__ __forceinline__ bool bulk_load(void*, const void*, long long) { return false; }
-};
-
-__device__ __forceinline__ void cp_async8(void* dst, const void* src)
-{
-    asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(smem_u32(dst)), "l"(src) : "memory");
-}
-__device__ __forceinline__ void cp_async4(void* dst, const void* src)
-{
-    asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(smem_u32(dst)), "l"(src) : "memory");
-}
-__device__ __forceinline__ void gp_wait(unsigned bar, unsigned parity)
-{
-    asm volatile(
-        "{\n"
-        ".reg .pred p;\n"
-        "GP_WAIT:\n"
-        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
-        "@p bra GP_DONE;\n"
-        "bra GP_WAIT;\n"
-        "GP_DONE:\n"
-        "}\n" ::"r"(bar),
-        "r"(parity)
-        : "memory");
-}
-
-// producer side: start the copies of one tile; returns the byte count of a bulk copy issued by
-// thread 0 (0 = element copies only)
-template <int MODE>
-__device__ __forceinline__ unsigned produce_tile(const KParams& p, long long tile, float2* buf, const float* in, int pt,
-                                                 unsigned full_bar)
-{
-    constexpr int NP = kPipeProducers;
-    if (MODE == dft::MODE_C2C_COLS) {
-        const int N = p.H, P = p.P;
-        const long long o_ = tile / p.chunks, c_ = tile - o_ * p.chunks, col0 = c_ * p.G;
-        const int ncol = (int)((p.inner - col0) < p.G ? (p.inner - col0) : p.G);
-        const int n1s = p.n1split > 1 ? p.n1split : 1;   // four-step first pass: rows n1 + n1split*n2 of image o_hi
-        const long long o_hi = o_ / n1s;
-        const int n1 = (int)(o_ - o_hi * n1s);
-        const long long ntot = (long long)n1s * N;
-        const float2* img = (const float2*)in + o_hi * ntot * p.inner + col0;
-        auto src_row = [&](int n) -> const float2* {
-            long long row = n1 + (long long)n1s * n;
-            if (p.rev_in) row = (row == 0) ? 0 : ntot - row;
-            return img + row * p.inner;
-        };
-        if (NP % ncol == 0) {
-            const int rstep = NP / ncol, j0 = pt % ncol, n0 = pt / ncol;
-            float2* d0 = buf + n0 * P + j0;
-            const int dstep = rstep * P;
-#pragma unroll 4
-            for (int n = n0; n < N; n += rstep, d0 += dstep) cp_async8(d0, src_row(n) + j0);
-        } else {
-            for (int idx = pt; idx < N * ncol; idx += NP) {
-                const int n = idx / ncol, j = idx - n * ncol;
-                cp_async8(buf + n * P + j, src_row(n) + j);
-            }
-        }
-        return 0;
-    } else {
-        // contiguous tiles.  rows: F1D reads nrows*M packed-complex (= real pairs), I1D nrows*(M+1) complex;
-        // fused 2-D: the same per image row, H rows per image, G images per tile (pitch == row length)
-        const int M = p.M;
-        const bool fwd_side = (MODE == dft::MODE_F1D || MODE == dft::MODE_F2D);
-        const bool two_d = (MODE == dft::MODE_F2D || MODE == dft::MODE_I2D);
-        const int per_row = fwd_side ? M : M + 1;
-        const int P = two_d ? per_row : p.P;
-        const long long first = tile * p.G * (two_d ? p.H : 1);
-        const long long units_left = (p.nunits - tile * p.G) < p.G ? (p.nunits - tile * p.G) : p.G;
-        const int nrows = (int)(units_left * (two_d ? p.H : 1));
-        const float* src = in + first * per_row * 2;
-        const long long nbytes = (long long)nrows * per_row * 8;
-        if (!p.pad && P == per_row && (((uintptr_t)src) & 15) == 0 && (nbytes & 15) == 0 && nbytes < (1 << 20)) {
-            if (pt == 0) {
-                asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(full_bar), "r"((unsigned)nbytes) : "memory");
-                asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
-                                 smem_u32(buf)),
-                             "l"(src), "r"((unsigned)nbytes), "r"(full_bar)
-                             : "memory");
-            }
-            return (unsigned)nbytes;
-        }
-        const unsigned mg = dft::magic_of((unsigned)per_row);
-        const int total = nrows * per_row;
-        if ((((uintptr_t)src) & 7) == 0) {
-            const float2* s2 = (const float2*)src;
-            for (int idx = pt; idx < total; idx += NP) {
-                const int r = dft::fdiv(idx, mg), k = idx - r * per_row;
-                cp_async8(buf + r * P + dft::phys(k, p.pad), s2 + idx);
-            }
-        } else {   // real rows that are only 4-byte aligned
-            for (int idx = pt; idx < total; idx += NP) {
-                const int r = dft::fdiv(idx, mg), k = idx - r * per_row;
-                float* d = (float*)(buf + r * P + dft::phys(k, p.pad));
-                cp_async4(d, src + 2 * idx);
-                cp_async4(d + 1, src + 2 * idx + 1);
-            }
-        }
-        return 0;
-    }
-}
-
-// Compile-time radix schedule of the transformed axis.  Injected into the kernel's private copy of
-// KParams, it lets the compiler fold the generic tile programs (radix switch, strides, magic divisors,
-// skew) down to immediates for registered lengths; GeoNone keeps everything run-time.
-struct GeoNone {
-    static constexpr bool kStatic = false;
-};
-template <int N_, int R0, int R1 = 1, int R2 = 1, int R3 = 1>
-struct GeoLine {
-    static constexpr bool kStatic = true;
-    static constexpr int N = N_;
-    static constexpr int nsteps = (R0 > 1) + (R1 > 1) + (R2 > 1) + (R3 > 1);
-    static_assert(R0 * R1 * R2 * R3 == N_, "schedule must multiply to N");
-    static constexpr bool pow2 = (N_ & (N_ - 1)) == 0;
-    __device__ static void apply(dft::LineFFT& f)
-    {
-        constexpr int r[4] = {R0, R1, R2, R3};
-        f.n = N_;
-        f.nsteps = nsteps;
-        int L = N_;
-#pragma unroll
-        for (int i = 0; i < 4; ++i) {
-            if (i >= nsteps) break;
-            f.radix[i] = r[i];
-            const unsigned m = (unsigned)(L / r[i]), bpl = (unsigned)(N_ / r[i]);
-            f.mmag[i] = m <= 1 ? 0u : (unsigned)(((1ull << 32) + m - 1) / m);
-            f.bmag[i] = bpl <= 1 ? 0u : (unsigned)(((1ull << 32) + bpl - 1) / bpl);
-            L /= r[i];
-        }
-    }
-};
-
-template <int MODE, class Geo = GeoNone>
-__global__ void __launch_bounds__(kPipeThreads, 1)
-    pipe_tile_kernel(const __grid_constant__ KParams p_in, const float* __restrict__ in, float* __restrict__ out, int ns, int ng,
-                     int stage_bytes, int tables_in_smem)
-{
-    extern __shared__ __align__(128) unsigned char smem_raw[];
-    const unsigned full0 = smem_u32(smem_raw + (size_t)ns * stage_bytes);
-    const unsigned empty0 = full0 + 8 * ns;
-    const int tid = threadIdx.x;
-    const int gt = kPipeCompute / ng;
-    KParams p = p_in;
-    if constexpr (Geo::kStatic) {
-        if (MODE == dft::MODE_C2C_COLS) {
-            Geo::apply(p.col);
-            p.H = Geo::N;
-        } else {
-            Geo::apply(p.row);
-            p.M = Geo::N;
-            p.W = 2 * Geo::N;
-            p.pad = (Geo::pow2 && Geo::N >= 32) ? 1 : 0;
-            constexpr int PP = Geo::N + (Geo::N >> 4) + (Geo::N >> 8) + 1;
-            p.P = (Geo::pow2 && Geo::N >= 32) ? PP : (MODE == dft::MODE_I1D ? Geo::N + 1 : Geo::N);
-        }
-    }
-    if (tables_in_smem) {
-        // twiddle / permutation tables move into shared memory once per (persistent) CTA
-        unsigned char* tb = smem_raw + (size_t)ns * stage_bytes + 2 * ns * 8 + 64;
-        auto stash = [&](const void* src, int bytes) -> void* {
-            void* dst = tb;
-            for (int i = tid * 4; i < bytes; i += kPipeThreads * 4) *(int*)(tb + i) = __ldg((const int*)((const unsigned char*)src + i));
-            tb += (bytes + 15) / 16 * 16;
-            return dst;
-        };
-        if (MODE == dft::MODE_C2C_COLS || MODE == dft::MODE_F2D || MODE == dft::MODE_I2D) {
-            p.tw_col = (const float2*)stash(p_in.tw_col, p_in.col.n * 8);
-            p.perm_col = (const int*)stash(p_in.perm_col, p_in.col.n * 4);
-        }
-        if (MODE != dft::MODE_C2C_COLS) {
-            p.tw_row = (const float2*)stash(p_in.tw_row, p_in.row.n * 8);
-            p.perm_row = (const int*)stash(p_in.perm_row, p_in.row.n * 4);
-            p.tw_unt = (const float2*)stash(p_in.tw_unt, (p_in.M + 1) * 8);
-        }
-    }
-    if (tid == 0) {
-        for (int s = 0; s < ns; ++s) {
-            asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(full0 + 8 * s), "r"(kPipeProducers) : "memory");
-            asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(empty0 + 8 * s), "r"(gt / 32) : "memory");
-        }
-        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
-        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
-    }
-    __syncthreads();
-
-    if (tid >= kPipeCompute) {
-        const int pt = tid - kPipeCompute;
-        long long it = 0;
-        for (long long tile = blockIdx.x; tile < p.ntiles; tile += gridDim.x, ++it) {
-            const int s = (int)(it % ns);
-            if (it >= ns) gp_wait(empty0 + 8 * s, (unsigned)(((it / ns) - 1) & 1));
-            asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
-            float2* buf = reinterpret_cast<float2*>(smem_raw + (size_t)s * stage_bytes);
-            const unsigned bar = full0 + 8 * s;
-            const unsigned bulk = produce_tile<MODE>(p, tile, buf, in, pt, bar);
-            if (bulk) {
-                if (pt != 0) asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
-            } else {
-                asm volatile("cp.async.mbarrier.arrive.noinc.shared::cta.b64 [%0];" ::"r"(bar) : "memory");
-            }
-        }
-        asm volatile("cp.async.wait_all;" ::: "memory");
-        return;
-    }
-    GroupCtx ctx;
-    const int g = tid / gt;
-    ctx.tid = tid - g * gt;
-    ctx.nthr = gt;
-    ctx.bar_id = 1 + g;
-    long long it = g;
-    for (long long tile = blockIdx.x + (long long)g * gridDim.x; tile < p.ntiles; tile += (long long)ng * gridDim.x, it += ng) {
-        const int s = (int)(it % ns);
-        float2* buf = reinterpret_cast<float2*>(smem_raw + (size_t)s * stage_bytes);
-        gp_wait(full0 + 8 * s, (unsigned)((it / ns) & 1));
-        if constexpr (MODE == dft::MODE_F2D) dft::program_f2d<GroupCtx, false>(p, tile, buf, in, out, ctx);
-        if constexpr (MODE == dft::MODE_I2D) dft::program_i2d<GroupCtx, false>(p, tile, buf, in, out, ctx);
-        if constexpr (MODE == dft::MODE_F1D) dft::program_f1d<GroupCtx, false>(p, tile, buf, in, out, ctx);
-        if constexpr (MODE == dft::MODE_I1D) dft::program_i1d<GroupCtx, false>(p, tile, buf, in, out, ctx);
-        if constexpr (MODE == dft::MODE_C2C_COLS) dft::program_cols<GroupCtx, false>(p, tile, buf, in, out, ctx);
-        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
-        __syncwarp();
-        if ((tid & 31) == 0) asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(empty0 + 8 * s) : "memory");
-    }
-}
-
-typedef void (*pipe_fn)(const KParams, const float*, float*, int, int, int, int);
-
-// registered lengths: (N, radix schedule) must equal what the planner chose for that axis
-#define DFT_GEO_LIST(X)          \
-    X(720, 16, 9, 5, 1)          \
-    X(720, 10, 9, 8, 1)          \
-    X(4096, 16, 16, 16, 1)       \
-    X(512, 2, 16, 16, 1)         \
-    X(1024, 4, 16, 16, 1)        \
-    X(2048, 8, 16, 16, 1)
-
-pipe_fn pipe_kernel_for_geo(int mode, const dft::LineFFT& f)
-{
-#define DFT_GEO_TRY(N_, A, B, C, D)                                                                                   \
-    if (f.n == N_ && f.nsteps == ((A > 1) + (B > 1) + (C > 1) + (D > 1)) && f.radix[0] == A && (B == 1 || f.radix[1] == B) && \
-        (C == 1 || f.radix[2] == C) && (D == 1 || f.radix[3] == D)) {                                              \
-        if (mode == dft::MODE_F1D) return pipe_tile_kernel<dft::MODE_F1D, GeoLine<N_, A, B, C, D>>;                 \
-        if (mode == dft::MODE_I1D) return pipe_tile_kernel<dft::MODE_I1D, GeoLine<N_, A, B, C, D>>;                 \
-        if (mode == dft::MODE_C2C_COLS) return pipe_tile_kernel<dft::MODE_C2C_COLS, GeoLine<N_, A, B, C, D>>;       \
-    }
-    DFT_GEO_LIST(DFT_GEO_TRY)
-#undef DFT_GEO_TRY
-    return nullptr;
-}
-
-pipe_fn pipe_kernel_for(int mode)
-{
-    switch (mode) {
-        case dft::MODE_F2D: return pipe_tile_kernel<dft::MODE_F2D>;
-        case dft::MODE_I2D: return pipe_tile_kernel<dft::MODE_I2D>;
-        case dft::MODE_F1D: return pipe_tile_kernel<dft::MODE_F1D>;
-        case dft::MODE_I1D: return pipe_tile_kernel<dft::MODE_I1D>;
-        case dft::MODE_C2C_COLS: return pipe_tile_kernel<dft::MODE_C2C_COLS>;
-        default: return nullptr;
-    }
-}
-
-template <int MODE>
-__global__ void __launch_bounds__(256) naive_kernel(const __grid_constant__ KParams p, const float* __restrict__ in,
-                                                    float* __restrict__ out)
-{
-    const long long stride = (long long)gridDim.x * blockDim.x;
-    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < p.nunits; i += stride) {
-        if constexpr (MODE == dft::MODE_NAIVE_ROWS_R2C) dft::naive_rows_r2c_elem(p, i, in, out);
-        if constexpr (MODE == dft::MODE_NAIVE_ROWS_C2R) dft::naive_rows_c2r_elem(p, i, in, out);
-        if constexpr (MODE == dft::MODE_NAIVE_COLS) dft::naive_cols_elem(p, i, in, out);
-    }
-}
-
-typedef void (*kernel_fn)(const KParams, const float*, float*);
-
-kernel_fn kernel_for(int mode, int threads)
-{
-    switch (mode) {
-        case dft::MODE_F2D: return tile_kernel<dft::MODE_F2D, 256>;
-        case dft::MODE_I2D: return tile_kernel<dft::MODE_I2D, 256>;
-        case dft::MODE_F1D: return tile_kernel<dft::MODE_F1D, 256>;
-        case dft::MODE_I1D: return tile_kernel<dft::MODE_I1D, 256>;
-        case dft::MODE_F1D_ODD: return tile_kernel<dft::MODE_F1D_ODD, 256>;
-        case dft::MODE_I1D_ODD: return tile_kernel<dft::MODE_I1D_ODD, 256>;
-        case dft::MODE_C2C_COLS:
-            return threads == 512 ? tile_kernel<dft::MODE_C2C_COLS, 512> : tile_kernel<dft::MODE_C2C_COLS, 256>;
-        case dft::MODE_NAIVE_ROWS_R2C: return naive_kernel<dft::MODE_NAIVE_ROWS_R2C>;
-        case dft::MODE_NAIVE_ROWS_C2R: return naive_kernel<dft::MODE_NAIVE_ROWS_C2R>;
-        case dft::MODE_NAIVE_COLS: return naive_kernel<dft::MODE_NAIVE_COLS>;
-        default: return nullptr;
-    }
-}
-
-// ---- shape-specialised fused 2-D kernels (dft_fused2d.cuh) ------------------------------------
-typedef void (*spec_fn)(const float*, float*, long long, const float2*, float);
-
-struct SpecEntry {
-    int H, W, RA, RB, CA, CB, NT;
-    int smem_f, smem_i;
-    spec_fn fwd, inv;
-    bool pipelined;      // dft_pipe2d.cuh: one persistent CTA per SM, needs 16-byte aligned in/out
-    int NT_inv = 0;      // threads of the inverse kernel when they differ from NT
-};
-
-template <class C>
-SpecEntry make_spec()
-{
-    return SpecEntry{C::H, C::W, C::RA, C::RB, C::CA, C::CB, C::NT, C::SMEM_F, C::SMEM_I,
-                     dft::fused_rfft2_kernel<C>, dft::fused_irfft2_kernel<C>, false};
-}
-
-template <class CF, class CI>
-SpecEntry make_pipe()
-{
-    static_assert(CF::H == CI::H && CF::W == CI::W && CF::RA == CI::RA && CF::RB == CI::RB && CF::CA == CI::CA && CF::CB == CI::CB, "");
-    SpecEntry e{CF::H, CF::W, CF::RA, CF::RB, CF::CA, CF::CB, CF::THREADS, CF::SMEM, CI::SMEM,
-                dft::pipe_rfft2_kernel<CF>, dft::pipe_irfft2_kernel<CI>, true};
-    e.NT_inv = CI::THREADS;
-    return e;
-}
-
-const SpecEntry* find_spec(int H, int W)
-{
-    static const SpecEntry table[] = {
-        //                     H    W   RA  RB  CA  CB  group threads, groups, stages
-        make_pipe<dft::PipeCfg<90, 180, 9, 10, 10, 9, 320, 2, 3>,      // forward: 2 x 320 threads, 96 registers
-                  dft::PipeCfg<90, 180, 9, 10, 10, 9, 480, 2, 3>>(),    // inverse: 2 x 480 (one-round merge)   (BASELINE cfg3)
-        //                      H    W   RA  RB  CA  CB   NT  min CTAs/SM
-        make_spec<dft::FusedCfg<128, 128, 8, 8, 16, 8, 256, 3>>(),     // FNO (BASELINE cfg2)
-        make_spec<dft::FusedCfg<64, 64, 8, 4, 8, 8, 256, 4>>(),
-    };
-    const bool no_pipe = getenv("TRT_DFT_NO_PIPE") != nullptr;   // benchmarking override
-    for (const auto& e : table)
-        if (e.H == H && e.W == W && !(no_pipe && e.pipelined)) return &e;
-    return nullptr;
-}
+using dft::SpecEntry;
+using dft::spec_fn;
+static const SpecEntry* find_spec(int H, int W) { return dft::find_spec(H, W); }
 
 // twR[(c-1)*RB + b] = w_M^(b c) | twC[(c-1)*CB + b] = w_H^(b c) | twU[k] = f * w_W^k, k = 0..M/2
 std::vector<float2> spec_tables(const SpecEntry& e, bool inverse, double scale)
@@ -661,7 +226,7 @@ static int realize_plan(trt_dft_plan_s* pl, trt_dft_plan_t* plan_out)
         if (l.perm_col_id >= 0) r.kp.perm_col = (const int*)(base + perm_off[l.perm_col_id]);
         if (l.tw_four_id >= 0) r.kp.tw_four = (const float2*)(base + tw_off[l.tw_four_id]);
         if (r.kp.mode != dft::MODE_C2C_COLS) r.kp.threads = 256;
-        r.fn = kernel_for(r.kp.mode, r.kp.threads);
+        r.fn = dft::tile_kernel_for(r.kp.mode, r.kp.threads);
         r.src = l.src;
         r.dst = l.dst;
         if (!r.fn) {
@@ -713,9 +278,9 @@ static int realize_plan(trt_dft_plan_s* pl, trt_dft_plan_t* plan_out)
             }
             r.grid = (int)std::min<long long>(r.kp.ntiles, (long long)num_sms * occ);
             // persistent pipelined variant for the big row / strided-axis passes
-            pipe_fn pf = pipe_kernel_for(r.kp.mode);
+            pipe_fn pf = dft::pipe_kernel_for(r.kp.mode);
             if (pf && !getenv("TRT_DFT_NO_GEO")) {
-                pipe_fn pg = pipe_kernel_for_geo(r.kp.mode, r.kp.mode == dft::MODE_C2C_COLS ? r.kp.col : r.kp.row);
+                pipe_fn pg = dft::pipe_kernel_for_geo(r.kp.mode, r.kp.mode == dft::MODE_C2C_COLS ? r.kp.col : r.kp.row);
                 if (pg) pf = pg;
             }
             const int stage = (r.kp.smem_bytes - dft::kBarrierBytes + 127) / 128 * 128;

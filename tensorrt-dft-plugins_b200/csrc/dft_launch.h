@@ -1,0 +1,18 @@
+// dft_launch.h -- kernel lookup functions shared between the executor (dft_kernels.cu) and the translation
+// units that instantiate the kernels (dft_tile_kernels.cu, dft_pipe_kernels.cu); split so that nvcc compiles
+// them in parallel.
+#pragma once
+#include "dft_types.h"
+
+namespace dft {
+
+typedef void (*kernel_fn)(const KParams, const float*, float*);
+typedef void (*pipe_fn)(const KParams, const float*, float*, int, int, int, int);
+
+constexpr int kPipeCompute = 512, kPipeProducers = 64, kPipeThreads = kPipeCompute + kPipeProducers;
+
+kernel_fn tile_kernel_for(int mode, int threads);           // nullptr: unknown mode
+pipe_fn pipe_kernel_for(int mode);                          // nullptr: mode has no pipelined variant
+pipe_fn pipe_kernel_for_geo(int mode, const LineFFT& f);    // nullptr: schedule not registered
+
+}  // namespace dft

@@ -124,9 +124,18 @@ DFT_HD void program_i2d(const KParams& p, long long tile, float2* buf, const flo
 DFT_HD long long packed_index(const KParams& p, int R, int k, int Mo)
 {
     const int b = R / p.pack_hn, rl = R - b * p.pack_hn;
-    int j = 0;
-    for (int t = 1; t < p.pack_n; ++t) j += (k >= p.pack_c0[t]) ? 1 : 0;
-    const int c0 = p.pack_c0[j], cn = p.pack_c0[j + 1] - c0;
+    // fully unrolled with constant indices: a run-time index into p.pack_c0 would push the kernel's
+    // private KParams copy into local memory
+    int c0 = p.pack_c0[0], cn = p.pack_c0[1] - p.pack_c0[0];
+#if defined(__CUDA_ARCH__)
+#pragma unroll
+#endif
+    for (int t = 1; t < 8; ++t) {
+        if (t < p.pack_n && k >= p.pack_c0[t]) {
+            c0 = p.pack_c0[t];
+            cn = p.pack_c0[t + 1] - p.pack_c0[t];
+        }
+    }
     return (long long)b * p.pack_hn * Mo + (long long)p.pack_hn * c0 + (long long)rl * cn + (k - c0);
 }
 
@@ -325,7 +334,6 @@ DFT_HD void program_cols(const KParams& p, long long tile, float2* buf, const fl
     run_line_fft(p.col, true, buf, ncol, P, p.tw_col, ncol, 0, ctx);
     float2* dst = (float2*)out + o_ * N * p.inner + col0;
     const float sc = p.scale;
-    const float cs = sc;
     const bool four = p.n1split > 1;
     if (fixed_col) {
         float2* d0 = dst + (long long)n0 * p.inner + j0;
@@ -333,10 +341,16 @@ DFT_HD void program_cols(const KParams& p, long long tile, float2* buf, const fl
 #if defined(__CUDA_ARCH__)
 #pragma unroll 4
 #endif
-        for (int q = n0; q < N; q += rstep, d0 += dstep2) {
-            float2 z = buf[DFT_LDT(p.perm_col + q) * P + j0];
-            if (four) z = cmul(z, DFT_LDT(p.tw_four + (long long)n1 * q));
-            *d0 = float2{z.x * sc, z.y * cs};
+        if (!four) {
+            for (int q = n0; q < N; q += rstep, d0 += dstep2) {
+                const float2 z = buf[DFT_LDT(p.perm_col + q) * P + j0];
+                *d0 = float2{z.x * sc, z.y * sc};
+            }
+        } else {
+            for (int q = n0; q < N; q += rstep, d0 += dstep2) {
+                const float2 z = cmul(buf[DFT_LDT(p.perm_col + q) * P + j0], DFT_LDT(p.tw_four + (long long)n1 * q));
+                *d0 = float2{z.x * sc, z.y * sc};
+            }
         }
     } else {
         for (int idx = ctx.tid; idx < total; idx += ctx.nthr) {
@@ -344,7 +358,7 @@ DFT_HD void program_cols(const KParams& p, long long tile, float2* buf, const fl
             const int j = idx - q * ncol;
             float2 z = buf[DFT_LDT(p.perm_col + q) * P + j];
             if (four) z = cmul(z, DFT_LDT(p.tw_four + (long long)n1 * q));
-            dst[(long long)q * p.inner + j] = float2{z.x * sc, z.y * cs};
+            dst[(long long)q * p.inner + j] = float2{z.x * sc, z.y * sc};
         }
     }
     ctx.sync();
