@@ -276,7 +276,9 @@ namespace dft {
 // registered lengths: (N, radix schedule) must equal what the planner chose for that axis
 #define DFT_GEO_ROWS(X)          \
     X(720, 16, 9, 5, 1)          \
-    X(4096, 16, 16, 16, 1)
+    X(4096, 16, 16, 16, 1)       \
+    X(1024, 4, 16, 16, 1)        \
+    X(2048, 8, 16, 16, 1)
 #define DFT_GEO_COLS(X) X(720, 10, 9, 8, 1)
 
 pipe_fn pipe_kernel_for_geo(int mode, const dft::LineFFT& f)
