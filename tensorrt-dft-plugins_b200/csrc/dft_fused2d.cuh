@@ -37,6 +37,10 @@ struct FusedCfg {
     static constexpr int PI = M + 1;              // inverse pitch (one-sided spectrum row)
     static constexpr int SMEM_F = (H * M + NTAB) * 8 + 16;
     static constexpr int SMEM_I = (H * PI + NTAB) * 8 + 16;
+    // Power-of-two chunk length: the forward kernel stores element e of chunk c at c*RB + (e ^ (c mod RB)).
+    // Without it, lanes reading "element j of consecutive chunks" (row step RB, and the column-pair step
+    // that walks consecutive frequencies k = c + RA*e) are RB * 8 bytes apart and collide 8-fold.
+    static constexpr bool SWZ = (RB & (RB - 1)) == 0 && RB >= 8 && (NT_ % 32 == 0) && (32 % RB == 0);
     static constexpr bool BULK_REAL = (H * W * 4) % 16 == 0;
     static constexpr bool BULK_CPLX = (H * PI * 8) % 16 == 0;
 };
@@ -136,17 +140,26 @@ __global__ void __launch_bounds__(C::NT, C::MINB)
             static_for<0, RA>([&](auto ac) { constexpr int a = decltype(ac)::value; v[a] = p[a * RB]; });
             dft_reg<RA>(v);
             static_for<1, RA>([&](auto cc) { constexpr int c = decltype(cc)::value; v[c] = cmul(v[c], twR[(c - 1) * RB + b]); });
-            static_for<0, RA>([&](auto cc) { constexpr int c = decltype(cc)::value; p[c * RB] = v[c]; });
+            if constexpr (C::SWZ) {
+                // swizzled store: not in place, but a row's RB items sit in one warp -> warp barrier between
+                // the row's loads and its stores is enough
+                __syncwarp();
+                float2* prow = buf + row * M;
+                static_for<0, RA>([&](auto cc) { constexpr int c = decltype(cc)::value; prow[c * RB + (b ^ (c & (RB - 1)))] = v[c]; });
+            } else {
+                static_for<0, RA>([&](auto cc) { constexpr int c = decltype(cc)::value; p[c * RB] = v[c]; });
+            }
         }
         __syncthreads();
         // rows, step RB: RB contiguous elements; row frequency k = k1 + RA*k2 ends at k1*RB + k2
 #pragma unroll 1
         for (int t = tid; t < H * RA; t += NT) {
             float2* p = buf + t * RB;
+            const int sw = C::SWZ ? ((t % RA) & (RB - 1)) : 0;      // chunk index k1 = t mod RA
             float2 v[RB];
-            static_for<0, RB>([&](auto jc) { constexpr int j = decltype(jc)::value; v[j] = p[j]; });
+            static_for<0, RB>([&](auto jc) { constexpr int j = decltype(jc)::value; v[j] = p[j ^ sw]; });
             dft_reg<RB>(v);
-            static_for<0, RB>([&](auto jc) { constexpr int j = decltype(jc)::value; p[j] = v[j]; });
+            static_for<0, RB>([&](auto jc) { constexpr int j = decltype(jc)::value; p[j ^ sw] = v[j]; });
         }
         __syncthreads();
         // columns, step CA: rows b + a*CB of each column (threads run along the row: stride 1)
@@ -167,8 +180,9 @@ __global__ void __launch_bounds__(C::NT, C::MINB)
         for (int t = tid; t < CA * KH; t += NT) {
             const int q1 = t / KH, k = t - q1 * KH;
             const int kk = (k == 0) ? 0 : M - k;
-            const int colA = (k % RA) * RB + k / RA;
-            const int colB = (kk % RA) * RB + kk / RA;
+            const int swA = C::SWZ ? ((k % RA) & (RB - 1)) : 0, swB = C::SWZ ? ((kk % RA) & (RB - 1)) : 0;
+            const int colA = (k % RA) * RB + ((k / RA) ^ swA);
+            const int colB = (kk % RA) * RB + ((kk / RA) ^ swB);
             const int q1B = (q1 == 0) ? 0 : CA - q1;
             const float2* pa = buf + q1 * CB * M + colA;
             const float2* pb = buf + q1B * CB * M + colB;
@@ -300,7 +314,13 @@ __global__ void __launch_bounds__(C::NT, C::MINB)
             static_for<0, RA>([&](auto ac) { constexpr int a = decltype(ac)::value; v[a] = p[a * RB]; });
             dft_reg<RA>(v);
             static_for<1, RA>([&](auto cc) { constexpr int c = decltype(cc)::value; v[c] = cmul(v[c], twR[(c - 1) * RB + b]); });
-            static_for<0, RA>([&](auto cc) { constexpr int c = decltype(cc)::value; p[c * RB] = v[c]; });
+            if constexpr (C::SWZ) {
+                __syncwarp();                                  // same swizzle as the forward kernel
+                float2* prow = buf + row * PI;
+                static_for<0, RA>([&](auto cc) { constexpr int c = decltype(cc)::value; prow[c * RB + (b ^ (c & (RB - 1)))] = v[c]; });
+            } else {
+                static_for<0, RA>([&](auto cc) { constexpr int c = decltype(cc)::value; p[c * RB] = v[c]; });
+            }
         }
         __syncthreads();
         // rows, step RB; results leave in natural order n = (M - f) mod M at dense pitch M.
@@ -316,7 +336,8 @@ __global__ void __launch_bounds__(C::NT, C::MINB)
                 float2 v[RB];
                 if (active) {
                     const float2* p = buf + row * PI + k1 * RB;
-                    static_for<0, RB>([&](auto jc) { constexpr int j = decltype(jc)::value; v[j] = p[j]; });
+                    const int sw = C::SWZ ? (k1 & (RB - 1)) : 0;
+                    static_for<0, RB>([&](auto jc) { constexpr int j = decltype(jc)::value; v[j] = p[j ^ sw]; });
                     dft_reg<RB>(v);
                 }
                 __syncthreads();
