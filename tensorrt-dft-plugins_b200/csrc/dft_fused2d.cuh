@@ -268,7 +268,7 @@ __global__ void __launch_bounds__(C::NT, C::MINB)
             constexpr int NTR = KPR * CA;
 #pragma unroll 1
             for (int k0 = 0; k0 < KH; k0 += KPR) {
-                const int kl = tid / CA, q1 = tid - kl * CA;
+                const int q1 = tid / KPR, kl = tid - q1 * KPR;       // lanes run along k: stride-1 shared-memory accesses
                 const int k = k0 + kl;
                 const bool active = (tid < NTR) && (k < KH);
                 float2 A[CB], B[CB];
