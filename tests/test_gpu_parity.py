@@ -208,3 +208,28 @@ def test_c2c_strided_axis_plan(capi, outer, n, inner, direction):
     plan.exec(zd, zd)                                   # in place
     torch.cuda.synchronize()
     assert torch.equal(zd, out)
+
+
+def test_exec_is_capturable_in_a_cuda_graph(capi):
+    """trt_dft_exec only launches kernels on the given stream, so a whole rfft2 -> irfft2 pair can be
+    captured once and replayed (what TensorRT does around enqueue)."""
+    torch.manual_seed(1)
+    x = torch.randn(6, 90, 180, device="cuda")
+    y = torch.empty(6, 90, 91, 2, device="cuda")
+    xr = torch.empty_like(x)
+    f = capi.Plan(capi.FORWARD, (90, 180), 6)
+    i = capi.Plan(capi.INVERSE, (90, 180), 6)
+    f.exec(x, y)
+    i.exec(y, xr)                              # warm-up outside capture (module load, attributes)
+    torch.cuda.synchronize()
+    g = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(g):
+        f.exec(x, y)
+        i.exec(y, xr)
+    x.copy_(torch.randn(6, 90, 180, device="cuda"))
+    xr.zero_()
+    g.replay()
+    torch.cuda.synchronize()
+    want = O.torch_rfftn(x.cpu(), 2, dtype=torch.float64).numpy()
+    assert O.rel_l2(y.cpu().numpy(), want) <= FWD_TOL
+    assert O.rel_l2(xr.cpu().numpy(), x.cpu().numpy()) <= RT_TOL
