@@ -74,6 +74,20 @@ __device__ __forceinline__ void mbar_wait(unsigned bar, unsigned parity)
         "r"(parity)
         : "memory");
 }
+__device__ __forceinline__ bool mbar_test(unsigned bar, unsigned parity)   // non-blocking
+{
+    unsigned ok;
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "mbarrier.test_wait.parity.shared::cta.b64 p, [%1], %2;\n"
+        "selp.u32 %0, 1, 0, p;\n"
+        "}\n"
+        : "=r"(ok)
+        : "r"(bar), "r"(parity)
+        : "memory");
+    return ok != 0;
+}
 __device__ __forceinline__ void mbar_arrive(unsigned bar)
 {
     asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");

@@ -1,0 +1,240 @@
+// dft_reg2d.cuh -- persistent fused rfft2 / irfft2 kernels that keep whole lines in registers.
+//
+// For images whose two FFT lengths are 2 * odd (M = W/2 = 2*Mh, H = 2*Hh; 90 = 2*45 for the 90 x 180
+// AFNO grid) a length-M line is split by Good-Thomas into a radix-2 step and a length-Mh FFT:
+//
+//     n = (Mh*n1 + 2*n2) mod M,   k = (Mh*k1 + (Mh+1)*k2) mod M,
+//     Z[k1,k2] = sum_n2 w_Mh^(n2 k2) * ( z[2*n2] + (-1)^k1 * z[(Mh + 2*n2) mod M] )
+//
+// Two threads share a line, one per parity k1 = p.  Each reads the whole line from shared memory
+// (128-bit loads), forms its Mh sums or differences and runs the length-Mh FFT entirely in registers
+// (a second Good-Thomas split RA x RB, no twiddles, every index a compile-time constant).  There is no
+// exchange step between butterfly passes at all: an image makes ONE trip through shared memory between
+// the row transform and the column transform (the transpose), where the pass-per-radix kernels of
+// dft_pipe2d.cuh make four.  The real-FFT split pairs Z[k] with Z[M-k], which have the same parity, so it
+// also stays inside the thread.
+//
+//   forward : TMA bulk load of the image -> rows (thread = (row, parity)): load, FFT, split, store
+//             transposed [k][row] -> columns (thread = (column k, parity)): load, FFT, coalesced 8-byte
+//             global stores.  The stage is handed back as soon as the column loads have landed.
+//   inverse : TMA bulk load of the spectrum -> columns (thread = (k, parity)): load (index-reversed, which
+//             turns the forward butterflies into the inverse transform), FFT, store transposed [k][row]
+//             -> rows: parities sit in the two halves of a warp; Hermitian merge of the thread's own
+//             parity, FFT, radix-2 step LAST (decimation in time) through one warp shuffle per value,
+//             store the dense real image -> one TMA bulk store.
+//
+// Bank behaviour: a thread's line is contiguous (pitch M*8 = 720 bytes, 45 16-byte units: odd), lanes
+// run across lines, so the 128-bit loads of a quarter warp hit 8 different 16-byte bank groups; the
+// transposed stores have lanes along the contiguous index.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "dft_butterflies.cuh"
+#include "dft_pipe2d.cuh"
+
+namespace dft {
+
+template <int H_, int W_, int RA_, int RB_, int CA_, int CB_, int NG_, int NS_>
+struct RegCfg {
+    static constexpr int H = H_, W = W_, M = W_ / 2, Mh = W_ / 4, Hh = H_ / 2, MO = W_ / 2 + 1;
+    static constexpr int RA = RA_, RB = RB_, CA = CA_, CB = CB_, NG = NG_, NS = NS_;
+    static_assert(W_ % 4 == 0 && Mh % 2 == 1 && H_ % 2 == 0 && Hh % 2 == 1, "both FFT lengths must be 2 * odd");
+    static_assert(RA_ * RB_ == Mh && CA_ * CB_ == Hh, "bad factorisation");
+    static constexpr int LINES = (H > MO ? H : MO);
+    static constexpr int WPP = (LINES + 31) / 32;          // warps per parity
+    static constexpr int GT = 2 * WPP * 32;                // threads per compute group
+    static constexpr int THREADS = NG * GT;
+    static constexpr int TILE_F = H * M * 8;               // real image == packed complex rows
+    static constexpr int TILE_I = H * MO * 8;              // one-sided spectrum
+    static_assert(TILE_F % 16 == 0 && TILE_I % 16 == 0, "bulk copies need 16-byte multiples");
+    static_assert((M / 2) % 2 == 1 && (H / 2) % 2 == 1, "line pitch must be odd in 16-byte units");
+    static constexpr int STAGE_F = (MO * H * 8 + 127) / 128 * 128;     // transposed [MO][H]
+    static constexpr int PI = (H % 2 == 0) ? H + 1 : H;                // inverse transpose pitch: odd
+    static constexpr int STAGE_I = (MO * PI * 8 + 127) / 128 * 128;
+    static constexpr int NPAIR = (Mh - 1) / 2;
+    static constexpr int NTAB_I = 2 * (NPAIR + 1);         // inverse merge twiddles, per parity
+    static constexpr int SMEM_F = NS * STAGE_F + 2 * NS * 8 + 16;
+    static constexpr int SMEM_I = NS * STAGE_I + NTAB_I * 8 + 2 * NS * 8 + 16;
+};
+
+#if defined(__CUDACC__)
+
+namespace reg2d {
+
+#ifdef DFT_REG2D_TRACE
+__device__ long long* g_trace;   // [image slot][8] clock64 stamps of CTA 0, debugging only
+#define DFT_TR(slot, i) do { if (blockIdx.x == 0 && (gt & 31) == 0 && warp % C::WPP == 0 && p == 0) reg2d::g_trace[(slot) * 8 + (i)] = clock64(); } while (0)
+#else
+#define DFT_TR(slot, i) do { } while (0)
+#endif
+
+// y[n2] = x[2*n2] + sg * x[(L2 + 2*n2) mod 2*L2] from a contiguous line of 2*L2 complex values (L2 odd)
+template <int L2>
+__device__ __forceinline__ void load_fold(float2 (&y)[L2], const float4* __restrict__ line, float sg)
+{
+    // 16-byte unit j holds x[2j], x[2j+1]; the odd partner of n2 sits in unit (n2 + (L2-1)/2) mod L2.
+    // Walking n2 in steps of (L2+1)/2 makes that partner the unit loaded one step earlier, so only two
+    // units are live at a time.
+    constexpr int S = (L2 + 1) / 2;
+    float4 prev = line[((L2 - 1) * S) % L2];
+    static_for<0, L2>([&](auto ic) {
+        constexpr int i = decltype(ic)::value;
+        constexpr int n2 = (i * S) % L2;
+        const float4 cur = line[n2];
+        y[n2] = float2{fmaf(sg, prev.z, cur.x), fmaf(sg, prev.w, cur.y)};
+        prev = cur;
+    });
+}
+
+template <int RA, int RB>
+__device__ __forceinline__ void line_fft(float2 (&y)[RA * RB])
+{
+    if constexpr (RB == 1) dft_reg<RA>(y);
+    else dft_pfa<RA, RB>(y);
+}
+
+// real-FFT split of the thread's parity P and transposed store: X[k] -> dst[k*H]
+template <class C, int P>
+__device__ __forceinline__ void split_store(const float2 (&z)[C::Mh], float2* __restrict__ dst)
+{
+    constexpr int M = C::M, Mh = C::Mh, H = C::H, W = C::W;
+    if constexpr (P == 0) {
+        dst[0] = float2{z[0].x + z[0].y, 0.f};
+        dst[M * H] = float2{z[0].x - z[0].y, 0.f};
+    } else {
+        dst[Mh * H] = float2{z[0].x, -z[0].y};
+    }
+    static_for<1, C::NPAIR + 1>([&](auto kc) {
+        constexpr int k2 = decltype(kc)::value;
+        constexpr int ka = (Mh * P + (Mh + 1) * k2) % M, kb = M - ka;
+        // t = (-i/2) * w_W^ka
+        constexpr float tx = float(-0.5 * cx_sin2pi(ka, W)), ty = float(-0.5 * cx_cos2pi(ka, W));
+        const float2 a = z[k2], b = z[Mh - k2];
+        const float sx = a.x + b.x, sy = a.y - b.y;      // a + conj b
+        const float dx = a.x - b.x, dy = a.y + b.y;      // a - conj b
+        const float ux = tx * dx - ty * dy, uy = tx * dy + ty * dx;
+        dst[ka * H] = float2{fmaf(0.5f, sx, ux), fmaf(0.5f, sy, uy)};
+        dst[kb * H] = float2{fmaf(0.5f, sx, -ux), fmaf(-0.5f, sy, uy)};
+    });
+}
+
+// column results of parity P: Y[k2] is output row (Hh*P + (Hh+1)*k2) mod H
+template <class C, int P>
+__device__ __forceinline__ void store_cols(const float2 (&y)[C::Hh], float2* __restrict__ dst)
+{
+    static_for<0, C::Hh>([&](auto kc) {
+        constexpr int k2 = decltype(kc)::value;
+        constexpr int q = (C::Hh * P + (C::Hh + 1) * k2) % C::H;
+        dst[q * C::MO] = y[k2];
+    });
+}
+
+}  // namespace reg2d
+
+// ---- forward ---------------------------------------------------------------------------------
+template <class C>
+__global__ void __launch_bounds__(C::THREADS, 1)
+    reg_rfft2_kernel(const float* __restrict__ in, float* __restrict__ out, long long nimg,
+                     const float2* __restrict__ /*tables*/, float /*scale*/)
+{
+    constexpr int H = C::H, M = C::M, MO = C::MO, GT = C::GT, NG = C::NG, NS = C::NS, WPP = C::WPP;
+    extern __shared__ __align__(128) unsigned char smem_raw[];
+    unsigned char* stages = smem_raw;
+    const unsigned full0 = pipe::s32(smem_raw + NS * C::STAGE_F);   // image has landed in the stage
+    const int tid = threadIdx.x;
+
+    if (tid == 0) {
+        for (int s = 0; s < NS; ++s) pipe::mbar_init(full0 + 8 * s, 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        pipe::fence_async();
+    }
+    __syncthreads();
+
+    // No I/O warp (12 warps keep 168 registers each).  Thread 0 fills the ring once; afterwards the first
+    // thread of each group stores the group's finished spectrum with one bulk copy and, one phase later,
+    // refills that stage with the image that uses it next (image it + NS).
+    auto issue_load = [&](long long it_load, int s) {
+        const long long tile = blockIdx.x + it_load * (long long)gridDim.x;
+        if (tile >= nimg) return;
+        const unsigned bar = full0 + 8 * s;
+        asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"((unsigned)C::TILE_F) : "memory");
+        asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+                         pipe::s32(stages + (size_t)s * C::STAGE_F)),
+                     "l"(reinterpret_cast<const unsigned char*>(in) + tile * (long long)C::TILE_F), "r"((unsigned)C::TILE_F), "r"(bar)
+                     : "memory");
+    };
+    if (tid == 0)
+        for (int s = 0; s < NS; ++s) issue_load(s, s);
+    const int g = tid / GT;
+    const int gt = tid - g * GT;
+    const int warp = gt >> 5;
+    const int p = warp / WPP;                           // parity handled by this warp
+    const int line = (warp - p * WPP) * 32 + (gt & 31); // row in the row phase, column in the column phase
+    const float sg = p ? -1.f : 1.f;
+    // lanes past the last line redo the last line (same values to the same addresses): no divergence, and
+    // no conditionally-live register arrays across the barriers
+    const int lrow = line < H ? line : H - 1, lcol = line < MO ? line : MO - 1;
+    const int bar_id = 1 + g;
+    long long pend_it = -1;                             // gt == 0: image whose bulk store is still reading its stage
+    auto refill = [&]() {
+        if (gt == 0 && pend_it >= 0) {
+            asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
+            issue_load(pend_it + NS, (int)(pend_it % NS));
+            pend_it = -1;
+        }
+    };
+
+    long long it = g;
+    for (long long tile = blockIdx.x + (long long)g * gridDim.x; tile < nimg; tile += (long long)NG * gridDim.x, it += NG) {
+        const int s = (int)(it % NS);
+        float2* buf = reinterpret_cast<float2*>(stages + (size_t)s * C::STAGE_F);
+        DFT_TR(it, 0);
+        pipe::mbar_wait(full0 + 8 * s, (unsigned)((it / NS) & 1));
+        DFT_TR(it, 1);
+
+        // rows: the whole packed row -> registers; the transposed result [k][row] overwrites the stage
+        {
+            float2 z[C::Mh];
+            reg2d::load_fold<C::Mh>(z, reinterpret_cast<const float4*>(buf) + lrow * (M / 2), sg);
+            refill();                                   // the previous image's store has long since drained
+            DFT_TR(it, 2);
+            pipe::group_sync(bar_id, GT);               // every row has been read
+            DFT_TR(it, 3);
+            reg2d::line_fft<C::RA, C::RB>(z);
+            if (p == 0) reg2d::split_store<C, 0>(z, buf + lrow);
+            else reg2d::split_store<C, 1>(z, buf + lrow);
+        }
+        DFT_TR(it, 4);
+        pipe::group_sync(bar_id, GT);
+        DFT_TR(it, 5);
+        // columns: column k is a contiguous line of the transposed tile; the spectrum [q][k] overwrites it
+        {
+            float2 y[C::Hh];
+            reg2d::load_fold<C::Hh>(y, reinterpret_cast<const float4*>(buf) + lcol * (H / 2), sg);
+            DFT_TR(it, 6);
+            reg2d::line_fft<C::CA, C::CB>(y);
+            pipe::group_sync(bar_id, GT);               // every column has been read
+            if (p == 0) reg2d::store_cols<C, 0>(y, buf + lcol);
+            else reg2d::store_cols<C, 1>(y, buf + lcol);
+            pipe::fence_async();
+            pipe::group_sync(bar_id, GT);
+            if (gt == 0) {
+                float* dst = out + tile * (long long)(H * MO * 2);
+                asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(dst), "r"(pipe::s32(buf)),
+                             "r"((unsigned)C::TILE_I)
+                             : "memory");
+                asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+                pend_it = it;
+            }
+            DFT_TR(it, 7);
+        }
+    }
+    refill();
+    // the last bulk store must have completed before the CTA (and its shared memory) goes away
+    if (gt == 0) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
+}
+
+#endif  // __CUDACC__
+
+}  // namespace dft

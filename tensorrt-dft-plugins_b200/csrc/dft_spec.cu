@@ -3,6 +3,7 @@
 
 #include "dft_fused2d.cuh"
 #include "dft_pipe2d.cuh"
+#include "dft_reg2d.cuh"
 #include "dft_spec.h"
 
 namespace dft {
@@ -25,10 +26,28 @@ SpecEntry make_pipe()
     return e;
 }
 
+// forward kernel with whole lines in registers (dft_reg2d.cuh); inverse from the pass-per-radix pipeline
+template <class CR, class CI>
+SpecEntry make_reg()
+{
+    static_assert(CR::H == CI::H && CR::W == CI::W, "");
+    SpecEntry e{CI::H, CI::W, CI::RA, CI::RB, CI::CA, CI::CB, CR::THREADS, CR::SMEM_F, CI::SMEM,
+                reg_rfft2_kernel<CR>, pipe_irfft2_kernel<CI>, true};
+    e.NT_inv = CI::THREADS;
+    return e;
+}
+
 }  // namespace
 
 const SpecEntry* find_spec(int H, int W)
 {
+    static const SpecEntry reg_table[] = {
+        //               H    W   RA RB CA CB groups stages
+        make_reg<RegCfg<90, 180, 9, 5, 9, 5, 2, 3>, PipeCfg<90, 180, 9, 10, 10, 9, 480, 2, 3>>(),
+    };
+    if (!getenv("TRT_DFT_NO_REG2D"))
+        for (const auto& e : reg_table)
+            if (e.H == H && e.W == W) return &e;
     static const SpecEntry table[] = {
         //                H    W   RA  RB  CA  CB  group threads, groups, stages
         make_pipe<PipeCfg<90, 180, 9, 10, 10, 9, 320, 2, 3>,      // forward: 2 x 320 threads
