@@ -130,6 +130,49 @@ __device__ __forceinline__ void store_cols(const float2 (&y)[C::Hh], float2* __r
     });
 }
 
+
+// inverse column fold: the forward butterflies run on the index-reversed line x'[n] = x[(L - n) mod L], which
+// makes them the inverse transform.  y[n2] = x'[2*n2] + sg * x'[(L2 + 2*n2) mod L], elements STRIDE apart.
+template <int L2, int STRIDE>
+__device__ __forceinline__ void load_fold_rev(float2 (&y)[L2], const float2* __restrict__ src, float sg)
+{
+    constexpr int L = 2 * L2;
+    static_for<0, L2>([&](auto nc) {
+        constexpr int n2 = decltype(nc)::value;
+        constexpr int ia = (L - 2 * n2) % L, ib = (2 * L - L2 - 2 * n2) % L;
+        const float2 a = src[ia * STRIDE], b = src[ib * STRIDE];
+        y[n2] = float2{fmaf(sg, b.x, a.x), fmaf(sg, b.y, a.y)};
+    });
+}
+
+// column results of parity P, transposed: value k2 is row r = (Hh*P + (Hh+1)*k2) mod H of this column
+template <class C, int P>
+__device__ __forceinline__ void store_rows_t(const float2 (&y)[C::Hh], float2* __restrict__ dst)
+{
+    static_for<0, C::Hh>([&](auto kc) {
+        constexpr int k2 = decltype(kc)::value;
+        constexpr int r = (C::Hh * P + (C::Hh + 1) * k2) % C::H;
+        dst[r] = y[k2];
+    });
+}
+
+// i * w_W^(-ka) for the Hermitian merge, ka = Mh*p + 2*k2 (compile-time table, scaled at kernel start)
+template <class C>
+struct MergeTable {
+    float x[2 * (C::NPAIR + 1)], y[2 * (C::NPAIR + 1)];
+    constexpr MergeTable() : x{}, y{}
+    {
+        for (int p = 0; p < 2; ++p)
+            for (int k2 = 0; k2 <= C::NPAIR; ++k2) {
+                const int ka = C::Mh * p + 2 * k2;
+                x[p * (C::NPAIR + 1) + k2] = float(-cx_sin2pi(ka, C::W));
+                y[p * (C::NPAIR + 1) + k2] = float(cx_cos2pi(ka, C::W));
+            }
+    }
+};
+template <class C>
+__device__ const MergeTable<C> g_merge_table{};
+
 }  // namespace reg2d
 
 // ---- forward ---------------------------------------------------------------------------------
@@ -228,6 +271,136 @@ __global__ void __launch_bounds__(C::THREADS, 1)
                 pend_it = it;
             }
             DFT_TR(it, 7);
+        }
+    }
+    refill();
+    // the last bulk store must have completed before the CTA (and its shared memory) goes away
+    if (gt == 0) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
+}
+
+// ---- inverse ---------------------------------------------------------------------------------
+template <class C>
+__global__ void __launch_bounds__(C::THREADS, 1)
+    reg_irfft2_kernel(const float* __restrict__ in, float* __restrict__ out, long long nimg,
+                      const float2* __restrict__ /*tables*/, float scale)
+{
+    constexpr int H = C::H, M = C::M, Mh = C::Mh, MO = C::MO, PI = C::PI, GT = C::GT, NG = C::NG, NS = C::NS, WPP = C::WPP;
+    constexpr int NTW = C::NPAIR + 1;
+    extern __shared__ __align__(128) unsigned char smem_raw[];
+    unsigned char* stages = smem_raw;
+    float2* twm = reinterpret_cast<float2*>(smem_raw + NS * C::STAGE_I);      // scale * i * w_W^(-ka), [parity][k2]
+    const unsigned full0 = pipe::s32(twm + C::NTAB_I);
+    const int tid = threadIdx.x;
+
+    for (int i = tid; i < C::NTAB_I; i += C::THREADS)
+        twm[i] = float2{scale * reg2d::g_merge_table<C>.x[i], scale * reg2d::g_merge_table<C>.y[i]};
+    if (tid == 0) {
+        for (int s = 0; s < NS; ++s) pipe::mbar_init(full0 + 8 * s, 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        pipe::fence_async();
+    }
+    __syncthreads();
+
+    auto issue_load = [&](long long it_load, int s) {
+        const long long tile = blockIdx.x + it_load * (long long)gridDim.x;
+        if (tile >= nimg) return;
+        const unsigned bar = full0 + 8 * s;
+        asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"((unsigned)C::TILE_I) : "memory");
+        asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+                         pipe::s32(stages + (size_t)s * C::STAGE_I)),
+                     "l"(reinterpret_cast<const unsigned char*>(in) + tile * (long long)C::TILE_I), "r"((unsigned)C::TILE_I), "r"(bar)
+                     : "memory");
+    };
+    if (tid == 0)
+        for (int s = 0; s < NS; ++s) issue_load(s, s);
+    const int g = tid / GT;
+    const int gt = tid - g * GT;
+    const int warp = gt >> 5, lane = gt & 31;
+    // column phase: parity per warp, lanes along the columns
+    const int pc = warp / WPP;
+    const int col = (warp - pc * WPP) * 32 + lane;
+    const int lcol = col < MO ? col : MO - 1;
+    const float sgc = pc ? -1.f : 1.f;
+    // row phase: the two parities of a row sit 16 lanes apart, so the last radix-2 step is one shuffle
+    const int pr = lane >> 4;
+    const int row = warp * 16 + (lane & 15);
+    const int lrow = row < H ? row : H - 1;
+    const float sgr = pr ? -1.f : 1.f;
+    const int bar_id = 1 + g;
+    long long pend_it = -1;                             // gt == 0: image whose bulk store is still reading its stage
+    auto refill = [&]() {
+        if (gt == 0 && pend_it >= 0) {
+            asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
+            issue_load(pend_it + NS, (int)(pend_it % NS));
+            pend_it = -1;
+        }
+    };
+
+    long long it = g;
+    for (long long tile = blockIdx.x + (long long)g * gridDim.x; tile < nimg; tile += (long long)NG * gridDim.x, it += NG) {
+        const int s = (int)(it % NS);
+        float2* buf = reinterpret_cast<float2*>(stages + (size_t)s * C::STAGE_I);
+        pipe::mbar_wait(full0 + 8 * s, (unsigned)((it / NS) & 1));
+
+        // columns: column k of the spectrum [q][k] -> registers; the transposed result [k][row], pitch PI,
+        // overwrites the stage
+        {
+            float2 y[C::Hh];
+            reg2d::load_fold_rev<C::Hh, MO>(y, buf + lcol, sgc);
+            refill();                                   // the previous image's store has long since drained
+            pipe::group_sync(bar_id, GT);               // every column has been read
+            reg2d::line_fft<C::CA, C::CB>(y);
+            if (pc == 0) reg2d::store_rows_t<C, 0>(y, buf + lcol * PI);
+            else reg2d::store_rows_t<C, 1>(y, buf + lcol * PI);
+        }
+        pipe::group_sync(bar_id, GT);
+        // rows: Hermitian merge of this thread's parity -> FFT -> radix-2 step across the half warps
+        {
+            float2 z[Mh];
+            const float2* pa = buf + lrow + pr * (Mh * PI);     // X[ka], ka = Mh*pr + 2*k2
+            const float2* pb = buf + lrow - pr * (Mh * PI);     // X[kb], kb = M - ka
+            const float2* tw = twm + pr * NTW;
+            {
+                // k2 = 0: Z[0] from the (real) DC and Nyquist bins, or Z[Mh] = 2 conj X[Mh]
+                const float2 u = pa[0], v = pb[M * PI];
+                z[0] = float2{scale * (u.x + v.x), scale * (pr ? -(u.y + v.y) : (u.x - v.x))};
+            }
+            static_for<1, NTW>([&](auto kc) {
+                constexpr int k2 = decltype(kc)::value;
+                const float2 a = pa[2 * k2 * PI], b = pb[(M - 2 * k2) * PI];
+                const float2 t = tw[k2];
+                const float sx = a.x + b.x, sy = a.y - b.y;      // a + conj b
+                const float dx = a.x - b.x, dy = a.y + b.y;      // a - conj b
+                const float ux = t.x * dx - t.y * dy, uy = t.x * dy + t.y * dx;
+                // Z[ka] = S + T goes to slot k2, Z[kb] = conj(S - T) to slot Mh - k2; the slots are filled
+                // index-reversed so that the forward butterflies compute the inverse transform
+                z[Mh - k2] = float2{fmaf(scale, sx, ux), fmaf(scale, sy, uy)};
+                z[k2] = float2{fmaf(scale, sx, -ux), fmaf(-scale, sy, uy)};
+            });
+            pipe::group_sync(bar_id, GT);               // every row has been read
+            reg2d::line_fft<C::RA, C::RB>(z);
+            // z[n2] now holds A_pr[n2]; x = A_0 + (-1)^n1 A_1 at n = (Mh*n1 + (Mh+1)*n2) mod M, n1 = pr
+            float2* op = buf + lrow * M + pr * Mh;
+            float2* om = buf + lrow * M - pr * Mh;
+            static_for<0, Mh>([&](auto nc) {
+                constexpr int n2 = decltype(nc)::value;
+                constexpr int c0 = ((Mh + 1) * n2) % M;
+                const float ox = __shfl_xor_sync(0xffffffffu, z[n2].x, 16);
+                const float oy = __shfl_xor_sync(0xffffffffu, z[n2].y, 16);
+                const float2 r = float2{fmaf(sgr, z[n2].x, ox), fmaf(sgr, z[n2].y, oy)};
+                if constexpr (c0 < Mh) op[c0] = r;
+                else om[c0] = r;
+            });
+            pipe::fence_async();
+            pipe::group_sync(bar_id, GT);
+            if (gt == 0) {
+                float* dst = out + tile * (long long)(H * C::W);
+                asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(dst), "r"(pipe::s32(buf)),
+                             "r"((unsigned)C::TILE_F)
+                             : "memory");
+                asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+                pend_it = it;
+            }
         }
     }
     refill();

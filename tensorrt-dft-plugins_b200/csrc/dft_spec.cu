@@ -26,14 +26,12 @@ SpecEntry make_pipe()
     return e;
 }
 
-// forward kernel with whole lines in registers (dft_reg2d.cuh); inverse from the pass-per-radix pipeline
-template <class CR, class CI>
+// both kernels keep whole lines in registers (dft_reg2d.cuh); they need no tables
+template <class CR>
 SpecEntry make_reg()
 {
-    static_assert(CR::H == CI::H && CR::W == CI::W, "");
-    SpecEntry e{CI::H, CI::W, CI::RA, CI::RB, CI::CA, CI::CB, CR::THREADS, CR::SMEM_F, CI::SMEM,
-                reg_rfft2_kernel<CR>, pipe_irfft2_kernel<CI>, true};
-    e.NT_inv = CI::THREADS;
+    SpecEntry e{CR::H, CR::W, CR::RA, CR::RB, CR::CA, CR::CB, CR::THREADS, CR::SMEM_F, CR::SMEM_I,
+                reg_rfft2_kernel<CR>, reg_irfft2_kernel<CR>, true};
     return e;
 }
 
@@ -43,7 +41,7 @@ const SpecEntry* find_spec(int H, int W)
 {
     static const SpecEntry reg_table[] = {
         //               H    W   RA RB CA CB groups stages
-        make_reg<RegCfg<90, 180, 9, 5, 9, 5, 2, 3>, PipeCfg<90, 180, 9, 10, 10, 9, 480, 2, 3>>(),
+        make_reg<RegCfg<90, 180, 9, 5, 9, 5, 2, 3>>(),                  // FourCastNet AFNO (BASELINE cfg3)
     };
     if (!getenv("TRT_DFT_NO_REG2D"))
         for (const auto& e : reg_table)
