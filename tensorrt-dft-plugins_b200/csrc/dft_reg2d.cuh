@@ -35,8 +35,16 @@
 
 namespace dft {
 
-template <int H_, int W_, int RA_, int RB_, int CA_, int CB_, int NG_, int NS_>
+template <int H_, int W_, int RA_, int RB_, int CA_, int CB_, int NG_, int NS_, bool IOW_ = false, bool PP_ = false>
 struct RegCfg {
+    // PP: the two groups take turns -- a group starts the first half of an image (load + first transform) only
+    // when the other group has moved on to its second half, so one group's shared-memory traffic always runs
+    // under the other's butterflies and finished images leave at even intervals.
+    static constexpr bool PP = PP_;
+    static_assert(!PP_ || NG_ == 2, "ping-pong is between two groups");
+    // IOW: one extra warp per compute group drives that group's bulk stores and the refills that follow
+    // them (the compute warps then never wait on a store), at the price of a 128-register budget.
+    static constexpr bool IOW = IOW_;
     static constexpr int H = H_, W = W_, M = W_ / 2, Mh = W_ / 4, Hh = H_ / 2, MO = W_ / 2 + 1;
     static constexpr int RA = RA_, RB = RB_, CA = CA_, CB = CB_, NG = NG_, NS = NS_;
     static_assert(W_ % 4 == 0 && Mh % 2 == 1 && H_ % 2 == 0 && Hh % 2 == 1, "both FFT lengths must be 2 * odd");
@@ -44,7 +52,8 @@ struct RegCfg {
     static constexpr int LINES = (H > MO ? H : MO);
     static constexpr int WPP = (LINES + 31) / 32;          // warps per parity
     static constexpr int GT = 2 * WPP * 32;                // threads per compute group
-    static constexpr int THREADS = NG * GT;
+    static constexpr int THREADS = NG * GT + (IOW ? NG * 32 : 0);
+    static constexpr int LCM = (NG * NS) / (NG % NS == 0 ? NS : (NS % NG == 0 ? NG : 1));   // NG, NS coprime or nested
     static constexpr int TILE_F = H * M * 8;               // real image == packed complex rows
     static constexpr int TILE_I = H * MO * 8;              // one-sided spectrum
     static_assert(TILE_F % 16 == 0 && TILE_I % 16 == 0, "bulk copies need 16-byte multiples");
@@ -54,8 +63,8 @@ struct RegCfg {
     static constexpr int STAGE_I = (MO * PI * 8 + 127) / 128 * 128;
     static constexpr int NPAIR = (Mh - 1) / 2;
     static constexpr int NTAB_I = 2 * (NPAIR + 1);         // inverse merge twiddles, per parity
-    static constexpr int SMEM_F = NS * STAGE_F + 2 * NS * 8 + 16;
-    static constexpr int SMEM_I = NS * STAGE_I + NTAB_I * 8 + 2 * NS * 8 + 16;
+    static constexpr int SMEM_F = NS * STAGE_F + (NS + NG * NS) * 8 + 16;
+    static constexpr int SMEM_I = NS * STAGE_I + NTAB_I * 8 + (NS + NG * NS) * 8 + 16;
 };
 
 #if defined(__CUDACC__)
@@ -173,6 +182,69 @@ struct MergeTable {
 template <class C>
 __device__ const MergeTable<C> g_merge_table{};
 
+// I/O warp of group g (one thread): for the group's images in order, wait until the result is staged, store
+// it, and refill the stage.  The store leaves in KP pieces (one bulk group each) and piece j of the next
+// image is requested as soon as pieces 0..j have been read out, so the stage's drain and its refill overlap
+// instead of adding up -- a stage in transit is what a group waits for.  done[g][s] is private to the
+// (group, stage) pair, whose uses are LCM images apart, so its phase parity is (it / LCM) & 1.
+template <class C, int STAGE, int LOAD_BYTES, int STORE_BYTES>
+__device__ __forceinline__ void io_loop(int g, const unsigned char* __restrict__ in, unsigned char* __restrict__ out, long long nimg,
+                                        unsigned char* stages, unsigned full0, unsigned done0)
+{
+    constexpr int NG = C::NG, NS = C::NS, KP = 4;
+    constexpr int SP = (STORE_BYTES / KP + 15) / 16 * 16;      // store piece (the last one is shorter)
+    constexpr int LP0 = (LOAD_BYTES / KP) / 16 * 16;
+    constexpr int LP = LP0 < SP ? LP0 : SP;                    // load piece  (the last one is longer)
+    static_assert(LP <= SP, "load piece j must lie inside store pieces 0..j");
+    auto load_piece = [&](long long tile, int s, int j) {
+        const unsigned off = (unsigned)(j * LP);
+        const unsigned bytes = (j == KP - 1) ? (unsigned)(LOAD_BYTES - (KP - 1) * LP) : (unsigned)LP;
+        asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+                         pipe::s32(stages + (size_t)s * STAGE) + off),
+                     "l"(in + tile * (long long)LOAD_BYTES + off), "r"(bytes), "r"(full0 + 8 * s)
+                     : "memory");
+    };
+    auto expect = [&](int s) {
+        asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(full0 + 8 * s), "r"((unsigned)LOAD_BYTES) : "memory");
+    };
+    if (g == 0)
+        for (int s = 0; s < NS; ++s) {
+            const long long tile = blockIdx.x + s * (long long)gridDim.x;
+            if (tile >= nimg) break;
+            expect(s);
+#pragma unroll
+            for (int j = 0; j < KP; ++j) load_piece(tile, s, j);
+        }
+    long long it = g;
+    for (long long tile = blockIdx.x + (long long)g * gridDim.x; tile < nimg; tile += (long long)NG * gridDim.x, it += NG) {
+        const int s = (int)(it % NS);
+        pipe::mbar_wait(done0 + 8 * (g * NS + s), (unsigned)((it / C::LCM) & 1));
+#pragma unroll
+        for (int j = 0; j < KP; ++j) {
+            const unsigned off = (unsigned)(j * SP);
+            const unsigned bytes = (j == KP - 1) ? (unsigned)(STORE_BYTES - (KP - 1) * SP) : (unsigned)SP;
+            asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(out + tile * (long long)STORE_BYTES + off),
+                         "r"(pipe::s32(stages + (size_t)s * STAGE) + off), "r"(bytes)
+                         : "memory");
+            asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+        }
+        const long long next = tile + (long long)NS * gridDim.x;   // the image that uses this stage next
+        if (next < nimg) {
+            expect(s);
+            asm volatile("cp.async.bulk.wait_group.read 3;" ::: "memory");
+            load_piece(next, s, 0);
+            asm volatile("cp.async.bulk.wait_group.read 2;" ::: "memory");
+            load_piece(next, s, 1);
+            asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory");
+            load_piece(next, s, 2);
+            asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
+            load_piece(next, s, 3);
+        }
+    }
+    // the last bulk stores must have completed before the CTA (and its shared memory) goes away
+    asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
+}
+
 }  // namespace reg2d
 
 // ---- forward ---------------------------------------------------------------------------------
@@ -185,15 +257,25 @@ __global__ void __launch_bounds__(C::THREADS, 1)
     extern __shared__ __align__(128) unsigned char smem_raw[];
     unsigned char* stages = smem_raw;
     const unsigned full0 = pipe::s32(smem_raw + NS * C::STAGE_F);   // image has landed in the stage
+    const unsigned done0 = full0 + 8 * NS;                          // [group][stage] spectrum staged (IOW only)
     const int tid = threadIdx.x;
 
     if (tid == 0) {
         for (int s = 0; s < NS; ++s) pipe::mbar_init(full0 + 8 * s, 1);
+        for (int s = 0; s < NG * NS; ++s) pipe::mbar_init(done0 + 8 * s, GT / 32);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
         pipe::fence_async();
     }
     __syncthreads();
 
+    if constexpr (C::IOW) {
+        if (tid >= NG * GT) {
+            if ((tid & 31) == 0)
+                reg2d::io_loop<C, C::STAGE_F, C::TILE_F, C::TILE_I>((tid - NG * GT) >> 5, reinterpret_cast<const unsigned char*>(in),
+                                                                    reinterpret_cast<unsigned char*>(out), nimg, stages, full0, done0);
+            return;
+        }
+    }
     // No I/O warp (12 warps keep 168 registers each).  Thread 0 fills the ring once; afterwards the first
     // thread of each group stores the group's finished spectrum with one bulk copy and, one phase later,
     // refills that stage with the image that uses it next (image it + NS).
@@ -207,7 +289,7 @@ __global__ void __launch_bounds__(C::THREADS, 1)
                      "l"(reinterpret_cast<const unsigned char*>(in) + tile * (long long)C::TILE_F), "r"((unsigned)C::TILE_F), "r"(bar)
                      : "memory");
     };
-    if (tid == 0)
+    if (!C::IOW && tid == 0)
         for (int s = 0; s < NS; ++s) issue_load(s, s);
     const int g = tid / GT;
     const int gt = tid - g * GT;
@@ -221,18 +303,20 @@ __global__ void __launch_bounds__(C::THREADS, 1)
     const int bar_id = 1 + g;
     long long pend_it = -1;                             // gt == 0: image whose bulk store is still reading its stage
     auto refill = [&]() {
-        if (gt == 0 && pend_it >= 0) {
+        if (!C::IOW && gt == 0 && pend_it >= 0) {
             asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
             issue_load(pend_it + NS, (int)(pend_it % NS));
             pend_it = -1;
         }
     };
 
+    if (C::PP && g == 1) asm volatile("bar.arrive %0, %1;" ::"r"(3), "r"(2 * GT) : "memory");   // group 0 goes first
     long long it = g;
     for (long long tile = blockIdx.x + (long long)g * gridDim.x; tile < nimg; tile += (long long)NG * gridDim.x, it += NG) {
         const int s = (int)(it % NS);
         float2* buf = reinterpret_cast<float2*>(stages + (size_t)s * C::STAGE_F);
         DFT_TR(it, 0);
+        if (C::PP) pipe::group_sync(3 + g, 2 * GT);     // my turn
         pipe::mbar_wait(full0 + 8 * s, (unsigned)((it / NS) & 1));
         DFT_TR(it, 1);
 
@@ -249,6 +333,7 @@ __global__ void __launch_bounds__(C::THREADS, 1)
             else reg2d::split_store<C, 1>(z, buf + lrow);
         }
         DFT_TR(it, 4);
+        if (C::PP) asm volatile("bar.arrive %0, %1;" ::"r"(4 - g), "r"(2 * GT) : "memory");   // the other group's turn
         pipe::group_sync(bar_id, GT);
         DFT_TR(it, 5);
         // columns: column k is a contiguous line of the transposed tile; the spectrum [q][k] overwrites it
@@ -261,6 +346,12 @@ __global__ void __launch_bounds__(C::THREADS, 1)
             if (p == 0) reg2d::store_cols<C, 0>(y, buf + lcol);
             else reg2d::store_cols<C, 1>(y, buf + lcol);
             pipe::fence_async();
+            if constexpr (C::IOW) {
+                __syncwarp();
+                if ((gt & 31) == 0) pipe::mbar_arrive(done0 + 8 * (g * NS + s));
+                DFT_TR(it, 7);
+                continue;
+            }
             pipe::group_sync(bar_id, GT);
             if (gt == 0) {
                 float* dst = out + tile * (long long)(H * MO * 2);
@@ -275,7 +366,7 @@ __global__ void __launch_bounds__(C::THREADS, 1)
     }
     refill();
     // the last bulk store must have completed before the CTA (and its shared memory) goes away
-    if (gt == 0) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
+    if (!C::IOW && gt == 0) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
 }
 
 // ---- inverse ---------------------------------------------------------------------------------
@@ -290,17 +381,27 @@ __global__ void __launch_bounds__(C::THREADS, 1)
     unsigned char* stages = smem_raw;
     float2* twm = reinterpret_cast<float2*>(smem_raw + NS * C::STAGE_I);      // scale * i * w_W^(-ka), [parity][k2]
     const unsigned full0 = pipe::s32(twm + C::NTAB_I);
+    const unsigned done0 = full0 + 8 * NS;                          // [group][stage] image staged (IOW only)
     const int tid = threadIdx.x;
 
     for (int i = tid; i < C::NTAB_I; i += C::THREADS)
         twm[i] = float2{scale * reg2d::g_merge_table<C>.x[i], scale * reg2d::g_merge_table<C>.y[i]};
     if (tid == 0) {
         for (int s = 0; s < NS; ++s) pipe::mbar_init(full0 + 8 * s, 1);
+        for (int s = 0; s < NG * NS; ++s) pipe::mbar_init(done0 + 8 * s, GT / 32);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
         pipe::fence_async();
     }
     __syncthreads();
 
+    if constexpr (C::IOW) {
+        if (tid >= NG * GT) {
+            if ((tid & 31) == 0)
+                reg2d::io_loop<C, C::STAGE_I, C::TILE_I, C::TILE_F>((tid - NG * GT) >> 5, reinterpret_cast<const unsigned char*>(in),
+                                                                    reinterpret_cast<unsigned char*>(out), nimg, stages, full0, done0);
+            return;
+        }
+    }
     auto issue_load = [&](long long it_load, int s) {
         const long long tile = blockIdx.x + it_load * (long long)gridDim.x;
         if (tile >= nimg) return;
@@ -311,7 +412,7 @@ __global__ void __launch_bounds__(C::THREADS, 1)
                      "l"(reinterpret_cast<const unsigned char*>(in) + tile * (long long)C::TILE_I), "r"((unsigned)C::TILE_I), "r"(bar)
                      : "memory");
     };
-    if (tid == 0)
+    if (!C::IOW && tid == 0)
         for (int s = 0; s < NS; ++s) issue_load(s, s);
     const int g = tid / GT;
     const int gt = tid - g * GT;
@@ -329,17 +430,19 @@ __global__ void __launch_bounds__(C::THREADS, 1)
     const int bar_id = 1 + g;
     long long pend_it = -1;                             // gt == 0: image whose bulk store is still reading its stage
     auto refill = [&]() {
-        if (gt == 0 && pend_it >= 0) {
+        if (!C::IOW && gt == 0 && pend_it >= 0) {
             asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
             issue_load(pend_it + NS, (int)(pend_it % NS));
             pend_it = -1;
         }
     };
 
+    if (C::PP && g == 1) asm volatile("bar.arrive %0, %1;" ::"r"(3), "r"(2 * GT) : "memory");   // group 0 goes first
     long long it = g;
     for (long long tile = blockIdx.x + (long long)g * gridDim.x; tile < nimg; tile += (long long)NG * gridDim.x, it += NG) {
         const int s = (int)(it % NS);
         float2* buf = reinterpret_cast<float2*>(stages + (size_t)s * C::STAGE_I);
+        if (C::PP) pipe::group_sync(3 + g, 2 * GT);     // my turn
         pipe::mbar_wait(full0 + 8 * s, (unsigned)((it / NS) & 1));
 
         // columns: column k of the spectrum [q][k] -> registers; the transposed result [k][row], pitch PI,
@@ -353,6 +456,7 @@ __global__ void __launch_bounds__(C::THREADS, 1)
             if (pc == 0) reg2d::store_rows_t<C, 0>(y, buf + lcol * PI);
             else reg2d::store_rows_t<C, 1>(y, buf + lcol * PI);
         }
+        if (C::PP) asm volatile("bar.arrive %0, %1;" ::"r"(4 - g), "r"(2 * GT) : "memory");   // the other group's turn
         pipe::group_sync(bar_id, GT);
         // rows: Hermitian merge of this thread's parity -> FFT -> radix-2 step across the half warps
         {
@@ -392,6 +496,11 @@ __global__ void __launch_bounds__(C::THREADS, 1)
                 else om[c0] = r;
             });
             pipe::fence_async();
+            if constexpr (C::IOW) {
+                __syncwarp();
+                if ((gt & 31) == 0) pipe::mbar_arrive(done0 + 8 * (g * NS + s));
+                continue;
+            }
             pipe::group_sync(bar_id, GT);
             if (gt == 0) {
                 float* dst = out + tile * (long long)(H * C::W);
@@ -404,6 +513,165 @@ __global__ void __launch_bounds__(C::THREADS, 1)
         }
     }
     refill();
+    // the last bulk store must have completed before the CTA (and its shared memory) goes away
+    if (!C::IOW && gt == 0) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
+}
+
+#endif  // __CUDACC__
+
+
+// =================================================================================================
+// Landing-ring variant.  With whole stages an image keeps 64 KB of shared memory busy from the moment its
+// load is issued until its store has drained, and only three fit: the pipeline is bound by stage time.
+// Here every compute group owns ONE full-size work buffer (transpose tile, then output staging), and the
+// input arrives through a small ring of row chunks that are handed back as soon as the lines are in
+// registers.  A producer warp keeps the ring full (more than one image ahead of the groups).
+template <int H_, int W_, int RA_, int RB_, int CA_, int CB_, int NG_, int RPC_, int NC_>
+struct RingCfg : RegCfg<H_, W_, RA_, RB_, CA_, CB_, NG_, 1> {
+    using B = RegCfg<H_, W_, RA_, RB_, CA_, CB_, NG_, 1>;
+    static constexpr int RPC = RPC_, NC = NC_;             // rows per chunk, chunks in the ring
+    static_assert(H_ % RPC_ == 0, "chunks must tile the image");
+    static constexpr int CPI = H_ / RPC_;                  // chunks per image
+    static constexpr int CH_F = RPC * B::M * 8;            // bytes of a chunk of real rows
+    static constexpr int CH_I = RPC * B::MO * 8;           // bytes of a chunk of spectrum rows
+    static_assert(CH_F % 16 == 0 && CH_I % 16 == 0, "bulk copies need 16-byte multiples");
+    static constexpr int THREADS = NG_ * B::GT + 32;       // + the producer warp
+    static constexpr int SMEM_F = NG_ * B::STAGE_F + NC * CH_F + 2 * NC * 8 + 16;
+    static constexpr int SMEM_I = NG_ * B::STAGE_I + NC * ((CH_I + 127) / 128 * 128) + B::NTAB_I * 8 + 2 * NC * 8 + 16;
+};
+
+#if defined(__CUDACC__)
+
+namespace reg2d {
+
+// producer thread: chunk c of this CTA's image sequence goes to ring slot c % NC
+template <class C, int CH_BYTES, int CH_PITCH>
+__device__ __forceinline__ void ring_producer(const unsigned char* __restrict__ in, long long nimg, unsigned char* ring, unsigned full0,
+                                              unsigned empty0)
+{
+    constexpr int NC = C::NC, CPI = C::CPI;
+    long long c = 0;
+    for (long long tile = blockIdx.x; tile < nimg; tile += gridDim.x) {
+#pragma unroll 1
+        for (int j = 0; j < CPI; ++j, ++c) {
+            const int slot = (int)(c % NC);
+            if (c >= NC) pipe::mbar_wait(empty0 + 8 * slot, (unsigned)(((c / NC) - 1) & 1));
+            pipe::fence_async();
+            const unsigned bar = full0 + 8 * slot;
+            asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"((unsigned)CH_BYTES) : "memory");
+            asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+                             pipe::s32(ring + (size_t)slot * CH_PITCH)),
+                         "l"(in + (tile * CPI + j) * (long long)CH_BYTES), "r"((unsigned)CH_BYTES), "r"(bar)
+                         : "memory");
+        }
+    }
+}
+
+}  // namespace reg2d
+
+template <class C>
+__global__ void __launch_bounds__(C::THREADS, 1)
+    ring_rfft2_kernel(const float* __restrict__ in, float* __restrict__ out, long long nimg,
+                      const float2* __restrict__ /*tables*/, float /*scale*/)
+{
+    constexpr int H = C::H, M = C::M, MO = C::MO, GT = C::GT, NG = C::NG, WPP = C::WPP, NC = C::NC, CPI = C::CPI, RPC = C::RPC;
+    extern __shared__ __align__(128) unsigned char smem_raw[];
+    unsigned char* gbufs = smem_raw;                                   // one work buffer per group
+    unsigned char* ring = smem_raw + NG * C::STAGE_F;                  // landing ring of row chunks
+    const unsigned full0 = pipe::s32(ring + NC * C::CH_F);
+    const unsigned empty0 = full0 + 8 * NC;
+    // images whose chunks have been seen to land.  A parity wait is only meaningful one phase ahead, and the
+    // previous use of a slot may belong to the other group's image it - 1: wait for that image to be seen first.
+    volatile int* seen = reinterpret_cast<volatile int*>(ring + NC * C::CH_F + 2 * NC * 8);
+    const int tid = threadIdx.x;
+
+    if (tid == 0) {
+        *seen = 0;
+        for (int s = 0; s < NC; ++s) {
+            pipe::mbar_init(full0 + 8 * s, 1);
+            pipe::mbar_init(empty0 + 8 * s, GT / 32);   // every warp of the consuming group
+        }
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        pipe::fence_async();
+    }
+    __syncthreads();
+
+    if (tid >= NG * GT) {
+        if (tid == NG * GT)
+            reg2d::ring_producer<C, C::CH_F, C::CH_F>(reinterpret_cast<const unsigned char*>(in), nimg, ring, full0, empty0);
+        return;
+    }
+    const int g = tid / GT;
+    const int gt = tid - g * GT;
+    const int warp = gt >> 5;
+    const int p = warp / WPP;                           // parity handled by this warp
+    const int line = (warp - p * WPP) * 32 + (gt & 31); // row in the row phase, column in the column phase
+    const float sg = p ? -1.f : 1.f;
+    // lanes past the last line redo the last line (same values to the same addresses): no divergence, and
+    // no conditionally-live register arrays across the barriers
+    const int lrow = line < H ? line : H - 1, lcol = line < MO ? line : MO - 1;
+    const int jrow = lrow / RPC, rrow = lrow - jrow * RPC;              // my row's chunk and place in it
+    const int bar_id = 1 + g;
+    float2* buf = reinterpret_cast<float2*>(gbufs + (size_t)g * C::STAGE_F);
+    bool pending = false;                               // gt == 0: a bulk store may still be reading buf
+
+    long long it = g;
+    for (long long tile = blockIdx.x + (long long)g * gridDim.x; tile < nimg; tile += (long long)NG * gridDim.x, it += NG) {
+        const long long c0 = it * CPI;
+        DFT_TR(it, 0);
+        while (*seen < (int)it) { }
+#pragma unroll
+        for (int j = 0; j < CPI; ++j) pipe::mbar_wait(full0 + 8 * (int)((c0 + j) % NC), (unsigned)(((c0 + j) / NC) & 1));
+        if (gt == 0) *seen = (int)it + 1;
+        DFT_TR(it, 1);
+
+        // rows: the whole packed row -> registers, chunks handed back at once
+        float2 z[C::Mh];
+        {
+            const int slot = (int)((c0 + jrow) % NC);
+            reg2d::load_fold<C::Mh>(z, reinterpret_cast<const float4*>(ring + (size_t)slot * C::CH_F) + rrow * (M / 2), sg);
+        }
+        pipe::fence_async();
+        __syncwarp();
+        if ((gt & 31) == 0) {
+#pragma unroll
+            for (int j = 0; j < CPI; ++j) pipe::mbar_arrive(empty0 + 8 * (int)((c0 + j) % NC));
+        }
+        DFT_TR(it, 2);
+        reg2d::line_fft<C::RA, C::RB>(z);
+        if (gt == 0 && pending) {
+            asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
+            pending = false;
+        }
+        pipe::group_sync(bar_id, GT);                   // the previous spectrum has left the work buffer
+        DFT_TR(it, 3);
+        if (p == 0) reg2d::split_store<C, 0>(z, buf + lrow);
+        else reg2d::split_store<C, 1>(z, buf + lrow);
+        DFT_TR(it, 4);
+        pipe::group_sync(bar_id, GT);
+        DFT_TR(it, 5);
+        // columns: column k is a contiguous line of the transposed tile; the spectrum [q][k] overwrites it
+        {
+            float2 y[C::Hh];
+            reg2d::load_fold<C::Hh>(y, reinterpret_cast<const float4*>(buf) + lcol * (H / 2), sg);
+            DFT_TR(it, 6);
+            reg2d::line_fft<C::CA, C::CB>(y);
+            pipe::group_sync(bar_id, GT);               // every column has been read
+            if (p == 0) reg2d::store_cols<C, 0>(y, buf + lcol);
+            else reg2d::store_cols<C, 1>(y, buf + lcol);
+            pipe::fence_async();
+            pipe::group_sync(bar_id, GT);
+            if (gt == 0) {
+                float* dst = out + tile * (long long)(H * MO * 2);
+                asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(dst), "r"(pipe::s32(buf)),
+                             "r"((unsigned)C::TILE_I)
+                             : "memory");
+                asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+                pending = true;
+            }
+            DFT_TR(it, 7);
+        }
+    }
     // the last bulk store must have completed before the CTA (and its shared memory) goes away
     if (gt == 0) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
 }

@@ -27,11 +27,13 @@ SpecEntry make_pipe()
 }
 
 // both kernels keep whole lines in registers (dft_reg2d.cuh); they need no tables
-template <class CR>
+template <class CF, class CI>
 SpecEntry make_reg()
 {
-    SpecEntry e{CR::H, CR::W, CR::RA, CR::RB, CR::CA, CR::CB, CR::THREADS, CR::SMEM_F, CR::SMEM_I,
-                reg_rfft2_kernel<CR>, reg_irfft2_kernel<CR>, true};
+    static_assert(CF::H == CI::H && CF::W == CI::W, "");
+    SpecEntry e{CF::H, CF::W, CF::RA, CF::RB, CF::CA, CF::CB, CF::THREADS, CF::SMEM_F, CI::SMEM_I,
+                reg_rfft2_kernel<CF>, reg_irfft2_kernel<CI>, true};
+    e.NT_inv = CI::THREADS;
     return e;
 }
 
@@ -40,8 +42,9 @@ SpecEntry make_reg()
 const SpecEntry* find_spec(int H, int W)
 {
     static const SpecEntry reg_table[] = {
-        //               H    W   RA RB CA CB groups stages
-        make_reg<RegCfg<90, 180, 9, 5, 9, 5, 2, 3>>(),                  // FourCastNet AFNO (BASELINE cfg3)
+        //               H    W   RA RB CA CB groups stages I/O-warps ping-pong
+        make_reg<RegCfg<90, 180, 9, 5, 9, 5, 2, 3, false, false>,
+                 RegCfg<90, 180, 9, 5, 9, 5, 2, 3, true, true>>(),       // FourCastNet AFNO (BASELINE cfg3)
     };
     if (!getenv("TRT_DFT_NO_REG2D"))
         for (const auto& e : reg_table)
