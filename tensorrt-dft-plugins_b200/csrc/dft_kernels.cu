@@ -369,8 +369,8 @@ int trt_dft_plan_describe(trt_dft_plan_t plan, char* buf, size_t len)
                 snprintf(t, sizeof t, "%s[%d]pipelined grid=%dx%d stages=%d groups=%d", i ? "," : " ", (int)i, rl.gp_grid,
                          kPipeThreads, rl.gp_ns, rl.gp_ng);
             else
-                snprintf(t, sizeof t, "%s[%d]grid=%dx%d", i ? "," : " ", (int)i, rl.spec ? rl.spec_grid : rl.grid,
-                         rl.spec ? rl.spec_nt : rl.kp.threads);
+                snprintf(t, sizeof t, rl.spec ? "%s[%d]grid=%dx%d smem=%d" : "%s[%d]grid=%dx%d", i ? "," : " ", (int)i,
+                         rl.spec ? rl.spec_grid : rl.grid, rl.spec ? rl.spec_nt : rl.kp.threads, rl.spec_smem);
             d += t;
         }
         strncpy(buf, d.c_str(), len - 1);

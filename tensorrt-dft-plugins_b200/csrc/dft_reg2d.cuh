@@ -35,13 +35,12 @@
 
 namespace dft {
 
-template <int H_, int W_, int RA_, int RB_, int CA_, int CB_, int NG_, int NS_, bool IOW_ = false, bool PP_ = false>
+template <int H_, int W_, int RA_, int RB_, int CA_, int CB_, int NG_, int NS_, bool IOW_ = false, int PP_ = 0>
 struct RegCfg {
     // PP: the two groups take turns -- a group starts the first half of an image (load + first transform) only
-    // when the other group has moved on to its second half, so one group's shared-memory traffic always runs
-    // under the other's butterflies and finished images leave at even intervals.
-    static constexpr bool PP = PP_;
-    static_assert(!PP_ || NG_ == 2, "ping-pong is between two groups");
+    // when the other group has moved on to its second half, so finished images leave at even intervals.
+    static constexpr int PP = PP_;
+    static_assert(PP_ == 0 || NG_ == 2, "ping-pong is between two groups");
     // IOW: one extra warp per compute group drives that group's bulk stores and the refills that follow
     // them (the compute warps then never wait on a store), at the price of a 128-register budget.
     static constexpr bool IOW = IOW_;
@@ -63,7 +62,8 @@ struct RegCfg {
     static constexpr int STAGE_I = (MO * PI * 8 + 127) / 128 * 128;
     static constexpr int NPAIR = (Mh - 1) / 2;
     static constexpr int NTAB_I = 2 * (NPAIR + 1);         // inverse merge twiddles, per parity
-    static constexpr int SMEM_F = NS * STAGE_F + (NS + NG * NS) * 8 + 16;
+    static constexpr int NTAB_F = 2 * (NPAIR + 1);         // forward split twiddles, per parity
+    static constexpr int SMEM_F = NS * STAGE_F + NTAB_F * 8 + (NS + NG * NS) * 8 + 16;
     static constexpr int SMEM_I = NS * STAGE_I + NTAB_I * 8 + (NS + NG * NS) * 8 + 16;
 };
 
@@ -103,42 +103,71 @@ __device__ __forceinline__ void line_fft(float2 (&y)[RA * RB])
     else dft_pfa<RA, RB>(y);
 }
 
-// real-FFT split of the thread's parity P and transposed store: X[k] -> dst[k*H]
-template <class C, int P>
-__device__ __forceinline__ void split_store(const float2 (&z)[C::Mh], float2* __restrict__ dst)
+// real-FFT split of the thread's parity p and transposed store: X[k] -> dst[k*H].  One code path for both
+// parities (the kernel is instruction-cache hungry): the twiddles come from a table, and k = ka(p, k2) is a
+// compile-time offset from one of two base pointers, dst +- p*Mh*H.
+template <class C>
+__device__ __forceinline__ void split_store(const float2 (&z)[C::Mh], float2* __restrict__ dst, int p, const float2* __restrict__ tw)
 {
-    constexpr int M = C::M, Mh = C::Mh, H = C::H, W = C::W;
-    if constexpr (P == 0) {
+    constexpr int M = C::M, Mh = C::Mh, H = C::H;
+    if (p == 0) {
         dst[0] = float2{z[0].x + z[0].y, 0.f};
         dst[M * H] = float2{z[0].x - z[0].y, 0.f};
     } else {
         dst[Mh * H] = float2{z[0].x, -z[0].y};
     }
+    float2* dp = dst + p * (Mh * H);
+    float2* dm = dst - p * (Mh * H);
     static_for<1, C::NPAIR + 1>([&](auto kc) {
         constexpr int k2 = decltype(kc)::value;
-        constexpr int ka = (Mh * P + (Mh + 1) * k2) % M, kb = M - ka;
-        // t = (-i/2) * w_W^ka
-        constexpr float tx = float(-0.5 * cx_sin2pi(ka, W)), ty = float(-0.5 * cx_cos2pi(ka, W));
+        constexpr int c0 = ((Mh + 1) * k2) % M;          // ka = c0 + Mh*p (c0 < Mh) or c0 - Mh*p; kb = M - ka
+        const float2 t = tw[k2];                         // (-i/2) * w_W^ka
         const float2 a = z[k2], b = z[Mh - k2];
         const float sx = a.x + b.x, sy = a.y - b.y;      // a + conj b
         const float dx = a.x - b.x, dy = a.y + b.y;      // a - conj b
-        const float ux = tx * dx - ty * dy, uy = tx * dy + ty * dx;
-        dst[ka * H] = float2{fmaf(0.5f, sx, ux), fmaf(0.5f, sy, uy)};
-        dst[kb * H] = float2{fmaf(0.5f, sx, -ux), fmaf(-0.5f, sy, uy)};
+        const float ux = t.x * dx - t.y * dy, uy = t.x * dy + t.y * dx;
+        const float2 xa = float2{fmaf(0.5f, sx, ux), fmaf(0.5f, sy, uy)};
+        const float2 xb = float2{fmaf(0.5f, sx, -ux), fmaf(-0.5f, sy, uy)};
+        if constexpr (c0 < Mh) {
+            dp[c0 * H] = xa;
+            dm[(M - c0) * H] = xb;
+        } else {
+            dm[c0 * H] = xa;
+            dp[(M - c0) * H] = xb;
+        }
     });
 }
 
-// column results of parity P: Y[k2] is output row (Hh*P + (Hh+1)*k2) mod H
-template <class C, int P>
-__device__ __forceinline__ void store_cols(const float2 (&y)[C::Hh], float2* __restrict__ dst)
+// (-i/2) * w_W^ka for the forward split, ka = (Mh*p + (Mh+1)*k2) mod M
+template <class C>
+struct SplitTable {
+    float x[2 * (C::NPAIR + 1)], y[2 * (C::NPAIR + 1)];
+    constexpr SplitTable() : x{}, y{}
+    {
+        for (int p = 0; p < 2; ++p)
+            for (int k2 = 0; k2 <= C::NPAIR; ++k2) {
+                const int ka = (C::Mh * p + (C::Mh + 1) * k2) % C::M;
+                x[p * (C::NPAIR + 1) + k2] = float(-0.5 * cx_sin2pi(ka, C::W));
+                y[p * (C::NPAIR + 1) + k2] = float(-0.5 * cx_cos2pi(ka, C::W));
+            }
+    }
+};
+template <class C>
+__device__ const SplitTable<C> g_split_table{};
+
+// column results of parity p: Y[k2] is output row (Hh*p + (Hh+1)*k2) mod H
+template <class C>
+__device__ __forceinline__ void store_cols(const float2 (&y)[C::Hh], float2* __restrict__ dst, int p)
 {
+    float2* dp = dst + p * (C::Hh * C::MO);
+    float2* dm = dst - p * (C::Hh * C::MO);
     static_for<0, C::Hh>([&](auto kc) {
         constexpr int k2 = decltype(kc)::value;
-        constexpr int q = (C::Hh * P + (C::Hh + 1) * k2) % C::H;
-        dst[q * C::MO] = y[k2];
+        constexpr int c0 = ((C::Hh + 1) * k2) % C::H;
+        if constexpr (c0 < C::Hh) dp[c0 * C::MO] = y[k2];
+        else dm[c0 * C::MO] = y[k2];
     });
 }
-
 
 // inverse column fold: the forward butterflies run on the index-reversed line x'[n] = x[(L - n) mod L], which
 // makes them the inverse transform.  y[n2] = x'[2*n2] + sg * x'[(L2 + 2*n2) mod L], elements STRIDE apart.
@@ -256,10 +285,12 @@ __global__ void __launch_bounds__(C::THREADS, 1)
     constexpr int H = C::H, M = C::M, MO = C::MO, GT = C::GT, NG = C::NG, NS = C::NS, WPP = C::WPP;
     extern __shared__ __align__(128) unsigned char smem_raw[];
     unsigned char* stages = smem_raw;
-    const unsigned full0 = pipe::s32(smem_raw + NS * C::STAGE_F);   // image has landed in the stage
+    float2* tws = reinterpret_cast<float2*>(smem_raw + NS * C::STAGE_F);      // (-i/2) * w_W^ka, [parity][k2]
+    const unsigned full0 = pipe::s32(tws + C::NTAB_F);              // image has landed in the stage
     const unsigned done0 = full0 + 8 * NS;                          // [group][stage] spectrum staged (IOW only)
     const int tid = threadIdx.x;
 
+    for (int i = tid; i < C::NTAB_F; i += C::THREADS) tws[i] = float2{reg2d::g_split_table<C>.x[i], reg2d::g_split_table<C>.y[i]};
     if (tid == 0) {
         for (int s = 0; s < NS; ++s) pipe::mbar_init(full0 + 8 * s, 1);
         for (int s = 0; s < NG * NS; ++s) pipe::mbar_init(done0 + 8 * s, GT / 32);
@@ -310,13 +341,13 @@ __global__ void __launch_bounds__(C::THREADS, 1)
         }
     };
 
-    if (C::PP && g == 1) asm volatile("bar.arrive %0, %1;" ::"r"(3), "r"(2 * GT) : "memory");   // group 0 goes first
+    if (C::PP != 0 && g == 1) asm volatile("bar.arrive %0, %1;" ::"r"(3), "r"(2 * GT) : "memory");   // group 0 goes first
     long long it = g;
     for (long long tile = blockIdx.x + (long long)g * gridDim.x; tile < nimg; tile += (long long)NG * gridDim.x, it += NG) {
         const int s = (int)(it % NS);
         float2* buf = reinterpret_cast<float2*>(stages + (size_t)s * C::STAGE_F);
         DFT_TR(it, 0);
-        if (C::PP) pipe::group_sync(3 + g, 2 * GT);     // my turn
+        if (C::PP == 1) pipe::group_sync(3 + g, 2 * GT);     // my turn
         pipe::mbar_wait(full0 + 8 * s, (unsigned)((it / NS) & 1));
         DFT_TR(it, 1);
 
@@ -329,11 +360,10 @@ __global__ void __launch_bounds__(C::THREADS, 1)
             pipe::group_sync(bar_id, GT);               // every row has been read
             DFT_TR(it, 3);
             reg2d::line_fft<C::RA, C::RB>(z);
-            if (p == 0) reg2d::split_store<C, 0>(z, buf + lrow);
-            else reg2d::split_store<C, 1>(z, buf + lrow);
+            reg2d::split_store<C>(z, buf + lrow, p, tws + p * (C::NPAIR + 1));
         }
         DFT_TR(it, 4);
-        if (C::PP) asm volatile("bar.arrive %0, %1;" ::"r"(4 - g), "r"(2 * GT) : "memory");   // the other group's turn
+        if (C::PP == 1) asm volatile("bar.arrive %0, %1;" ::"r"(4 - g), "r"(2 * GT) : "memory");   // the other group's turn
         pipe::group_sync(bar_id, GT);
         DFT_TR(it, 5);
         // columns: column k is a contiguous line of the transposed tile; the spectrum [q][k] overwrites it
@@ -343,8 +373,7 @@ __global__ void __launch_bounds__(C::THREADS, 1)
             DFT_TR(it, 6);
             reg2d::line_fft<C::CA, C::CB>(y);
             pipe::group_sync(bar_id, GT);               // every column has been read
-            if (p == 0) reg2d::store_cols<C, 0>(y, buf + lcol);
-            else reg2d::store_cols<C, 1>(y, buf + lcol);
+            reg2d::store_cols<C>(y, buf + lcol, p);
             pipe::fence_async();
             if constexpr (C::IOW) {
                 __syncwarp();
@@ -437,12 +466,12 @@ __global__ void __launch_bounds__(C::THREADS, 1)
         }
     };
 
-    if (C::PP && g == 1) asm volatile("bar.arrive %0, %1;" ::"r"(3), "r"(2 * GT) : "memory");   // group 0 goes first
+    if (C::PP != 0 && g == 1) asm volatile("bar.arrive %0, %1;" ::"r"(3), "r"(2 * GT) : "memory");   // group 0 goes first
     long long it = g;
     for (long long tile = blockIdx.x + (long long)g * gridDim.x; tile < nimg; tile += (long long)NG * gridDim.x, it += NG) {
         const int s = (int)(it % NS);
         float2* buf = reinterpret_cast<float2*>(stages + (size_t)s * C::STAGE_I);
-        if (C::PP) pipe::group_sync(3 + g, 2 * GT);     // my turn
+        if (C::PP == 1) pipe::group_sync(3 + g, 2 * GT);     // my turn
         pipe::mbar_wait(full0 + 8 * s, (unsigned)((it / NS) & 1));
 
         // columns: column k of the spectrum [q][k] -> registers; the transposed result [k][row], pitch PI,
@@ -456,7 +485,7 @@ __global__ void __launch_bounds__(C::THREADS, 1)
             if (pc == 0) reg2d::store_rows_t<C, 0>(y, buf + lcol * PI);
             else reg2d::store_rows_t<C, 1>(y, buf + lcol * PI);
         }
-        if (C::PP) asm volatile("bar.arrive %0, %1;" ::"r"(4 - g), "r"(2 * GT) : "memory");   // the other group's turn
+        if (C::PP == 1) asm volatile("bar.arrive %0, %1;" ::"r"(4 - g), "r"(2 * GT) : "memory");   // the other group's turn
         pipe::group_sync(bar_id, GT);
         // rows: Hermitian merge of this thread's parity -> FFT -> radix-2 step across the half warps
         {
@@ -519,163 +548,5 @@ __global__ void __launch_bounds__(C::THREADS, 1)
 
 #endif  // __CUDACC__
 
-
-// =================================================================================================
-// Landing-ring variant.  With whole stages an image keeps 64 KB of shared memory busy from the moment its
-// load is issued until its store has drained, and only three fit: the pipeline is bound by stage time.
-// Here every compute group owns ONE full-size work buffer (transpose tile, then output staging), and the
-// input arrives through a small ring of row chunks that are handed back as soon as the lines are in
-// registers.  A producer warp keeps the ring full (more than one image ahead of the groups).
-template <int H_, int W_, int RA_, int RB_, int CA_, int CB_, int NG_, int RPC_, int NC_>
-struct RingCfg : RegCfg<H_, W_, RA_, RB_, CA_, CB_, NG_, 1> {
-    using B = RegCfg<H_, W_, RA_, RB_, CA_, CB_, NG_, 1>;
-    static constexpr int RPC = RPC_, NC = NC_;             // rows per chunk, chunks in the ring
-    static_assert(H_ % RPC_ == 0, "chunks must tile the image");
-    static constexpr int CPI = H_ / RPC_;                  // chunks per image
-    static constexpr int CH_F = RPC * B::M * 8;            // bytes of a chunk of real rows
-    static constexpr int CH_I = RPC * B::MO * 8;           // bytes of a chunk of spectrum rows
-    static_assert(CH_F % 16 == 0 && CH_I % 16 == 0, "bulk copies need 16-byte multiples");
-    static constexpr int THREADS = NG_ * B::GT + 32;       // + the producer warp
-    static constexpr int SMEM_F = NG_ * B::STAGE_F + NC * CH_F + 2 * NC * 8 + 16;
-    static constexpr int SMEM_I = NG_ * B::STAGE_I + NC * ((CH_I + 127) / 128 * 128) + B::NTAB_I * 8 + 2 * NC * 8 + 16;
-};
-
-#if defined(__CUDACC__)
-
-namespace reg2d {
-
-// producer thread: chunk c of this CTA's image sequence goes to ring slot c % NC
-template <class C, int CH_BYTES, int CH_PITCH>
-__device__ __forceinline__ void ring_producer(const unsigned char* __restrict__ in, long long nimg, unsigned char* ring, unsigned full0,
-                                              unsigned empty0)
-{
-    constexpr int NC = C::NC, CPI = C::CPI;
-    long long c = 0;
-    for (long long tile = blockIdx.x; tile < nimg; tile += gridDim.x) {
-#pragma unroll 1
-        for (int j = 0; j < CPI; ++j, ++c) {
-            const int slot = (int)(c % NC);
-            if (c >= NC) pipe::mbar_wait(empty0 + 8 * slot, (unsigned)(((c / NC) - 1) & 1));
-            pipe::fence_async();
-            const unsigned bar = full0 + 8 * slot;
-            asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"((unsigned)CH_BYTES) : "memory");
-            asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
-                             pipe::s32(ring + (size_t)slot * CH_PITCH)),
-                         "l"(in + (tile * CPI + j) * (long long)CH_BYTES), "r"((unsigned)CH_BYTES), "r"(bar)
-                         : "memory");
-        }
-    }
-}
-
-}  // namespace reg2d
-
-template <class C>
-__global__ void __launch_bounds__(C::THREADS, 1)
-    ring_rfft2_kernel(const float* __restrict__ in, float* __restrict__ out, long long nimg,
-                      const float2* __restrict__ /*tables*/, float /*scale*/)
-{
-    constexpr int H = C::H, M = C::M, MO = C::MO, GT = C::GT, NG = C::NG, WPP = C::WPP, NC = C::NC, CPI = C::CPI, RPC = C::RPC;
-    extern __shared__ __align__(128) unsigned char smem_raw[];
-    unsigned char* gbufs = smem_raw;                                   // one work buffer per group
-    unsigned char* ring = smem_raw + NG * C::STAGE_F;                  // landing ring of row chunks
-    const unsigned full0 = pipe::s32(ring + NC * C::CH_F);
-    const unsigned empty0 = full0 + 8 * NC;
-    // images whose chunks have been seen to land.  A parity wait is only meaningful one phase ahead, and the
-    // previous use of a slot may belong to the other group's image it - 1: wait for that image to be seen first.
-    volatile int* seen = reinterpret_cast<volatile int*>(ring + NC * C::CH_F + 2 * NC * 8);
-    const int tid = threadIdx.x;
-
-    if (tid == 0) {
-        *seen = 0;
-        for (int s = 0; s < NC; ++s) {
-            pipe::mbar_init(full0 + 8 * s, 1);
-            pipe::mbar_init(empty0 + 8 * s, GT / 32);   // every warp of the consuming group
-        }
-        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
-        pipe::fence_async();
-    }
-    __syncthreads();
-
-    if (tid >= NG * GT) {
-        if (tid == NG * GT)
-            reg2d::ring_producer<C, C::CH_F, C::CH_F>(reinterpret_cast<const unsigned char*>(in), nimg, ring, full0, empty0);
-        return;
-    }
-    const int g = tid / GT;
-    const int gt = tid - g * GT;
-    const int warp = gt >> 5;
-    const int p = warp / WPP;                           // parity handled by this warp
-    const int line = (warp - p * WPP) * 32 + (gt & 31); // row in the row phase, column in the column phase
-    const float sg = p ? -1.f : 1.f;
-    // lanes past the last line redo the last line (same values to the same addresses): no divergence, and
-    // no conditionally-live register arrays across the barriers
-    const int lrow = line < H ? line : H - 1, lcol = line < MO ? line : MO - 1;
-    const int jrow = lrow / RPC, rrow = lrow - jrow * RPC;              // my row's chunk and place in it
-    const int bar_id = 1 + g;
-    float2* buf = reinterpret_cast<float2*>(gbufs + (size_t)g * C::STAGE_F);
-    bool pending = false;                               // gt == 0: a bulk store may still be reading buf
-
-    long long it = g;
-    for (long long tile = blockIdx.x + (long long)g * gridDim.x; tile < nimg; tile += (long long)NG * gridDim.x, it += NG) {
-        const long long c0 = it * CPI;
-        DFT_TR(it, 0);
-        while (*seen < (int)it) { }
-#pragma unroll
-        for (int j = 0; j < CPI; ++j) pipe::mbar_wait(full0 + 8 * (int)((c0 + j) % NC), (unsigned)(((c0 + j) / NC) & 1));
-        if (gt == 0) *seen = (int)it + 1;
-        DFT_TR(it, 1);
-
-        // rows: the whole packed row -> registers, chunks handed back at once
-        float2 z[C::Mh];
-        {
-            const int slot = (int)((c0 + jrow) % NC);
-            reg2d::load_fold<C::Mh>(z, reinterpret_cast<const float4*>(ring + (size_t)slot * C::CH_F) + rrow * (M / 2), sg);
-        }
-        pipe::fence_async();
-        __syncwarp();
-        if ((gt & 31) == 0) {
-#pragma unroll
-            for (int j = 0; j < CPI; ++j) pipe::mbar_arrive(empty0 + 8 * (int)((c0 + j) % NC));
-        }
-        DFT_TR(it, 2);
-        reg2d::line_fft<C::RA, C::RB>(z);
-        if (gt == 0 && pending) {
-            asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
-            pending = false;
-        }
-        pipe::group_sync(bar_id, GT);                   // the previous spectrum has left the work buffer
-        DFT_TR(it, 3);
-        if (p == 0) reg2d::split_store<C, 0>(z, buf + lrow);
-        else reg2d::split_store<C, 1>(z, buf + lrow);
-        DFT_TR(it, 4);
-        pipe::group_sync(bar_id, GT);
-        DFT_TR(it, 5);
-        // columns: column k is a contiguous line of the transposed tile; the spectrum [q][k] overwrites it
-        {
-            float2 y[C::Hh];
-            reg2d::load_fold<C::Hh>(y, reinterpret_cast<const float4*>(buf) + lcol * (H / 2), sg);
-            DFT_TR(it, 6);
-            reg2d::line_fft<C::CA, C::CB>(y);
-            pipe::group_sync(bar_id, GT);               // every column has been read
-            if (p == 0) reg2d::store_cols<C, 0>(y, buf + lcol);
-            else reg2d::store_cols<C, 1>(y, buf + lcol);
-            pipe::fence_async();
-            pipe::group_sync(bar_id, GT);
-            if (gt == 0) {
-                float* dst = out + tile * (long long)(H * MO * 2);
-                asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(dst), "r"(pipe::s32(buf)),
-                             "r"((unsigned)C::TILE_I)
-                             : "memory");
-                asm volatile("cp.async.bulk.commit_group;" ::: "memory");
-                pending = true;
-            }
-            DFT_TR(it, 7);
-        }
-    }
-    // the last bulk store must have completed before the CTA (and its shared memory) goes away
-    if (gt == 0) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
-}
-
-#endif  // __CUDACC__
 
 }  // namespace dft

@@ -27,14 +27,11 @@ SpecEntry make_pipe()
 }
 
 // both kernels keep whole lines in registers (dft_reg2d.cuh); they need no tables
-template <class CF, class CI>
+template <class C>
 SpecEntry make_reg()
 {
-    static_assert(CF::H == CI::H && CF::W == CI::W, "");
-    SpecEntry e{CF::H, CF::W, CF::RA, CF::RB, CF::CA, CF::CB, CF::THREADS, CF::SMEM_F, CI::SMEM_I,
-                reg_rfft2_kernel<CF>, reg_irfft2_kernel<CI>, true};
-    e.NT_inv = CI::THREADS;
-    return e;
+    return SpecEntry{C::H, C::W, C::RA, C::RB, C::CA, C::CB, C::THREADS, C::SMEM_F, C::SMEM_I,
+                     reg_rfft2_kernel<C>, reg_irfft2_kernel<C>, true};
 }
 
 }  // namespace
@@ -43,8 +40,7 @@ const SpecEntry* find_spec(int H, int W)
 {
     static const SpecEntry reg_table[] = {
         //               H    W   RA RB CA CB groups stages I/O-warps ping-pong
-        make_reg<RegCfg<90, 180, 9, 5, 9, 5, 2, 3, false, false>,
-                 RegCfg<90, 180, 9, 5, 9, 5, 2, 3, true, true>>(),       // FourCastNet AFNO (BASELINE cfg3)
+        make_reg<RegCfg<90, 180, 9, 5, 9, 5, 2, 3, true, 1>>(),         // FourCastNet AFNO (BASELINE cfg3)
     };
     if (!getenv("TRT_DFT_NO_REG2D"))
         for (const auto& e : reg_table)

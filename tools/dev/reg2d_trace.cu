@@ -11,16 +11,10 @@ using namespace dft;
 #ifndef CFG_IOW
 #define CFG_IOW false
 #endif
-#ifdef CFG_RING
-using C = RingCfg<90, 180, 9, 5, 9, 5, CFG_NG, CFG_RPC, CFG_NC>;
-#define reg_rfft2_kernel ring_rfft2_kernel
-#define reg_irfft2_kernel ring_rfft2_kernel
-#else
 #ifndef CFG_PP
-#define CFG_PP false
+#define CFG_PP 0
 #endif
 using C = RegCfg<90, 180, 9, 5, 9, 5, CFG_NG, 3, CFG_IOW, CFG_PP>;
-#endif
 int main()
 {
     const long long nimg = 6144;
