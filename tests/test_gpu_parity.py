@@ -233,3 +233,24 @@ def test_exec_is_capturable_in_a_cuda_graph(capi):
     want = O.torch_rfftn(x.cpu(), 2, dtype=torch.float64).numpy()
     assert O.rel_l2(y.cpu().numpy(), want) <= FWD_TOL
     assert O.rel_l2(xr.cpu().numpy(), x.cpu().numpy()) <= RT_TOL
+
+
+@pytest.mark.parametrize("nimg", [1, 2, 3, 5, 147, 148, 149, 296, 297, 445, 593])
+def test_headline_kernels_at_every_batch_remainder(capi, nimg):
+    """The persistent 90x180 kernels deal images round-robin to 148 CTAs x 2 ping-ponging groups x 3 stages:
+    cover batches below, at and just above each of those periods (odd counts leave one group an image short),
+    every image checked against fp64 torch.fft, and the inverse against the exact inverse of what it was fed."""
+    g = torch.Generator().manual_seed(nimg)
+    x = torch.randn(nimg, 90, 180, generator=g)
+    want = O.torch_rfftn(x, 2, dtype=torch.float64)
+    y = capi.rfftn(x.cuda(), 2)
+    torch.cuda.synchronize()
+    err = (y.cpu().double() - want).flatten(1).norm(dim=1) / want.flatten(1).norm(dim=1)
+    assert float(err.max()) <= FWD_TOL, f"worst image {int(err.argmax())}"
+    # a spectrum that is NOT Hermitian-consistent in its DC / Nyquist columns, as a network would produce
+    s = torch.randn(nimg, 90, 91, 2, generator=g)
+    want_x = O.torch_irfftn(s, 2, dtype=torch.float64)
+    xr = capi.irfftn(s.cuda(), 2)
+    torch.cuda.synchronize()
+    err = (xr.cpu().double() - want_x).flatten(1).norm(dim=1) / want_x.flatten(1).norm(dim=1)
+    assert float(err.max()) <= FWD_TOL, f"worst image {int(err.argmax())}"
