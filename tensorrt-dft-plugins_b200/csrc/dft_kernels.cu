@@ -284,7 +284,8 @@ static int realize_plan(trt_dft_plan_s* pl, trt_dft_plan_t* plan_out)
                 if (pg) pf = pg;
             }
             const int stage = (r.kp.smem_bytes - dft::kBarrierBytes + 127) / 128 * 128;
-            int ns = std::min(4, (dft::kSmemMax - 256) / std::max(stage, 1));
+            const int ns_cap = getenv("TRT_DFT_GP_NS") ? atoi(getenv("TRT_DFT_GP_NS")) : 4;   // tuning override
+            int ns = std::min(ns_cap, (dft::kSmemMax - 256) / std::max(stage, 1));
             // tables (twiddles, permutation) ride in shared memory when they fit beside >= 2 stages
             const bool m2d = r.kp.mode == dft::MODE_F2D || r.kp.mode == dft::MODE_I2D;
             const int tab_bytes = r.kp.mode == dft::MODE_C2C_COLS
@@ -292,7 +293,7 @@ static int realize_plan(trt_dft_plan_s* pl, trt_dft_plan_t* plan_out)
                                       : r.kp.row.n * 12 + (r.kp.M + 1) * 8 + 64 + (m2d ? r.kp.col.n * 12 + 64 : 0);
             int tables = 0;
             if (ns >= 2) {
-                int ns_t = std::min(4, (dft::kSmemMax - 256 - tab_bytes) / std::max(stage, 1));
+                int ns_t = std::min(ns_cap, (dft::kSmemMax - 256 - tab_bytes) / std::max(stage, 1));
                 if (ns_t >= 2 && (ns_t >= 3 || ns < 3)) {
                     ns = ns_t;
                     tables = 1;
@@ -305,6 +306,7 @@ static int realize_plan(trt_dft_plan_s* pl, trt_dft_plan_t* plan_out)
                     r.gpipe = pf;
                     r.gp_ns = ns;
                     r.gp_ng = ns >= 3 ? 2 : 1;
+                    if (getenv("TRT_DFT_GP_NG")) r.gp_ng = std::max(1, std::min(atoi(getenv("TRT_DFT_GP_NG")), ns - 1));
                     r.gp_stage = stage;
                     r.gp_smem = smem;
                     r.gp_grid = (int)std::min<long long>(r.kp.ntiles, num_sms);

@@ -47,12 +47,14 @@ DFT_HD int phys(int p, int pad) { return pad ? p + (p >> 4) + (p >> 8) : p; }
 // linear in the element index (see dft_planner.h).
 template <int R, bool COLS>
 DFT_HD void fft_step(float2* buf, int nlines, int pitch, int N, int L, const float2* tw, int ncols,
-                     int img_stride, unsigned mmag, unsigned bmag, unsigned lmag, int pad, int tid, int nthr)
+                     int img_stride, unsigned mmag, unsigned bmag, unsigned lmag, int pad, int ord, int tid, int nthr)
 {
     const int m = L / R;         // element stride inside the butterfly
     const int bpl = N / R;       // butterflies per line
     const int tws = N / L;       // twiddle table stride: w_L^x = w_N^(x*tws)
-    const int total = nlines * bpl;
+    // rows: work items per line, padded to whole half-warps when the planner asked for it (LineFFT::ord)
+    const int bplp = (!COLS && (ord & 2)) ? ((bpl + 15) & ~15) : bpl;
+    const int total = nlines * bplp;
     const int es_rows = pad ? m + (m >> 4) + (m >> 8) : m;
     for (int t = tid; t < total; t += nthr) {
         int line, u;
@@ -61,12 +63,17 @@ DFT_HD void fft_step(float2* buf, int nlines, int pitch, int N, int L, const flo
             line = t - u * nlines;
         } else {
             line = fdiv(t, bmag);
-            u = t - line * bpl;
+            u = t - line * bplp;
+            if (u >= bpl) continue;
         }
         int blk, b;
         if (m == 1) {
             blk = u;
             b = 0;
+        } else if (!COLS && (ord & 1)) {     // consecutive items walk the blocks (mmag = magic of N/L)
+            const int nblk = N / L;
+            b = fdiv(u, mmag);
+            blk = u - b * nblk;
         } else {
             blk = fdiv(u, mmag);
             b = u - blk * m;
@@ -111,12 +118,12 @@ DFT_HD void fft_step(float2* buf, int nlines, int pitch, int N, int L, const flo
 template <bool COLS>
 DFT_HD void fft_step_dispatch(int radix, float2* buf, int nlines, int pitch, int N, int L,
                               const float2* tw, int ncols, int img_stride, unsigned mmag, unsigned bmag,
-                              unsigned lmag, int pad, int tid, int nthr)
+                              unsigned lmag, int pad, int ord, int tid, int nthr)
 {
     switch (radix) {
 #define DFT_CASE(R)                                                                     \
     case R:                                                                             \
-        fft_step<R, COLS>(buf, nlines, pitch, N, L, tw, ncols, img_stride, mmag, bmag, lmag, pad, tid, nthr); \
+        fft_step<R, COLS>(buf, nlines, pitch, N, L, tw, ncols, img_stride, mmag, bmag, lmag, pad, ord, tid, nthr); \
         break;
         DFT_CASE(2)
         DFT_CASE(3)

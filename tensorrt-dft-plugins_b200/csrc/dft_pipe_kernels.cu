@@ -171,7 +171,38 @@ struct GeoLine {
             const unsigned m = (unsigned)(L / r[i]), bpl = (unsigned)(N_ / r[i]);
             f.mmag[i] = m <= 1 ? 0u : (unsigned)(((1ull << 32) + m - 1) / m);
             f.bmag[i] = bpl <= 1 ? 0u : (unsigned)(((1ull << 32) + bpl - 1) / bpl);
+            f.ord[i] = 0;
             L /= r[i];
+        }
+    }
+    // the planner's bank-conflict-free work-item orders for unskewed rows of pitch PITCH, folded at compile time
+    template <int PITCH>
+    struct Orders {
+        dft::LineFFT f;
+        constexpr Orders() : f{}
+        {
+            constexpr int r[4] = {R0, R1, R2, R3};
+            f.n = N_;
+            f.nsteps = nsteps;
+            for (int i = 0; i < nsteps; ++i) f.radix[i] = r[i];
+            dft::set_row_orders(f, PITCH);
+        }
+    };
+    template <int PITCH>
+    __device__ static void apply_orders(dft::LineFFT& f)
+    {
+        constexpr Orders<PITCH> o{};
+        static_for_orders<PITCH, 0>(f);
+    }
+    template <int PITCH, int I>
+    __device__ static void static_for_orders(dft::LineFFT& f)
+    {
+        if constexpr (I < nsteps) {
+            constexpr Orders<PITCH> o{};
+            f.ord[I] = o.f.ord[I];
+            f.mmag[I] = o.f.mmag[I];
+            f.bmag[I] = o.f.bmag[I];
+            static_for_orders<PITCH, I + 1>(f);
         }
     }
 };
@@ -198,6 +229,10 @@ __global__ void __launch_bounds__(kPipeThreads, 1)
             p.pad = (Geo::pow2 && Geo::N >= 32) ? 1 : 0;
             constexpr int PP = Geo::N + (Geo::N >> 4) + (Geo::N >> 8) + 1;
             p.P = (Geo::pow2 && Geo::N >= 32) ? PP : (MODE == dft::MODE_I1D ? Geo::N + 1 : Geo::N);
+            if constexpr (!(Geo::pow2 && Geo::N >= 32)) {
+                // same decision as the planner's (dft_planner.h: add_rows)
+                Geo::template apply_orders<(MODE == dft::MODE_I1D ? Geo::N + 1 : Geo::N)>(p.row);
+            }
         }
     }
     if (tables_in_smem) {

@@ -214,6 +214,7 @@ struct Planner {
         make_line_fft(M, true, &k.row);
         k.pad = (even && is_pow2(M) && M >= 32) ? 1 : 0;
         k.P = k.pad ? phys_index(M, true) + 1 : ((inverse && even) ? M + 1 : M);
+        if (even && !k.pad && !getenv("TRT_DFT_NO_ROW_ORDER")) set_row_orders(k.row, k.P);   // bank-conflict-free work-item order
         k.nunits = nrows;
         k.G = pick_group(nrows, (long long)k.P * 8, 48 * 1024);
         k.ntiles = (nrows + k.G - 1) / k.G;

@@ -24,11 +24,11 @@ DFT_HD void run_line_fft(const LineFFT& f, bool cols, float2* buf, int nlines, i
         if (s >= f.nsteps) break;
         const int r = f.radix[s];
         if (cols)
-            fft_step_dispatch<true>(r, buf, nlines, pitch, f.n, L, tw, ncols, img_stride, f.mmag[s], f.bmag[s], lmag, 0,
+            fft_step_dispatch<true>(r, buf, nlines, pitch, f.n, L, tw, ncols, img_stride, f.mmag[s], f.bmag[s], lmag, 0, 0,
                                     ctx.tid, ctx.nthr);
         else
             fft_step_dispatch<false>(r, buf, nlines, pitch, f.n, L, tw, ncols, img_stride, f.mmag[s], f.bmag[s], lmag, pad,
-                                     ctx.tid, ctx.nthr);
+                                     f.ord[s], ctx.tid, ctx.nthr);
         ctx.sync();
         L /= r;
     }

@@ -25,7 +25,82 @@ struct LineFFT {
     // floor(x / d) == umulhi(x, magic) exactly whenever x * d < 2^32 (tile-local indices are < 2^16).
     unsigned mmag[kMaxSteps];
     unsigned bmag[kMaxSteps];
+    // Row steps only (see row_step_order): bit 0 = consecutive work items walk the blocks (stride L) instead
+    // of the offsets inside a block (mmag is then the magic of n/L); bit 1 = work items per line are padded to
+    // a multiple of 16 so that no half-warp straddles two lines (bmag is then the magic of the padded count).
+    unsigned char ord[kMaxSteps];
 };
+
+#if defined(__CUDACC__)
+#define DFT_CXF __host__ __device__ constexpr
+#else
+#define DFT_CXF constexpr
+#endif
+
+// Shared-memory cost (wavefronts for 16 lines) of one radix-r row step on blocks of length L of n-point lines
+// stored `pitch` complex elements apart, for work-item order `ord`: 16 consecutive work items form one
+// 8-byte-access wavefront and every extra hit on one of the 16 bank pairs costs another.
+DFT_CXF int row_step_cost(int n, int pitch, int L, int r, int ord)
+{
+    const int m = L / r, nblk = n / L, bpl = n / r;
+    const int bplp = (ord & 2) ? (bpl + 15) / 16 * 16 : bpl;
+    const int total = 16 * bplp;
+    int cost = 0;
+    for (int w0 = 0; w0 < total; w0 += 16) {
+        int cnt[16] = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0};
+        int mx = 0;
+        for (int l = 0; l < 16 && w0 + l < total; ++l) {
+            const int t = w0 + l, line = t / bplp, u = t - line * bplp;
+            if (u >= bpl) continue;
+            int blk = u, b = 0;
+            if (m > 1) {
+                if (ord & 1) {
+                    b = u / nblk;
+                    blk = u - b * nblk;
+                } else {
+                    blk = u / m;
+                    b = u - blk * m;
+                }
+            }
+            const int bank = (line * pitch + blk * L + b) & 15;
+            ++cnt[bank];
+            if (cnt[bank] > mx) mx = cnt[bank];
+        }
+        cost += mx;
+    }
+    return cost;
+}
+
+// cheapest work-item order of a row step (0 keeps the plain order when nothing is gained)
+DFT_CXF int row_step_order(int n, int pitch, int L, int r)
+{
+    int best = 0, bc = row_step_cost(n, pitch, L, r, 0);
+    for (int o = 1; o < 4; ++o) {
+        if ((o & 1) && (L / r <= 1 || n / L <= 1)) continue;
+        const int c = row_step_cost(n, pitch, L, r, o);
+        if (c < bc) {
+            bc = c;
+            best = o;
+        }
+    }
+    return best;
+}
+
+DFT_CXF unsigned magic_u32(unsigned d) { return d <= 1u ? 0u : (unsigned)(((1ull << 32) + d - 1) / d); }
+
+// apply row_step_order to every step of a row schedule (unskewed rows only)
+DFT_CXF void set_row_orders(LineFFT& f, int pitch)
+{
+    int L = f.n;
+    for (int i = 0; i < f.nsteps; ++i) {
+        const int r = f.radix[i], m = L / r, bpl = f.n / r, nblk = f.n / L;
+        const int o = row_step_order(f.n, pitch, L, r);
+        f.ord[i] = (unsigned char)o;
+        f.mmag[i] = magic_u32((unsigned)((o & 1) ? nblk : m));
+        f.bmag[i] = magic_u32((unsigned)((o & 2) ? (bpl + 15) / 16 * 16 : bpl));
+        L = m;
+    }
+}
 
 enum Mode : int {
     MODE_F2D = 0,       // fused rfft2: real image [H][W] (W = 2M) -> complex [H][M+1]
