@@ -280,7 +280,7 @@ static int realize_plan(trt_dft_plan_s* pl, trt_dft_plan_t* plan_out)
             // persistent pipelined variant for the big row / strided-axis passes
             pipe_fn pf = dft::pipe_kernel_for(r.kp.mode);
             if (pf && !getenv("TRT_DFT_NO_GEO")) {
-                pipe_fn pg = dft::pipe_kernel_for_geo(r.kp.mode, r.kp.mode == dft::MODE_C2C_COLS ? r.kp.col : r.kp.row);
+                pipe_fn pg = dft::pipe_kernel_for_geo(r.kp);
                 if (pg) pf = pg;
             }
             const int stage = (r.kp.smem_bytes - dft::kBarrierBytes + 127) / 128 * 128;

@@ -1,11 +1,15 @@
 // dft_pipe_kernels.cu -- the persistent pipelined shell of the generic engine.
 #include <cuda_runtime.h>
 #include <stdint.h>
+#include <stdlib.h>
 #include <string.h>
+
+#include <type_traits>
 
 #include "dft_launch.h"
 #include "dft_planner.h"
 #include "dft_programs.cuh"
+#include "dft_twostep.cuh"
 
 namespace {
 
@@ -207,6 +211,27 @@ struct GeoLine {
     }
 };
 
+// Registered strided-axis length with a two-step register-resident program (dft_twostep.cuh): N = (R1A*R1B) * (R2A*R2B),
+// tiles TM columns wide.  The generic schedule S0..S2 is still what the planner chose (it keys the dispatch).
+template <int N_, int S0, int S1, int S2, int R1A, int R1B, int R2A, int R2B, int TM_>
+struct GeoTwo : GeoLine<N_, S0, S1, S2, 1> {
+    static constexpr bool kTwoStep = true;
+    static constexpr int TM = TM_;
+    static_assert(R1A * R1B * R2A * R2B == N_, "two-step factors must multiply to N");
+    template <class Ctx>
+    __device__ static void run_cols(const KParams& p, long long tile, float2* buf, float* out, Ctx& ctx)
+    {
+        const long long o_ = tile / p.chunks, c_ = tile - o_ * p.chunks, col0 = c_ * p.G;
+        const int ncol = (int)((p.inner - col0) < p.G ? (p.inner - col0) : p.G);
+        float2* dst = (float2*)out + o_ * N_ * p.inner + col0;
+        dft::cols_two_step<R1A, R1B, R2A, R2B, TM_>(buf, p.P, p.tw_col, dst, p.inner, ncol, p.scale, p.inverse != 0, ctx);
+    }
+};
+template <class G, class = void>
+struct geo_two_step : std::false_type {};
+template <class G>
+struct geo_two_step<G, std::void_t<decltype(G::kTwoStep)>> : std::true_type {};
+
 template <int MODE, class Geo = GeoNone>
 __global__ void __launch_bounds__(kPipeThreads, 1)
     pipe_tile_kernel(const __grid_constant__ KParams p_in, const float* __restrict__ in, float* __restrict__ out, int ns, int ng,
@@ -297,7 +322,10 @@ __global__ void __launch_bounds__(kPipeThreads, 1)
         if constexpr (MODE == dft::MODE_I2D) dft::program_i2d<GroupCtx, false>(p, tile, buf, in, out, ctx);
         if constexpr (MODE == dft::MODE_F1D) dft::program_f1d<GroupCtx, false>(p, tile, buf, in, out, ctx);
         if constexpr (MODE == dft::MODE_I1D) dft::program_i1d<GroupCtx, false>(p, tile, buf, in, out, ctx);
-        if constexpr (MODE == dft::MODE_C2C_COLS) dft::program_cols<GroupCtx, false>(p, tile, buf, in, out, ctx);
+        if constexpr (MODE == dft::MODE_C2C_COLS) {
+            if constexpr (geo_two_step<Geo>::value) Geo::run_cols(p, tile, buf, out, ctx);
+            else dft::program_cols<GroupCtx, false>(p, tile, buf, in, out, ctx);
+        }
         asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
         __syncwarp();
         if ((tid & 31) == 0) asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(empty0 + 8 * s) : "memory");
@@ -315,9 +343,13 @@ namespace dft {
     X(1024, 4, 16, 16, 1)        \
     X(2048, 8, 16, 16, 1)
 #define DFT_GEO_COLS(X) X(720, 10, 9, 8, 1)
+// (N, planner schedule, R1A, R1B, R2A, R2B, TM): plain (not four-step) passes with TM-wide tiles only
+#define DFT_GEO_COLS_TWO(X) X(720, 10, 9, 8, 3, 8, 5, 6, 16) X(720, 10, 9, 8, 3, 8, 5, 6, 8)
 
-pipe_fn pipe_kernel_for_geo(int mode, const dft::LineFFT& f)
+pipe_fn pipe_kernel_for_geo(const KParams& k)
 {
+    const int mode = k.mode;
+    const dft::LineFFT& f = mode == dft::MODE_C2C_COLS ? k.col : k.row;
 #define DFT_GEO_MATCH(N_, A, B, C, D)                                                                          \
     (f.n == N_ && f.nsteps == ((A > 1) + (B > 1) + (C > 1) + (D > 1)) && f.radix[0] == A && (B == 1 || f.radix[1] == B) && \
      (C == 1 || f.radix[2] == C) && (D == 1 || f.radix[3] == D))
@@ -329,6 +361,12 @@ pipe_fn pipe_kernel_for_geo(int mode, const dft::LineFFT& f)
 #define DFT_GEO_TRY_COLS(N_, A, B, C, D)                                                                      \
     if (DFT_GEO_MATCH(N_, A, B, C, D) && mode == dft::MODE_C2C_COLS)                                          \
         return pipe_tile_kernel<dft::MODE_C2C_COLS, GeoLine<N_, A, B, C, D>>;
+#define DFT_GEO_TRY_COLS_TWO(N_, A, B, C, R1A, R1B, R2A, R2B, TM_)                                            \
+    if (DFT_GEO_MATCH(N_, A, B, C, 1) && mode == dft::MODE_C2C_COLS && k.G == TM_ && k.n1split <= 1 && !k.rev_in && \
+        !getenv("TRT_DFT_NO_TWOSTEP"))                                                                         \
+        return pipe_tile_kernel<dft::MODE_C2C_COLS, GeoTwo<N_, A, B, C, R1A, R1B, R2A, R2B, TM_>>;
+    DFT_GEO_COLS_TWO(DFT_GEO_TRY_COLS_TWO)
+#undef DFT_GEO_TRY_COLS_TWO
     DFT_GEO_ROWS(DFT_GEO_TRY_ROWS)
     DFT_GEO_COLS(DFT_GEO_TRY_COLS)
 #undef DFT_GEO_TRY_ROWS

@@ -299,6 +299,7 @@ struct Planner {
         k.ntiles = k.nunits;
         k.smem_bytes = N * k.P * 8 + kBarrierBytes;
         k.scale = scale;
+        k.inverse = inverse ? 1 : 0;
         k.threads = ((long long)N * tm >= 8192) ? 512 : 256;   // big tiles: more warps to hide the strided loads
         if (const char* e = getenv("TRT_DFT_COLS_THREADS")) k.threads = atoi(e) == 512 ? 512 : 256;
         Launch l;

@@ -154,6 +154,7 @@ struct KParams {
     int n1split;
     const float2* tw_four;
     int rev_in;
+    int inverse;             // cols mode: 1 = inverse transform (output index reversed)
     int in_place_ok;         // informational
     int io_align;            // 16 if in/out base pointers and unit strides allow 16-byte bulk copies
 };

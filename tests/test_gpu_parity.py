@@ -79,7 +79,7 @@ SHAPES = [
     # 2-D
     ((7, 8, 8), 2), ((3, 6, 10), 2), ((2, 5, 7), 2), ((2, 12, 18), 2), ((2, 17, 6), 2), ((2, 6, 38), 2),
     ((700, 4, 4), 2), ((1, 1, 16), 2), ((2, 16, 1), 2), ((2, 3, 3), 2), ((300, 32, 32), 2), ((5, 64, 64), 2),
-    ((3, 256, 256), 2), ((2, 180, 360), 2), ((2, 720, 1440), 2), ((1, 1024, 1024), 2), ((1, 2048, 4096), 2), ((2, 4096, 512), 2), ((1, 8192, 1024), 2), ((1, 5120, 320), 2),
+    ((3, 256, 256), 2), ((2, 180, 360), 2), ((2, 720, 1440), 2), ((4, 720, 1440), 2), ((1, 1024, 1024), 2), ((1, 2048, 4096), 2), ((2, 4096, 512), 2), ((1, 8192, 1024), 2), ((1, 5120, 320), 2),
     # 3-D
     ((2, 4, 6, 8), 3), ((2, 3, 5, 6), 3), ((1, 2, 3, 5, 7), 3), ((2, 1, 4, 4), 3), ((1, 17, 4, 6), 3),
     ((2, 32, 32, 32), 3), ((1, 20, 90, 180), 3),
@@ -191,7 +191,8 @@ def test_exec_host_and_streams(capi):
     assert O.rel_l2(out.cpu().numpy(), want) <= FWD_TOL
 
 
-@pytest.mark.parametrize("outer,n,inner", [(2, 90, 91), (3, 64, 5), (1, 720, 37), (2, 1, 8), (1, 17, 6), (1, 8192, 12), (2, 8192, 300), (1, 4096, 70)])
+@pytest.mark.parametrize("outer,n,inner", [(2, 90, 91), (3, 64, 5), (1, 720, 37), (2, 1, 8), (1, 17, 6), (1, 8192, 12), (2, 8192, 300), (1, 4096, 70),
+                                           (4, 720, 721), (3, 720, 800)])   # persistent two-step column kernel (>= 148 tiles)
 @pytest.mark.parametrize("direction", [0, 1])
 def test_c2c_strided_axis_plan(capi, outer, n, inner, direction):
     """trt_dft_plan_create_c2c: the column pass on its own (used by the pencil decomposition)."""

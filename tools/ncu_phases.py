@@ -1,7 +1,7 @@
 """Phase-level breakdown of a kernel from an .ncu-rep: SASS is cut at every BAR.SYNC (and at the
 mbarrier wait), and warp-instructions, stall samples and shared-memory wavefronts are summed per
 segment.  Run here (no GPU needed).
-    python tools/ncu_phases.py gpurun_out/prof.ncu-rep <kernel-regex>"""
+    python tools/ncu_phases.py gpurun_out/prof.ncu-rep <kernel-regex> [launch index]"""
 import csv
 import subprocess
 import sys
@@ -11,7 +11,15 @@ out = subprocess.run(['ncu', '-i', rep, '--page', 'source', '--csv', '--kernel-n
                      capture_output=True, text=True).stdout
 rows = list(csv.reader(out.splitlines()))
 hdr = next(r for r in rows if r and r[0] == 'Address')
-data = [r for r in rows if len(r) == len(hdr) and r[0].startswith('0x')]
+# one block per captured launch; an optional third argument picks one of them
+blocks, cur_b = [], None
+for r in rows:
+    if r and r[0] == 'Address':
+        cur_b = []
+        blocks.append(cur_b)
+    elif cur_b is not None and len(r) == len(hdr) and r[0].startswith('0x'):
+        cur_b.append(r)
+data = blocks[int(sys.argv[3])] if len(sys.argv) > 3 else [r for b in blocks for r in b]
 ix = {n: hdr.index(n) for n in hdr}
 def num(r, n):
     try:
