@@ -279,10 +279,6 @@ static int realize_plan(trt_dft_plan_s* pl, trt_dft_plan_t* plan_out)
             r.grid = (int)std::min<long long>(r.kp.ntiles, (long long)num_sms * occ);
             // persistent pipelined variant for the big row / strided-axis passes
             pipe_fn pf = dft::pipe_kernel_for(r.kp.mode);
-            if (pf && !getenv("TRT_DFT_NO_GEO")) {
-                pipe_fn pg = dft::pipe_kernel_for_geo(r.kp);
-                if (pg) pf = pg;
-            }
             const int stage = (r.kp.smem_bytes - dft::kBarrierBytes + 127) / 128 * 128;
             const int ns_cap = getenv("TRT_DFT_GP_NS") ? atoi(getenv("TRT_DFT_GP_NS")) : 4;   // tuning override
             int ns = std::min(ns_cap, (dft::kSmemMax - 256) / std::max(stage, 1));
@@ -298,6 +294,10 @@ static int realize_plan(trt_dft_plan_s* pl, trt_dft_plan_t* plan_out)
                     ns = ns_t;
                     tables = 1;
                 }
+            }
+            if (pf && !getenv("TRT_DFT_NO_GEO")) {
+                pipe_fn pg = dft::pipe_kernel_for_geo(r.kp, tables != 0);
+                if (pg) pf = pg;
             }
             if (pf && !getenv("TRT_DFT_NO_GPIPE") && stage >= 8 * 1024 && ns >= 2 && r.kp.ntiles >= num_sms) {
                 const int smem = ns * stage + 2 * ns * 8 + 64 + (tables ? tab_bytes : 0);

@@ -13,6 +13,6 @@ constexpr int kPipeCompute = 512, kPipeProducers = 64, kPipeThreads = kPipeCompu
 
 kernel_fn tile_kernel_for(int mode, int threads);           // nullptr: unknown mode
 pipe_fn pipe_kernel_for(int mode);                          // nullptr: mode has no pipelined variant
-pipe_fn pipe_kernel_for_geo(const KParams& k);              // nullptr: schedule not registered
+pipe_fn pipe_kernel_for_geo(const KParams& k, bool tables_in_smem);   // nullptr: schedule not registered
 
 }  // namespace dft

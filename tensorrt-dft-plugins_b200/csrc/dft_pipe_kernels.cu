@@ -227,6 +227,39 @@ struct GeoTwo : GeoLine<N_, S0, S1, S2, 1> {
         dft::cols_two_step<R1A, R1B, R2A, R2B, TM_>(buf, p.P, p.tw_col, dst, p.inner, ncol, p.scale, p.inverse != 0, ctx);
     }
 };
+// Registered row length (M packed complex points) with the two-step register-resident row programs.
+template <int N_, int S0, int S1, int S2, int R1A, int R1B, int R2A, int R2B>
+struct GeoTwoRows : GeoLine<N_, S0, S1, S2, 1> {
+    static constexpr bool kTwoStepRows = true;
+    static constexpr int R1 = R1A * R1B, R2 = R2A * R2B;
+    static_assert(R1 * R2 == N_, "two-step factors must multiply to N");
+    // T[a*R1 + k1] = w_M^(a*k1), built once per CTA where the generic kernels keep w_M^j
+    __device__ static void fill_table(float2* T, const float2* tw_global, int tid, int nthr)
+    {
+        for (int i = tid; i < N_; i += nthr) {
+            const int a = i / R1, k1 = i - a * R1;
+            T[i] = __ldg(tw_global + (a * k1) % N_);
+        }
+    }
+    template <class Ctx>
+    __device__ static void run_f1d(const KParams& p, long long tile, float2* buf, float* out, Ctx& ctx)
+    {
+        const long long first = tile * p.G;
+        const int nrows = (int)((p.nunits - first) < p.G ? (p.nunits - first) : p.G);
+        dft::rows_r2c_two_step<R1A, R1B, R2A, R2B>(buf, nrows, p.P, p.tw_row, p.tw_unt, (float2*)out + first * (N_ + 1), ctx);
+    }
+    template <class Ctx>
+    __device__ static void run_i1d(const KParams& p, long long tile, float2* buf, float* out, Ctx& ctx)
+    {
+        const long long first = tile * p.G;
+        const int nrows = (int)((p.nunits - first) < p.G ? (p.nunits - first) : p.G);
+        dft::rows_c2r_two_step<R1A, R1B, R2A, R2B>(buf, nrows, p.P, p.tw_row, p.tw_unt, (float2*)out + first * N_, p.scale, ctx);
+    }
+};
+template <class G, class = void>
+struct geo_two_rows : std::false_type {};
+template <class G>
+struct geo_two_rows<G, std::void_t<decltype(G::kTwoStepRows)>> : std::true_type {};
 template <class G, class = void>
 struct geo_two_step : std::false_type {};
 template <class G>
@@ -274,6 +307,11 @@ __global__ void __launch_bounds__(kPipeThreads, 1)
             p.perm_col = (const int*)stash(p_in.perm_col, p_in.col.n * 4);
         }
         if (MODE != dft::MODE_C2C_COLS) {
+            if constexpr (geo_two_rows<Geo>::value) {
+                Geo::fill_table((float2*)tb, p_in.tw_row, tid, kPipeThreads);   // p.tw_row now means T (dft_twostep.cuh)
+                p.tw_row = (const float2*)tb;
+                tb += (p_in.row.n * 8 + 15) / 16 * 16;
+            } else
             p.tw_row = (const float2*)stash(p_in.tw_row, p_in.row.n * 8);
             p.perm_row = (const int*)stash(p_in.perm_row, p_in.row.n * 4);
             p.tw_unt = (const float2*)stash(p_in.tw_unt, (p_in.M + 1) * 8);
@@ -320,8 +358,14 @@ __global__ void __launch_bounds__(kPipeThreads, 1)
         gp_wait(full0 + 8 * s, (unsigned)((it / ns) & 1));
         if constexpr (MODE == dft::MODE_F2D) dft::program_f2d<GroupCtx, false>(p, tile, buf, in, out, ctx);
         if constexpr (MODE == dft::MODE_I2D) dft::program_i2d<GroupCtx, false>(p, tile, buf, in, out, ctx);
-        if constexpr (MODE == dft::MODE_F1D) dft::program_f1d<GroupCtx, false>(p, tile, buf, in, out, ctx);
-        if constexpr (MODE == dft::MODE_I1D) dft::program_i1d<GroupCtx, false>(p, tile, buf, in, out, ctx);
+        if constexpr (MODE == dft::MODE_F1D) {
+            if constexpr (geo_two_rows<Geo>::value) Geo::run_f1d(p, tile, buf, out, ctx);
+            else dft::program_f1d<GroupCtx, false>(p, tile, buf, in, out, ctx);
+        }
+        if constexpr (MODE == dft::MODE_I1D) {
+            if constexpr (geo_two_rows<Geo>::value) Geo::run_i1d(p, tile, buf, out, ctx);
+            else dft::program_i1d<GroupCtx, false>(p, tile, buf, in, out, ctx);
+        }
         if constexpr (MODE == dft::MODE_C2C_COLS) {
             if constexpr (geo_two_step<Geo>::value) Geo::run_cols(p, tile, buf, out, ctx);
             else dft::program_cols<GroupCtx, false>(p, tile, buf, in, out, ctx);
@@ -344,9 +388,11 @@ namespace dft {
     X(2048, 8, 16, 16, 1)
 #define DFT_GEO_COLS(X) X(720, 10, 9, 8, 1)
 // (N, planner schedule, R1A, R1B, R2A, R2B, TM): plain (not four-step) passes with TM-wide tiles only
+// (M, planner schedule, R1A, R1B, R2A, R2B): unskewed rows, plain output, tables in shared memory
+#define DFT_GEO_ROWS_TWO(X) X(720, 16, 9, 5, 3, 8, 5, 6)
 #define DFT_GEO_COLS_TWO(X) X(720, 10, 9, 8, 3, 8, 5, 6, 16) X(720, 10, 9, 8, 3, 8, 5, 6, 8)
 
-pipe_fn pipe_kernel_for_geo(const KParams& k)
+pipe_fn pipe_kernel_for_geo(const KParams& k, bool tables_in_smem)
 {
     const int mode = k.mode;
     const dft::LineFFT& f = mode == dft::MODE_C2C_COLS ? k.col : k.row;
@@ -367,6 +413,13 @@ pipe_fn pipe_kernel_for_geo(const KParams& k)
         return pipe_tile_kernel<dft::MODE_C2C_COLS, GeoTwo<N_, A, B, C, R1A, R1B, R2A, R2B, TM_>>;
     DFT_GEO_COLS_TWO(DFT_GEO_TRY_COLS_TWO)
 #undef DFT_GEO_TRY_COLS_TWO
+#define DFT_GEO_TRY_ROWS_TWO(N_, A, B, C, R1A, R1B, R2A, R2B)                                                     \
+    if (DFT_GEO_MATCH(N_, A, B, C, 1) && k.pad == 0 && k.pack_n == 0 && tables_in_smem && !getenv("TRT_DFT_NO_TWOSTEP")) { \
+        if (mode == dft::MODE_F1D) return pipe_tile_kernel<dft::MODE_F1D, GeoTwoRows<N_, A, B, C, R1A, R1B, R2A, R2B>>; \
+        if (mode == dft::MODE_I1D) return pipe_tile_kernel<dft::MODE_I1D, GeoTwoRows<N_, A, B, C, R1A, R1B, R2A, R2B>>; \
+    }
+    DFT_GEO_ROWS_TWO(DFT_GEO_TRY_ROWS_TWO)
+#undef DFT_GEO_TRY_ROWS_TWO
     DFT_GEO_ROWS(DFT_GEO_TRY_ROWS)
     DFT_GEO_COLS(DFT_GEO_TRY_COLS)
 #undef DFT_GEO_TRY_ROWS

@@ -75,7 +75,8 @@ SHAPES = [
     # 1-D
     ((3, 2), 1), ((3, 6), 1), ((5, 30), 1), ((2, 9), 1), ((2, 15), 1), ((3, 1), 1), ((2, 360), 1),
     ((1000, 1024), 1), ((2, 2 * 7 * 11 * 13), 1), ((2, 34), 1), ((3, 19), 1), ((3, 4096), 1), ((2, 8192), 1),
-    ((2, 50000), 1), ((2, 65536), 1),
+    ((2, 50000), 1), ((2, 65536), 1), ((1203, 1440), 1),   # persistent two-step row kernels, last tile partial
+   
     # 2-D
     ((7, 8, 8), 2), ((3, 6, 10), 2), ((2, 5, 7), 2), ((2, 12, 18), 2), ((2, 17, 6), 2), ((2, 6, 38), 2),
     ((700, 4, 4), 2), ((1, 1, 16), 2), ((2, 16, 1), 2), ((2, 3, 3), 2), ((300, 32, 32), 2), ((5, 64, 64), 2),
