@@ -224,7 +224,10 @@ struct GeoTwo : GeoLine<N_, S0, S1, S2, 1> {
         const long long o_ = tile / p.chunks, c_ = tile - o_ * p.chunks, col0 = c_ * p.G;
         const int ncol = (int)((p.inner - col0) < p.G ? (p.inner - col0) : p.G);
         float2* dst = (float2*)out + o_ * N_ * p.inner + col0;
-        dft::cols_two_step<R1A, R1B, R2A, R2B, TM_>(buf, p.P, p.tw_col, dst, p.inner, ncol, p.scale, p.inverse != 0, ctx);
+        const int n1s = p.n1split > 1 ? p.n1split : 1;
+        const int n1 = (int)(o_ % n1s);
+        dft::cols_two_step<R1A, R1B, R2A, R2B, TM_>(buf, p.P, p.tw_col, dst, p.inner, ncol, p.scale, p.inverse != 0,
+                                                    p.n1split > 1 ? p.tw_four : nullptr, n1, ctx);
     }
 };
 // Registered row length (M packed complex points) with the two-step register-resident row programs.
@@ -390,7 +393,10 @@ namespace dft {
 // (N, planner schedule, R1A, R1B, R2A, R2B, TM): plain (not four-step) passes with TM-wide tiles only
 // (M, planner schedule, R1A, R1B, R2A, R2B): unskewed rows, plain output, tables in shared memory
 #define DFT_GEO_ROWS_TWO(X) X(720, 16, 9, 5, 3, 8, 5, 6)
-#define DFT_GEO_COLS_TWO(X) X(720, 10, 9, 8, 3, 8, 5, 6, 16) X(720, 10, 9, 8, 3, 8, 5, 6, 8)
+#define DFT_GEO_COLS_TWO(X)              \
+    X(720, 10, 9, 8, 3, 8, 5, 6, 16)     \
+    X(128, 16, 8, 1, 8, 1, 16, 1, 32)    \
+    X(64, 8, 8, 1, 8, 1, 8, 1, 64)
 
 pipe_fn pipe_kernel_for_geo(const KParams& k, bool tables_in_smem)
 {
@@ -408,7 +414,7 @@ pipe_fn pipe_kernel_for_geo(const KParams& k, bool tables_in_smem)
     if (DFT_GEO_MATCH(N_, A, B, C, D) && mode == dft::MODE_C2C_COLS)                                          \
         return pipe_tile_kernel<dft::MODE_C2C_COLS, GeoLine<N_, A, B, C, D>>;
 #define DFT_GEO_TRY_COLS_TWO(N_, A, B, C, R1A, R1B, R2A, R2B, TM_)                                            \
-    if (DFT_GEO_MATCH(N_, A, B, C, 1) && mode == dft::MODE_C2C_COLS && k.G == TM_ && k.n1split <= 1 && !k.rev_in && \
+    if (DFT_GEO_MATCH(N_, A, B, C, 1) && mode == dft::MODE_C2C_COLS && k.G == TM_ && !(k.inverse && k.n1split > 1) && \
         !getenv("TRT_DFT_NO_TWOSTEP"))                                                                         \
         return pipe_tile_kernel<dft::MODE_C2C_COLS, GeoTwo<N_, A, B, C, R1A, R1B, R2A, R2B, TM_>>;
     DFT_GEO_COLS_TWO(DFT_GEO_TRY_COLS_TWO)

@@ -26,10 +26,11 @@ DFT_HD void reg_fft(float2 (&v)[RA * RB])
 
 // Strided-axis complex FFT of one shared-memory tile buf[n*P + j] (n < N rows, TM columns), results to
 // global rows q*inner (+ column), natural order; `inverse` reverses the output index (IDFT = DFT read
-// backwards).  Columns j >= ncol of a partial tile are computed on whatever the tile holds and dropped.
+// backwards; the four-step passes instead read their input reversed and come here with inverse = false).
+// Columns j >= ncol of a partial tile are computed on whatever the tile holds and dropped.
 template <int R1A, int R1B, int R2A, int R2B, int TM, class Ctx>
 DFT_HD void cols_two_step(float2* buf, int P, const float2* tw /* w_N^j */, float2* dst, long long inner, int ncol, float scale,
-                          bool inverse, Ctx& ctx)
+                          bool inverse, const float2* tw4 /* four-step: w_Ntot^j, else null */, int n1, Ctx& ctx)
 {
     constexpr int R1 = R1A * R1B, R2 = R2A * R2B, N = R1 * R2;
     // step A
@@ -56,6 +57,15 @@ DFT_HD void cols_two_step(float2* buf, int P, const float2* tw /* w_N^j */, floa
             v[a] = cmul(p[a * P], DFT_LDT(twp));
         });
         reg_fft<R2A, R2B>(v);
+        if (tw4) {
+            // first pass of a four-step FFT: output row q = k1 + R1*k2 of slab n1 is multiplied by w_Ntot^(n1*q)
+            const float2* t4 = tw4 + n1 * k1;
+            const int t4s = n1 * R1;
+            static_for<0, R2>([&](auto kc) {
+                constexpr int k2 = decltype(kc)::value;
+                v[k2] = cmul(v[k2], DFT_LDT(t4 + k2 * t4s));
+            });
+        }
         if (j < ncol) {
             // output row q = k1 + R1*k2, or (N - q) mod N for the inverse
             // one pointer walks down (or, for the inverse, up) the output rows
