@@ -220,6 +220,7 @@ static int realize_plan(trt_dft_plan_s* pl, trt_dft_plan_t* plan_out)
         ResolvedLaunch r;
         r.kp = l.kp;
         if (l.tw_row_id >= 0) r.kp.tw_row = (const float2*)(base + tw_off[l.tw_row_id]);
+        if (l.tw_row_t_id >= 0) r.kp.tw_row_t = (const float2*)(base + tw_off[l.tw_row_t_id]);
         if (l.tw_col_id >= 0) r.kp.tw_col = (const float2*)(base + tw_off[l.tw_col_id]);
         if (l.tw_unt_id >= 0) r.kp.tw_unt = (const float2*)(base + tw_off[l.tw_unt_id]);
         if (l.perm_row_id >= 0) r.kp.perm_row = (const int*)(base + perm_off[l.perm_row_id]);

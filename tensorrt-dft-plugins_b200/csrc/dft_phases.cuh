@@ -47,7 +47,8 @@ DFT_HD int phys(int p, int pad) { return pad ? p + (p >> 4) + (p >> 8) : p; }
 // linear in the element index (see dft_planner.h).
 template <int R, bool COLS>
 DFT_HD void fft_step(float2* buf, int nlines, int pitch, int N, int L, const float2* tw, int ncols,
-                     int img_stride, unsigned mmag, unsigned bmag, unsigned lmag, int pad, int ord, int tid, int nthr)
+                     int img_stride, unsigned mmag, unsigned bmag, unsigned lmag, int pad, int ord, int tid, int nthr,
+                     const float2* tw_t = nullptr /* rows: this step's transposed twiddles, [(c-1)*m + b] */)
 {
     const int m = L / R;         // element stride inside the butterfly
     const int bpl = N / R;       // butterflies per line
@@ -99,7 +100,13 @@ DFT_HD void fft_step(float2* buf, int nlines, int pitch, int N, int L, const flo
             v[a] = p[a * es];
         });
         dft_reg<R>(v);
-        if (m > 1) {
+        if (m > 1 && !COLS && tw_t) {
+            const float2* twb = tw_t + b;
+            static_for<1, R>([&](auto cc) {
+                constexpr int c = decltype(cc)::value;
+                v[c] = cmul(v[c], DFT_LDT(twb + (c - 1) * m));
+            });
+        } else if (m > 1) {
             const float2* twb = tw + (long long)b * tws;
             const int tstep = b * tws;
             static_for<1, R>([&](auto cc) {
@@ -118,12 +125,12 @@ DFT_HD void fft_step(float2* buf, int nlines, int pitch, int N, int L, const flo
 template <bool COLS>
 DFT_HD void fft_step_dispatch(int radix, float2* buf, int nlines, int pitch, int N, int L,
                               const float2* tw, int ncols, int img_stride, unsigned mmag, unsigned bmag,
-                              unsigned lmag, int pad, int ord, int tid, int nthr)
+                              unsigned lmag, int pad, int ord, int tid, int nthr, const float2* tw_t = nullptr)
 {
     switch (radix) {
 #define DFT_CASE(R)                                                                     \
     case R:                                                                             \
-        fft_step<R, COLS>(buf, nlines, pitch, N, L, tw, ncols, img_stride, mmag, bmag, lmag, pad, ord, tid, nthr); \
+        fft_step<R, COLS>(buf, nlines, pitch, N, L, tw, ncols, img_stride, mmag, bmag, lmag, pad, ord, tid, nthr, tw_t); \
         break;
         DFT_CASE(2)
         DFT_CASE(3)

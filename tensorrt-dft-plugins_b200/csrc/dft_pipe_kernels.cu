@@ -314,8 +314,11 @@ __global__ void __launch_bounds__(kPipeThreads, 1)
                 Geo::fill_table((float2*)tb, p_in.tw_row, tid, kPipeThreads);   // p.tw_row now means T (dft_twostep.cuh)
                 p.tw_row = (const float2*)tb;
                 tb += (p_in.row.n * 8 + 15) / 16 * 16;
-            } else
-            p.tw_row = (const float2*)stash(p_in.tw_row, p_in.row.n * 8);
+            } else if (p_in.tw_row_t) {
+                p.tw_row_t = (const float2*)stash(p_in.tw_row_t, (p_in.row.n > 1 ? p_in.row.n - 1 : 1) * 8);   // (the plain table stays in global memory, unused)
+            } else {
+                p.tw_row = (const float2*)stash(p_in.tw_row, p_in.row.n * 8);
+            }
             p.perm_row = (const int*)stash(p_in.perm_row, p_in.row.n * 4);
             p.tw_unt = (const float2*)stash(p_in.tw_unt, (p_in.M + 1) * 8);
         }

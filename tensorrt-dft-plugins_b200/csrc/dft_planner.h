@@ -28,7 +28,7 @@ enum BufSel : int { BUF_IN = 0, BUF_OUT = 1, BUF_WS = 2, BUF_WS1 = 3 };
 struct Launch {
     KParams kp;            // pointers left null; resolved by the executor from the ids below
     int src, dst;          // BufSel
-    int tw_row_id = -1, tw_col_id = -1, tw_unt_id = -1;
+    int tw_row_id = -1, tw_col_id = -1, tw_unt_id = -1, tw_row_t_id = -1;
     int perm_row_id = -1, perm_col_id = -1;
     int tw_four_id = -1;   // four-step first pass: w_Ntot^j table
     std::string name;
@@ -176,6 +176,24 @@ inline std::vector<float2> make_twiddles(int n, int count)
     return t;
 }
 
+// per-step transposed twiddles of a row schedule (KParams::tw_row_t)
+inline std::vector<float2> make_twiddles_steps(const LineFFT& f)
+{
+    std::vector<float2> t;
+    int L = f.n;
+    for (int s = 0; s < f.nsteps; ++s) {
+        const int r = f.radix[s], m = L / r;
+        for (int c = 1; c < r; ++c)
+            for (int b = 0; b < m; ++b) {
+                const double a = 2.0 * 3.14159265358979323846264338327950288 * (double)(((long long)b * c) % L) / (double)L;
+                t.push_back(float2{(float)cos(a), (float)(-sin(a))});
+            }
+        L = m;
+    }
+    if (t.empty()) t.push_back(float2{1.f, 0.f});
+    return t;
+}
+
 // ---- plan -------------------------------------------------------------------------------------
 struct Planner {
     PlanDesc* pd;
@@ -225,6 +243,7 @@ struct Planner {
         l.src = src;
         l.dst = dst;
         l.tw_row_id = add_tw(make_twiddles(M, M));
+        l.tw_row_t_id = add_tw(make_twiddles_steps(k.row));
         l.perm_row_id = add_perm(make_perm(k.row, inverse, k.pad != 0));
         if (even) l.tw_unt_id = add_tw(make_twiddles(W, M + 1));
         char nm[128];
@@ -335,6 +354,7 @@ struct Planner {
         l.src = src;
         l.dst = dst;
         l.tw_row_id = add_tw(make_twiddles(M, M));
+        l.tw_row_t_id = add_tw(make_twiddles_steps(k.row));
         l.tw_col_id = add_tw(make_twiddles(H, H));
         l.tw_unt_id = add_tw(make_twiddles(W, M + 1));
         l.perm_row_id = add_perm(make_perm(k.row, inverse));

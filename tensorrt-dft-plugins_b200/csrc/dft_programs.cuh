@@ -13,9 +13,10 @@ namespace dft {
 
 template <class Ctx>
 DFT_HD void run_line_fft(const LineFFT& f, bool cols, float2* buf, int nlines, int pitch,
-                         const float2* tw, int ncols, int img_stride, Ctx& ctx, int pad = 0)
+                         const float2* tw, int ncols, int img_stride, Ctx& ctx, int pad = 0, const float2* tw_t = nullptr)
 {
     int L = f.n;
+    int toff = 0;                                       // start of this step's block of tw_t
     const unsigned lmag = cols ? magic_of((unsigned)nlines) : 0u;   // nlines differs on the last, partial tile
 #if defined(__CUDA_ARCH__)
 #pragma unroll
@@ -28,8 +29,9 @@ DFT_HD void run_line_fft(const LineFFT& f, bool cols, float2* buf, int nlines, i
                                     ctx.tid, ctx.nthr);
         else
             fft_step_dispatch<false>(r, buf, nlines, pitch, f.n, L, tw, ncols, img_stride, f.mmag[s], f.bmag[s], lmag, pad,
-                                     f.ord[s], ctx.tid, ctx.nthr);
+                                     f.ord[s], ctx.tid, ctx.nthr, tw_t ? tw_t + toff : nullptr);
         ctx.sync();
+        toff += (r - 1) * (L / r);
         L /= r;
     }
 }
@@ -62,7 +64,7 @@ DFT_HD void program_f2d(const KParams& p, long long tile, float2* buf, const flo
     const long long first = tile * p.G;
     const int nimg = (int)((p.nunits - first) < p.G ? (p.nunits - first) : p.G);
     if (LOAD) load_contig(ctx, (float*)buf, in + first * H * p.W, (long long)nimg * H * p.W);
-    run_line_fft(p.row, false, buf, nimg * H, M, p.tw_row, 0, 0, ctx);
+    run_line_fft(p.row, false, buf, nimg * H, M, p.tw_row, 0, 0, ctx, 0, p.tw_row_t);
     run_line_fft(p.col, true, buf, nimg * M, M, p.tw_col, M, H * M, ctx);
     // 2-D real-FFT split, two outputs per item: X[q][k] and X[(H-q)%H][M-k] share the pair
     // Y[q][k], Y[(H-q)%H][(M-k)%M].  k = M/2 (M even) is produced twice with identical values.
@@ -103,7 +105,7 @@ DFT_HD void program_i2d(const KParams& p, long long tile, float2* buf, const flo
     run_line_fft(p.col, true, buf, nimg * P, P, p.tw_col, P, H * P, ctx);
     merge_rows(buf, nimg * H, P, M, p.tw_unt, 0, ctx.tid, ctx.nthr);
     ctx.sync();
-    run_line_fft(p.row, false, buf, nimg * H, P, p.tw_row, 0, 0, ctx);
+    run_line_fft(p.row, false, buf, nimg * H, P, p.tw_row, 0, 0, ctx, 0, p.tw_row_t);
     float2* o = (float2*)out + first * H * M;
     const int per_img = H * M;
     const int total = nimg * per_img;
@@ -168,7 +170,7 @@ DFT_HD void program_f1d(const KParams& p, long long tile, float2* buf, const flo
     } else {
         load_contig(ctx, (float*)buf, in + first * p.W, (long long)nrows * p.W);
     }
-    run_line_fft(p.row, false, buf, nrows, P, p.tw_row, 0, 0, ctx, p.pad);
+    run_line_fft(p.row, false, buf, nrows, P, p.tw_row, 0, 0, ctx, p.pad, p.tw_row_t);
     // real-FFT split, two outputs per item: X[k] and X[M-k] come from the same pair Z[k], Z[M-k]
     float2* o = (float2*)out + first * Mo;
     const int per_row = M / 2 + 1;
@@ -222,7 +224,7 @@ DFT_HD void program_i1d(const KParams& p, long long tile, float2* buf, const flo
     }
     merge_rows(buf, nrows, P, M, p.tw_unt, p.pad, ctx.tid, ctx.nthr);
     ctx.sync();
-    run_line_fft(p.row, false, buf, nrows, P, p.tw_row, 0, 0, ctx, p.pad);
+    run_line_fft(p.row, false, buf, nrows, P, p.tw_row, 0, 0, ctx, p.pad, p.tw_row_t);
     float2* o = (float2*)out + first * M;
     const int total = nrows * M;
     const float sc = p.scale;

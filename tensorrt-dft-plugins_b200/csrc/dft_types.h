@@ -130,6 +130,9 @@ struct KParams {
     LineFFT row;             // FFT along the contiguous axis (length M)
     LineFFT col;             // FFT along the strided axis (length H)
     const float2* tw_row;    // w_M^j,  j in [0,M)        w_n = exp(-2*pi*i/n)
+    const float2* tw_row_t;  // row twiddles per step, transposed: step s (block length L, radix r, m = L/r) holds
+                             // w_L^(b*c) at [(c-1)*m + b]; consecutive work items b read consecutive entries.
+                             // Steps follow each other (n - 1 entries in all).  Null: use tw_row.
     const float2* tw_col;    // w_H^j,  j in [0,H)
     const float2* tw_unt;    // w_W^k,  k in [0,M]        (real-FFT split twiddles)
     const int* perm_row;     // smem position of output index k of the row FFT

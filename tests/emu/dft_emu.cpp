@@ -38,6 +38,7 @@ extern "C" int dft_emu_exec(int direction, int rank, const int64_t* dims, int64_
     for (auto& l : pd.launches) {
         dft::KParams kp = l.kp;
         if (l.tw_row_id >= 0) kp.tw_row = pd.tw_tables[l.tw_row_id].data();
+        if (l.tw_row_t_id >= 0) kp.tw_row_t = pd.tw_tables[l.tw_row_t_id].data();
         if (l.tw_col_id >= 0) kp.tw_col = pd.tw_tables[l.tw_col_id].data();
         if (l.tw_unt_id >= 0) kp.tw_unt = pd.tw_tables[l.tw_unt_id].data();
         if (l.perm_row_id >= 0) kp.perm_row = pd.perm_tables[l.perm_row_id].data();
