@@ -213,7 +213,7 @@ struct GeoLine {
 
 // Registered strided-axis length with a two-step register-resident program (dft_twostep.cuh): N = (R1A*R1B) * (R2A*R2B),
 // tiles TM columns wide.  The generic schedule S0..S2 is still what the planner chose (it keys the dispatch).
-template <int N_, int S0, int S1, int S2, int R1A, int R1B, int R2A, int R2B, int TM_>
+template <int N_, int S0, int S1, int S2, int R1A, int R1B, int R2A, int R2B, int TM_, bool FOUR_>
 struct GeoTwo : GeoLine<N_, S0, S1, S2, 1> {
     static constexpr bool kTwoStep = true;
     static constexpr int TM = TM_;
@@ -226,7 +226,7 @@ struct GeoTwo : GeoLine<N_, S0, S1, S2, 1> {
         float2* dst = (float2*)out + o_ * N_ * p.inner + col0;
         const int n1s = p.n1split > 1 ? p.n1split : 1;
         const int n1 = (int)(o_ % n1s);
-        dft::cols_two_step<R1A, R1B, R2A, R2B, TM_>(buf, p.P, p.tw_col, dst, p.inner, ncol, p.scale, p.inverse != 0,
+        dft::cols_two_step<R1A, R1B, R2A, R2B, TM_, FOUR_>(buf, p.P, p.tw_col, dst, p.inner, ncol, p.scale, p.inverse != 0,
                                                     p.n1split > 1 ? p.tw_four : nullptr, n1, ctx);
     }
 };
@@ -393,13 +393,13 @@ namespace dft {
     X(1024, 4, 16, 16, 1)        \
     X(2048, 8, 16, 16, 1)
 #define DFT_GEO_COLS(X) X(720, 10, 9, 8, 1)
-// (N, planner schedule, R1A, R1B, R2A, R2B, TM): plain (not four-step) passes with TM-wide tiles only
+// (N, planner schedule, R1A, R1B, R2A, R2B, TM, may be the first pass of a four-step FFT)
 // (M, planner schedule, R1A, R1B, R2A, R2B): unskewed rows, plain output, tables in shared memory
 #define DFT_GEO_ROWS_TWO(X) X(720, 16, 9, 5, 3, 8, 5, 6)
 #define DFT_GEO_COLS_TWO(X)              \
-    X(720, 10, 9, 8, 3, 8, 5, 6, 16)     \
-    X(128, 16, 8, 1, 8, 1, 16, 1, 32)    \
-    X(64, 8, 8, 1, 8, 1, 8, 1, 64)
+    X(720, 10, 9, 8, 3, 8, 5, 6, 16, false)     \
+    X(128, 16, 8, 1, 8, 1, 16, 1, 32, true)     \
+    X(64, 8, 8, 1, 8, 1, 8, 1, 64, true)
 
 pipe_fn pipe_kernel_for_geo(const KParams& k, bool tables_in_smem)
 {
@@ -416,10 +416,10 @@ pipe_fn pipe_kernel_for_geo(const KParams& k, bool tables_in_smem)
 #define DFT_GEO_TRY_COLS(N_, A, B, C, D)                                                                      \
     if (DFT_GEO_MATCH(N_, A, B, C, D) && mode == dft::MODE_C2C_COLS)                                          \
         return pipe_tile_kernel<dft::MODE_C2C_COLS, GeoLine<N_, A, B, C, D>>;
-#define DFT_GEO_TRY_COLS_TWO(N_, A, B, C, R1A, R1B, R2A, R2B, TM_)                                            \
-    if (DFT_GEO_MATCH(N_, A, B, C, 1) && mode == dft::MODE_C2C_COLS && k.G == TM_ && !(k.inverse && k.n1split > 1) && \
+#define DFT_GEO_TRY_COLS_TWO(N_, A, B, C, R1A, R1B, R2A, R2B, TM_, FOUR_)                                            \
+    if (DFT_GEO_MATCH(N_, A, B, C, 1) && mode == dft::MODE_C2C_COLS && k.G == TM_ && !(k.inverse && k.n1split > 1) && (FOUR_ || k.n1split <= 1) && \
         !getenv("TRT_DFT_NO_TWOSTEP"))                                                                         \
-        return pipe_tile_kernel<dft::MODE_C2C_COLS, GeoTwo<N_, A, B, C, R1A, R1B, R2A, R2B, TM_>>;
+        return pipe_tile_kernel<dft::MODE_C2C_COLS, GeoTwo<N_, A, B, C, R1A, R1B, R2A, R2B, TM_, FOUR_>>;
     DFT_GEO_COLS_TWO(DFT_GEO_TRY_COLS_TWO)
 #undef DFT_GEO_TRY_COLS_TWO
 #define DFT_GEO_TRY_ROWS_TWO(N_, A, B, C, R1A, R1B, R2A, R2B)                                                     \

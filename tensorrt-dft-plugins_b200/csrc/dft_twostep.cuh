@@ -28,7 +28,7 @@ DFT_HD void reg_fft(float2 (&v)[RA * RB])
 // global rows q*inner (+ column), natural order; `inverse` reverses the output index (IDFT = DFT read
 // backwards; the four-step passes instead read their input reversed and come here with inverse = false).
 // Columns j >= ncol of a partial tile are computed on whatever the tile holds and dropped.
-template <int R1A, int R1B, int R2A, int R2B, int TM, class Ctx>
+template <int R1A, int R1B, int R2A, int R2B, int TM, bool FOUR, class Ctx>
 DFT_HD void cols_two_step(float2* buf, int P, const float2* tw /* w_N^j */, float2* dst, long long inner, int ncol, float scale,
                           bool inverse, const float2* tw4 /* four-step: w_Ntot^j, else null */, int n1, Ctx& ctx)
 {
@@ -57,8 +57,8 @@ DFT_HD void cols_two_step(float2* buf, int P, const float2* tw /* w_N^j */, floa
             v[a] = cmul(p[a * P], DFT_LDT(twp));
         });
         reg_fft<R2A, R2B>(v);
-        if (tw4) {
-            // first pass of a four-step FFT: output row q = k1 + R1*k2 of slab n1 is multiplied by w_Ntot^(n1*q)
+        if (FOUR && tw4) {
+            // first pass of a four-step FFT (compiled in only for lengths that occur as four-step factors): output row q = k1 + R1*k2 of slab n1 is multiplied by w_Ntot^(n1*q)
             const float2* t4 = tw4 + n1 * k1;
             const int t4s = n1 * R1;
             static_for<0, R2>([&](auto kc) {
