@@ -340,10 +340,10 @@ DFT_HD void program_cols(const KParams& p, long long tile, float2* buf, const fl
     if (fixed_col) {
         float2* d0 = dst + (long long)n0 * p.inner + j0;
         const long long dstep2 = (long long)rstep * p.inner;
+        if (!four) {
 #if defined(__CUDA_ARCH__)
 #pragma unroll 4
 #endif
-        if (!four) {
             for (int q = n0; q < N; q += rstep, d0 += dstep2) {
                 const float2 z = buf[DFT_LDT(p.perm_col + q) * P + j0];
                 *d0 = float2{z.x * sc, z.y * sc};
