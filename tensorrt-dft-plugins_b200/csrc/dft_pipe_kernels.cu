@@ -215,8 +215,7 @@ struct GeoLine {
 // tiles TM columns wide.  The generic schedule S0..S2 is still what the planner chose (it keys the dispatch).
 template <int N_, int S0, int S1, int S2, int R1A, int R1B, int R2A, int R2B, int TM_, bool FOUR_>
 struct GeoTwo : GeoLine<N_, S0, S1, S2, 1> {
-    static constexpr bool kTwoStep = true;
-    static constexpr int TM = TM_;
+    using two_step_cols_tag = void;                        // detected by geo_two_step
     static_assert(R1A * R1B * R2A * R2B == N_, "two-step factors must multiply to N");
     template <class Ctx>
     __device__ static void run_cols(const KParams& p, long long tile, float2* buf, float* out, Ctx& ctx)
@@ -233,7 +232,7 @@ struct GeoTwo : GeoLine<N_, S0, S1, S2, 1> {
 // Registered row length (M packed complex points) with the two-step register-resident row programs.
 template <int N_, int S0, int S1, int S2, int R1A, int R1B, int R2A, int R2B>
 struct GeoTwoRows : GeoLine<N_, S0, S1, S2, 1> {
-    static constexpr bool kTwoStepRows = true;
+    using two_step_rows_tag = void;                        // detected by geo_two_rows
     static constexpr int R1 = R1A * R1B, R2 = R2A * R2B;
     static_assert(R1 * R2 == N_, "two-step factors must multiply to N");
     // T[a*R1 + k1] = w_M^(a*k1), built once per CTA where the generic kernels keep w_M^j
@@ -262,11 +261,11 @@ struct GeoTwoRows : GeoLine<N_, S0, S1, S2, 1> {
 template <class G, class = void>
 struct geo_two_rows : std::false_type {};
 template <class G>
-struct geo_two_rows<G, std::void_t<decltype(G::kTwoStepRows)>> : std::true_type {};
+struct geo_two_rows<G, std::void_t<typename G::two_step_rows_tag>> : std::true_type {};
 template <class G, class = void>
 struct geo_two_step : std::false_type {};
 template <class G>
-struct geo_two_step<G, std::void_t<decltype(G::kTwoStep)>> : std::true_type {};
+struct geo_two_step<G, std::void_t<typename G::two_step_cols_tag>> : std::true_type {};
 
 template <int MODE, class Geo = GeoNone>
 __global__ void __launch_bounds__(kPipeThreads, 1)
