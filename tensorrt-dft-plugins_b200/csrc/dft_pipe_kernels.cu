@@ -416,7 +416,7 @@ pipe_fn pipe_kernel_for_geo(const KParams& k, bool tables_in_smem)
     if (DFT_GEO_MATCH(N_, A, B, C, D) && mode == dft::MODE_C2C_COLS)                                          \
         return pipe_tile_kernel<dft::MODE_C2C_COLS, GeoLine<N_, A, B, C, D>>;
 #define DFT_GEO_TRY_COLS_TWO(N_, A, B, C, R1A, R1B, R2A, R2B, TM_, FOUR_)                                            \
-    if (DFT_GEO_MATCH(N_, A, B, C, 1) && mode == dft::MODE_C2C_COLS && k.G == TM_ && !(k.inverse && k.n1split > 1) && (FOUR_ || k.n1split <= 1) && \
+    if (DFT_GEO_MATCH(N_, A, B, C, 1) && mode == dft::MODE_C2C_COLS && k.G == TM_ && !(k.inverse && k.n1split > 1) && (FOUR_ || k.n1split <= 1) && tables_in_smem && \
         !getenv("TRT_DFT_NO_TWOSTEP"))                                                                         \
         return pipe_tile_kernel<dft::MODE_C2C_COLS, GeoTwo<N_, A, B, C, R1A, R1B, R2A, R2B, TM_, FOUR_>>;
     DFT_GEO_COLS_TWO(DFT_GEO_TRY_COLS_TWO)

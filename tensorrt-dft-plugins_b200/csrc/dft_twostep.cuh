@@ -17,6 +17,20 @@
 
 namespace dft {
 
+// Table loads of the two-step programs: the dispatch guarantees that their tables sit in shared memory, so
+// say so (a generic load of a shared address takes the long-latency path through L1TEX address translation).
+#if defined(__CUDA_ARCH__)
+__device__ __forceinline__ float2 lds_f2(const float2* p)
+{
+    float2 v;
+    asm("ld.shared.v2.f32 {%0, %1}, [%2];" : "=f"(v.x), "=f"(v.y) : "r"((unsigned)__cvta_generic_to_shared(p)));
+    return v;
+}
+#define DFT_LDS(ptr) ::dft::lds_f2(ptr)
+#else
+#define DFT_LDS(ptr) (*(ptr))
+#endif
+
 template <int RA, int RB>
 DFT_HD void reg_fft(float2 (&v)[RA * RB])
 {
@@ -128,8 +142,8 @@ DFT_HD void rows_two_step(float2* buf, int nrows_tile, int P, int PA, const floa
             constexpr int j = decltype(jc)::value;
             const float4 q = p4[j];
             if constexpr (j == 0) v[0] = float2{q.x, q.y};
-            else v[2 * j] = cmul(float2{q.x, q.y}, DFT_LDT(tw + (2 * j) * R1));
-            v[2 * j + 1] = cmul(float2{q.z, q.w}, DFT_LDT(tw + (2 * j + 1) * R1));
+            else v[2 * j] = cmul(float2{q.x, q.y}, DFT_LDS(tw + (2 * j) * R1));
+            v[2 * j + 1] = cmul(float2{q.z, q.w}, DFT_LDS(tw + (2 * j + 1) * R1));
         });
         reg_fft<R2A, R2B>(v);
         if (barrier_before_emit) ctx.sync();            // emit overwrites the tile: every line must be in registers
@@ -151,7 +165,7 @@ DFT_HD void rows_r2c_two_step(float2* buf, int nrows, int P, const float2* T, co
     // real-FFT split: each thread keeps its frequencies k (and M-k) and walks down the rows
     for (int k = ctx.tid; k <= M / 2; k += ctx.nthr) {
         const int kk = M - k;
-        const float2 w = DFT_LDT(twU + k);
+        const float2 w = DFT_LDS(twU + k);
         const float2* za = buf + k;
         const float2* zb = buf + (k == 0 ? 0 : kk);
         float2* oa = o + k;
@@ -177,7 +191,7 @@ DFT_HD void rows_c2r_two_step(float2* buf, int nrows, int P, const float2* T, co
     // Hermitian merge, in place, stored conjugated and scaled: Z'[k] = (a + conj b) + i conj(w)(a - conj b)
     for (int k = ctx.tid; k <= M / 2; k += ctx.nthr) {
         const int kk = M - k;
-        const float2 w = DFT_LDT(twU + k);
+        const float2 w = DFT_LDS(twU + k);
         float2* pa = buf + k;
         float2* pb = buf + kk;
         for (int r = 0; r < nrows; ++r, pa += P, pb += P) {
