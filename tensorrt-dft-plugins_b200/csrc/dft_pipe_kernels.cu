@@ -295,7 +295,9 @@ __global__ void __launch_bounds__(kPipeThreads, 1)
             }
         }
     }
-    if (tables_in_smem) {
+    // Registered geometries are only dispatched when their tables fit (pipe_kernel_for_geo): the branch is then
+    // compile-time true and the compiler knows that every table pointer is a shared-memory address (LDS, not LD).
+    if (Geo::kStatic || tables_in_smem) {
         // twiddle / permutation tables move into shared memory once per (persistent) CTA
         unsigned char* tb = smem_raw + (size_t)ns * stage_bytes + 2 * ns * 8 + 64;
         auto stash = [&](const void* src, int bytes) -> void* {
@@ -313,7 +315,7 @@ __global__ void __launch_bounds__(kPipeThreads, 1)
                 Geo::fill_table((float2*)tb, p_in.tw_row, tid, kPipeThreads);   // p.tw_row now means T (dft_twostep.cuh)
                 p.tw_row = (const float2*)tb;
                 tb += (p_in.row.n * 8 + 15) / 16 * 16;
-            } else if (p_in.tw_row_t) {
+            } else if (Geo::kStatic || p_in.tw_row_t) {           // (the planner always provides it for the row modes)
                 p.tw_row_t = (const float2*)stash(p_in.tw_row_t, (p_in.row.n > 1 ? p_in.row.n - 1 : 1) * 8);   // (the plain table stays in global memory, unused)
             } else {
                 p.tw_row = (const float2*)stash(p_in.tw_row, p_in.row.n * 8);
@@ -402,6 +404,7 @@ namespace dft {
 
 pipe_fn pipe_kernel_for_geo(const KParams& k, bool tables_in_smem)
 {
+    if (!tables_in_smem) return nullptr;                 // the static kernels keep their tables in shared memory
     const int mode = k.mode;
     const dft::LineFFT& f = mode == dft::MODE_C2C_COLS ? k.col : k.row;
 #define DFT_GEO_MATCH(N_, A, B, C, D)                                                                          \
