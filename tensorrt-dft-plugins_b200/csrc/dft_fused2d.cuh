@@ -41,6 +41,11 @@ struct FusedCfg {
     // Without it, lanes reading "element j of consecutive chunks" (row step RB, and the column-pair step
     // that walks consecutive frequencies k = c + RA*e) are RB * 8 bytes apart and collide 8-fold.
     static constexpr bool SWZ = (RB & (RB - 1)) == 0 && RB >= 8 && (NT_ % 32 == 0) && (32 % RB == 0);
+    // Forward kernel, RB == 8 and rows a multiple of 16 elements long: rows r and r+1 start in the same bank, so
+    // two rows' items in one half-warp collide 2-way.  Odd rows therefore swap the two 8-element halves of every
+    // 16-element window (position ^ 8, i.e. chunk c sits at c ^ 1).  Column steps only ever combine rows of equal
+    // parity at one position (CB even) or know the parity statically (the last step), so they follow for free.
+    static constexpr bool RSW = SWZ && RB == 8 && (W_ / 2) % 16 == 0 && CB_ % 2 == 0 && H_ % 2 == 0;
     static constexpr bool BULK_REAL = (H * W * 4) % 16 == 0;
     static constexpr bool BULK_CPLX = (H * PI * 8) % 16 == 0;
 };
@@ -145,7 +150,8 @@ __global__ void __launch_bounds__(C::NT, C::MINB)
                 // the row's loads and its stores is enough
                 __syncwarp();
                 float2* prow = buf + row * M;
-                static_for<0, RA>([&](auto cc) { constexpr int c = decltype(cc)::value; prow[c * RB + (b ^ (c & (RB - 1)))] = v[c]; });
+                const int rp = C::RSW ? (row & 1) : 0;
+                static_for<0, RA>([&](auto cc) { constexpr int c = decltype(cc)::value; prow[(c ^ rp) * RB + (b ^ (c & (RB - 1)))] = v[c]; });
             } else {
                 static_for<0, RA>([&](auto cc) { constexpr int c = decltype(cc)::value; p[c * RB] = v[c]; });
             }
@@ -154,8 +160,9 @@ __global__ void __launch_bounds__(C::NT, C::MINB)
         // rows, step RB: RB contiguous elements; row frequency k = k1 + RA*k2 ends at k1*RB + k2
 #pragma unroll 1
         for (int t = tid; t < H * RA; t += NT) {
-            float2* p = buf + t * RB;
-            const int sw = C::SWZ ? ((t % RA) & (RB - 1)) : 0;      // chunk index k1 = t mod RA
+            const int k1 = t % RA;                                  // chunk index
+            float2* p = buf + (C::RSW ? (t - k1 + (k1 ^ ((t / RA) & 1))) : t) * RB;
+            const int sw = C::SWZ ? (k1 & (RB - 1)) : 0;
             float2 v[RB];
             static_for<0, RB>([&](auto jc) { constexpr int j = decltype(jc)::value; v[j] = p[j ^ sw]; });
             dft_reg<RB>(v);
@@ -187,7 +194,13 @@ __global__ void __launch_bounds__(C::NT, C::MINB)
             const float2* pa = buf + q1 * CB * M + colA;
             const float2* pb = buf + q1B * CB * M + colB;
             float2 A[CB], B[CB];
-            static_for<0, CB>([&](auto jc) { constexpr int j = decltype(jc)::value; A[j] = pa[j * M]; B[j] = pb[j * M]; });
+            // rows q1*CB + j and q1B*CB + j have parity j & 1 (CB even): odd rows hold the position ^ 8
+            const int dA = C::RSW ? ((colA ^ 8) - colA) : 0, dB = C::RSW ? ((colB ^ 8) - colB) : 0;
+            static_for<0, CB>([&](auto jc) {
+                constexpr int j = decltype(jc)::value;
+                A[j] = pa[j * M + (j & 1) * dA];
+                B[j] = pb[j * M + (j & 1) * dB];
+            });
             dft_reg<CB>(A);
             dft_reg<CB>(B);
             // A[k2] = Y[q1 + CA*k2][k]; its partner Y[(H-q) mod H][M-k] is B[CB-1-k2] (q1 > 0) or
