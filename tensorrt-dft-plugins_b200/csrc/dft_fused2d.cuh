@@ -46,6 +46,10 @@ struct FusedCfg {
     // 16-element window (position ^ 8, i.e. chunk c sits at c ^ 1).  Column steps only ever combine rows of equal
     // parity at one position (CB even) or know the parity statically (the last step), so they follow for free.
     static constexpr bool RSW = SWZ && RB == 8 && (W_ / 2) % 16 == 0 && CB_ % 2 == 0 && H_ % 2 == 0;
+    // Inverse kernel, RB == RA == 8: rows sit M+1 (odd) elements apart, so rows r and r+8 start 8 banks apart.
+    // The row steps hand consecutive 8-lane groups the rows r, r+8, r+1, r+9, ... of each block of 16 rows: a
+    // half-warp then covers all 16 banks (in natural row order two neighbouring rows overlap in 7 of 8).
+    static constexpr bool IRW = SWZ && RB == 8 && RA == 8 && H_ % 16 == 0 && (NT_ / RA_) % 16 == 0;
     static constexpr bool BULK_REAL = (H * W * 4) % 16 == 0;
     static constexpr bool BULK_CPLX = (H * PI * 8) % 16 == 0;
 };
@@ -321,7 +325,8 @@ __global__ void __launch_bounds__(C::NT, C::MINB)
         // rows, step RA (pitch M+1)
 #pragma unroll 1
         for (int t = tid; t < H * RB; t += NT) {
-            const int row = t / RB, b = t - row * RB;
+            const int g = t / RB, b = t - g * RB;
+            const int row = C::IRW ? ((g & ~15) | ((g & 1) << 3) | ((g >> 1) & 7)) : g;
             float2* p = buf + row * PI + b;
             float2 v[RA];
             static_for<0, RA>([&](auto ac) { constexpr int a = decltype(ac)::value; v[a] = p[a * RB]; });
@@ -343,7 +348,8 @@ __global__ void __launch_bounds__(C::NT, C::MINB)
             constexpr int NTR = RPR * RA;
 #pragma unroll 1
             for (int r0 = 0; r0 < H; r0 += RPR) {
-                const int rl = tid / RA, k1 = tid - rl * RA;
+                const int g = tid / RA, k1 = tid - g * RA;
+                const int rl = C::IRW ? ((g & ~15) | ((g & 1) << 3) | ((g >> 1) & 7)) : g;
                 const int row = r0 + rl;
                 const bool active = (tid < NTR) && (row < H);
                 float2 v[RB];
