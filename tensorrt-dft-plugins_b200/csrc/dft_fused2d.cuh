@@ -362,12 +362,27 @@ __global__ void __launch_bounds__(C::NT, C::MINB)
                 __syncthreads();
                 if (active) {
                     float2* d = buf + row * M;
-                    static_for<0, RB>([&](auto kc) {
-                        constexpr int k2 = decltype(kc)::value;
-                        int n = M - k1 - RA * k2;
-                        if (k2 == 0 && k1 == 0) n = 0;
-                        d[n] = v[k2];
-                    });
+                    if constexpr (C::IRW) {
+                        // the output rows are dense (pitch M: rows r and r+8 share banks), so the odd 8-lane groups
+                        // store each pair (k2, k2+1) in the opposite order: their n differ by RA = 8 banks
+                        const bool odd = (g & 1) != 0;
+                        static_for<0, RB / 2>([&](auto kc) {
+                            constexpr int k2 = 2 * decltype(kc)::value;
+                            int n0 = M - k1 - RA * k2;
+                            if (k2 == 0 && k1 == 0) n0 = 0;
+                            const int n1 = M - k1 - RA * (k2 + 1);
+                            const float2 a = odd ? v[k2 + 1] : v[k2], b = odd ? v[k2] : v[k2 + 1];
+                            d[odd ? n1 : n0] = a;
+                            d[odd ? n0 : n1] = b;
+                        });
+                    } else {
+                        static_for<0, RB>([&](auto kc) {
+                            constexpr int k2 = decltype(kc)::value;
+                            int n = M - k1 - RA * k2;
+                            if (k2 == 0 && k1 == 0) n = 0;
+                            d[n] = v[k2];
+                        });
+                    }
                 }
             }
         }
