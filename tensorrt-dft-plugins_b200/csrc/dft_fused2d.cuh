@@ -146,7 +146,20 @@ __global__ void __launch_bounds__(C::NT, C::MINB)
             const int row = t / RB, b = t - row * RB;
             float2* p = buf + row * M + b;
             float2 v[RA];
-            static_for<0, RA>([&](auto ac) { constexpr int a = decltype(ac)::value; v[a] = p[a * RB]; });
+            if constexpr (C::RSW && RA % 2 == 0) {
+                // the image arrives dense (rows r and r+1 share banks): odd rows read each pair (a, a+1) in the
+                // opposite order, RB = 8 banks away from what the even row's lanes read at the same time
+                const bool odd = (row & 1) != 0;
+                const int o = odd ? RB : 0;
+                static_for<0, RA / 2>([&](auto ac) {
+                    constexpr int a = 2 * decltype(ac)::value;
+                    const float2 x0 = p[a * RB + o], x1 = p[a * RB + RB - o];
+                    v[a] = odd ? x1 : x0;
+                    v[a + 1] = odd ? x0 : x1;
+                });
+            } else {
+                static_for<0, RA>([&](auto ac) { constexpr int a = decltype(ac)::value; v[a] = p[a * RB]; });
+            }
             dft_reg<RA>(v);
             static_for<1, RA>([&](auto cc) { constexpr int c = decltype(cc)::value; v[c] = cmul(v[c], twR[(c - 1) * RB + b]); });
             if constexpr (C::SWZ) {
