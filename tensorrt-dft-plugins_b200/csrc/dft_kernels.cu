@@ -77,6 +77,8 @@ struct ResolvedLaunch {
     int spec_smem = 0, spec_nt = 0, spec_grid = 0;
     bool spec_needs_align16 = false; // pipelined kernels move whole images with TMA bulk copies only
     pipe_fn gpipe = nullptr;         // non-null: persistent pipelined generic kernel instead of fn
+    pipe_fn gpipe_pack = nullptr;    // what runs in its place once trt_dft_plan_set_column_split has been called
+                                     // (the two-step row programs write plain rows only)
     int gp_ns = 0, gp_ng = 0, gp_stage = 0, gp_smem = 0, gp_grid = 0, gp_tables = 0;
 };
 
@@ -305,6 +307,19 @@ static int realize_plan(trt_dft_plan_s* pl, trt_dft_plan_t* plan_out)
                 r.gp_tables = tables;
                 if (cudaFuncSetAttribute((const void*)pf, cudaFuncAttributeMaxDynamicSharedMemorySize, dft::kSmemMax) == cudaSuccess) {
                     r.gpipe = pf;
+                    r.gpipe_pack = pf;
+                    if (r.kp.mode == dft::MODE_F1D) {
+                        KParams kpack = r.kp;
+                        kpack.pack_n = 1;
+                        pipe_fn pp = dft::pipe_kernel_for(r.kp.mode);
+                        if (!getenv("TRT_DFT_NO_GEO"))
+                            if (pipe_fn pg2 = dft::pipe_kernel_for_geo(kpack, tables != 0)) pp = pg2;
+                        if (pp != pf && cudaFuncSetAttribute((const void*)pp, cudaFuncAttributeMaxDynamicSharedMemorySize, dft::kSmemMax) != cudaSuccess) {
+                            cudaGetLastError();
+                            pp = nullptr;            // fall back to the non-persistent kernel for split output
+                        }
+                        r.gpipe_pack = pp;
+                    }
                     r.gp_ns = ns;
                     r.gp_ng = ns >= 3 ? 2 : 1;
                     if (getenv("TRT_DFT_GP_NG")) r.gp_ng = std::max(1, std::min(atoi(getenv("TRT_DFT_GP_NG")), ns - 1));
@@ -336,7 +351,7 @@ int trt_dft_plan_set_column_split(trt_dft_plan_t plan, int nparts, const int64_t
             if (col_starts[j + 1] < col_starts[j]) return TRT_DFT_ERR_INVALID_ARG;
     }
     k.pack_n = nparts;
-    for (int j = 0; j <= nparts; ++j) k.pack_c0[j] = (int)col_starts[j];
+    for (int j = 0; nparts > 0 && j <= nparts; ++j) k.pack_c0[j] = (int)col_starts[j];   // (nparts == 0: back to plain rows, col_starts may be null)
     k.pack_hn = (int)rows_per_image;
     return TRT_DFT_OK;
 }
@@ -409,8 +424,9 @@ int trt_dft_exec(trt_dft_plan_t plan, const void* in, void* out, void* workspace
         if ((r.kp.mode == dft::MODE_I1D || r.kp.mode == dft::MODE_I2D) && ((uintptr_t)dst & 7)) return TRT_DFT_ERR_INVALID_ARG;
         if (r.spec && !(r.spec_needs_align16 && ((((uintptr_t)src) | ((uintptr_t)dst)) & 15)))
             r.spec<<<r.spec_grid, r.spec_nt, r.spec_smem, st>>>(src, dst, r.kp.nunits, r.spec_tab, r.kp.scale);
-        else if (r.gpipe)
-            r.gpipe<<<r.gp_grid, kPipeThreads, r.gp_smem, st>>>(r.kp, src, dst, r.gp_ns, r.gp_ng, r.gp_stage, r.gp_tables);
+        else if (r.gpipe && (r.kp.pack_n == 0 || r.gpipe_pack))
+            (r.kp.pack_n ? r.gpipe_pack : r.gpipe)<<<r.gp_grid, kPipeThreads, r.gp_smem, st>>>(r.kp, src, dst, r.gp_ns, r.gp_ng, r.gp_stage,
+                                                                                            r.gp_tables);
         else
             r.fn<<<r.grid, r.kp.threads, r.kp.smem_bytes, st>>>(r.kp, src, dst);
         if (cudaPeekAtLastError() != cudaSuccess) {

@@ -256,3 +256,41 @@ def test_headline_kernels_at_every_batch_remainder(capi, nimg):
     torch.cuda.synchronize()
     err = (xr.cpu().double() - want_x).flatten(1).norm(dim=1) / want_x.flatten(1).norm(dim=1)
     assert float(err.max()) <= FWD_TOL, f"worst image {int(err.argmax())}"
+
+
+@pytest.mark.parametrize("W", [1440, 512, 90])
+def test_column_split_output_matches_plain_rows(capi, W):
+    """trt_dft_plan_set_column_split after plan creation: the row pass must write every image's spectrum split by
+    destination rank whichever kernel the plan had picked for plain rows (1440-point rows run a specialised
+    persistent kernel that only writes plain rows, so the plan has to switch kernels)."""
+    import ctypes
+    hn, nimg = 720, 2
+    Mo = W // 2 + 1
+    torch.manual_seed(3)
+    x = torch.randn(nimg * hn, W, device="cuda")
+    plain = capi.rfftn(x, 1)                                   # [rows, Mo, 2]
+    plan = capi.Plan(capi.FORWARD, (W,), nimg * hn)
+    starts = [0, Mo // 3, Mo // 3, Mo - 5, Mo]                  # uneven, one empty part
+    L = capi.lib()
+    L.trt_dft_plan_set_column_split.restype = ctypes.c_int
+    L.trt_dft_plan_set_column_split.argtypes = [ctypes.c_void_p, ctypes.c_int, ctypes.POINTER(ctypes.c_int64), ctypes.c_int64]
+    arr = (ctypes.c_int64 * len(starts))(*starts)
+    assert L.trt_dft_plan_set_column_split(plan.handle, len(starts) - 1, arr, hn) == 0
+    out = torch.full((nimg * hn * Mo, 2), float("nan"), device="cuda")
+    plan.exec(x, out)
+    torch.cuda.synchronize()
+    want = []
+    p3 = plain.view(nimg, hn, Mo, 2)
+    for b in range(nimg):
+        for j in range(len(starts) - 1):
+            want.append(p3[b, :, starts[j]:starts[j + 1], :].reshape(-1, 2))
+    want = torch.cat(want)
+    # (two different kernels may have produced `plain` and `out`: same values up to fp32 rounding, every element placed)
+    assert not torch.isnan(out).any()
+    assert O.rel_l2(out.cpu().numpy(), want.cpu().numpy()) <= RT_TOL
+    # and back to plain rows
+    assert L.trt_dft_plan_set_column_split(plan.handle, 0, None, 0) == 0
+    out2 = torch.empty_like(plain)
+    plan.exec(x, out2)
+    torch.cuda.synchronize()
+    assert torch.equal(out2, plain)
