@@ -76,7 +76,6 @@ SHAPES = [
     ((3, 2), 1), ((3, 6), 1), ((5, 30), 1), ((2, 9), 1), ((2, 15), 1), ((3, 1), 1), ((2, 360), 1),
     ((1000, 1024), 1), ((2, 2 * 7 * 11 * 13), 1), ((2, 34), 1), ((3, 19), 1), ((3, 4096), 1), ((2, 8192), 1),
     ((2, 50000), 1), ((2, 65536), 1), ((1203, 1440), 1),   # persistent two-step row kernels, last tile partial
-   
     # 2-D
     ((7, 8, 8), 2), ((3, 6, 10), 2), ((2, 5, 7), 2), ((2, 12, 18), 2), ((2, 17, 6), 2), ((2, 6, 38), 2),
     ((700, 4, 4), 2), ((1, 1, 16), 2), ((2, 16, 1), 2), ((2, 3, 3), 2), ((300, 32, 32), 2), ((5, 64, 64), 2),
@@ -294,3 +293,36 @@ def test_column_split_output_matches_plain_rows(capi, W):
     plan.exec(x, out2)
     torch.cuda.synchronize()
     assert torch.equal(out2, plain)
+
+
+@pytest.mark.parametrize("shape,nd,off_floats", [((300, 90, 180), 2, 1), ((300, 90, 180), 2, 2), ((40, 128, 128), 2, 1),
+                                                  ((1300, 1440), 1, 1), ((1300, 1440), 1, 2), ((2, 720, 1440), 2, 2)])
+def test_specialised_shapes_with_unaligned_buffers(capi, shape, nd, off_floats):
+    """The shape-specialised kernels move whole images with 16-byte bulk copies; buffers that are only 4- or
+    8-byte aligned (a view into a larger tensor) must take another kernel and still give the same transform."""
+    torch.manual_seed(2)
+    n = 1
+    for s in shape:
+        n *= s
+    base = torch.randn(n + off_floats)
+    x = base[off_floats:].view(*shape)
+    xd = base.cuda()[off_floats:].view(*shape)
+    batch, dims = 1, shape[-nd:]
+    for s in shape[:-nd]:
+        batch *= s
+    oshape = shape[:-1] + (shape[-1] // 2 + 1, 2)
+    obase = torch.full((n // shape[-1] * oshape[-2] * 2 + 2,), float("nan"), device="cuda")
+    out = obase[2:].view(*oshape)                               # complex side: 8-byte aligned, not 16
+    f = capi.Plan(capi.FORWARD, dims, batch)
+    ws = torch.empty(max(f.workspace_bytes, 16), dtype=torch.uint8, device="cuda")
+    f.exec_ptr(xd.data_ptr(), out.data_ptr(), ws.data_ptr())
+    torch.cuda.synchronize()
+    want = O.torch_rfftn(x.contiguous(), nd, dtype=torch.float64).numpy()
+    assert O.rel_l2(out.cpu().numpy(), want) <= FWD_TOL
+    if off_floats % 2 == 0:                                     # real output rows are written as float2 pairs
+        i = capi.Plan(capi.INVERSE, dims, batch)
+        ws = torch.empty(max(i.workspace_bytes, 16), dtype=torch.uint8, device="cuda")
+        back = torch.full((n + off_floats,), float("nan"), device="cuda")
+        i.exec_ptr(out.data_ptr(), back[off_floats:].data_ptr(), ws.data_ptr())
+        torch.cuda.synchronize()
+        assert O.rel_l2(back[off_floats:].view(*shape).cpu().numpy(), x.numpy()) <= RT_TOL
