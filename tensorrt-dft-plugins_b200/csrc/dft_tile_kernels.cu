@@ -67,7 +67,7 @@ struct CtaCtx {
 };
 
 template <int MODE, int NT>
-__global__ void __launch_bounds__(NT, NT == 512 ? 2 : 1) tile_kernel(const __grid_constant__ KParams p, const float* __restrict__ in,
+__global__ void __launch_bounds__(NT, NT == 512 ? 2 : 3) tile_kernel(const __grid_constant__ KParams p, const float* __restrict__ in,
                                                               float* __restrict__ out)
 {
     extern __shared__ __align__(128) unsigned char smem_raw[];
