@@ -42,7 +42,10 @@ def build(force=False, verbose=False):
     cu, deps = sources()
     if not force and OUT.exists() and all(OUT.stat().st_mtime >= d.stat().st_mtime for d in deps + [Path(__file__)]):
         return OUT
-    cmd = ["nvcc"] + NVCC_FLAGS + ["-I", tensorrt_include()] + (["-Xptxas", "-v"] if verbose else []) + ["-o", str(OUT)] + [str(c) for c in cu]
+    trt_inc = tensorrt_include()
+    print(f"[build] plugin shell compiled against {trt_inc}/NvInfer.h"
+          + (" (STAND-IN: creators register with the test double only)" if "trt_min" in trt_inc else ""), file=sys.stderr)
+    cmd = ["nvcc"] + NVCC_FLAGS + ["-I", trt_inc] + (["-Xptxas", "-v"] if verbose else []) + ["-o", str(OUT)] + [str(c) for c in cu]
     if verbose:
         print(" ".join(cmd))
     subprocess.check_call(cmd)

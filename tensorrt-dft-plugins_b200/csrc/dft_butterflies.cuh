@@ -2,7 +2,7 @@
 //
 // Every index is a compile-time constant (static_for + integral constants), so a float2 v[R]
 // lives entirely in registers and every internal twiddle is an immediate.  Radices: the
-// primes 2,3,5,7,11,13 (symmetric half-sum form); 6,10,12,15 by a twiddle-free Good-Thomas
+// primes 2,3,5,7,11,13,17,19,23,29,31 (symmetric half-sum form); 6,10,12,15 by a twiddle-free Good-Thomas
 // prime-factor split; 8,9,16 by one Cooley-Tukey split with constant twiddles.  The inverse transform never needs its own
 // butterflies: IDFT(x)[n] = DFT(x)[(N-n) mod N], and the index reversal is folded into the
 // permutation tables used when results are stored (see dft_planner.cpp).
@@ -256,7 +256,7 @@ DFT_HD void dft_reg(float2 (&v)[R])
         v[2] = csub(t0, t2);
         v[1] = cadd(t1, t3);
         v[3] = csub(t1, t3);
-    } else if constexpr (R == 3 || R == 5 || R == 7 || R == 11 || R == 13) {
+    } else if constexpr (R == 3 || R == 5 || R == 7 || R == 11 || R == 13 || R == 17 || R == 19 || R == 23 || R == 29 || R == 31) {
         dft_prime<R>(v);
     } else if constexpr (R == 6) {
         dft_pfa<2, 3>(v);

@@ -402,6 +402,14 @@ int trt_dft_exec(trt_dft_plan_t plan, const void* in, void* out, void* workspace
     if (!plan) return TRT_DFT_ERR_INVALID_ARG;
     if (plan->launches.empty()) return TRT_DFT_OK;
     if (!in || !out) return TRT_DFT_ERR_INVALID_ARG;
+    // the plan's tables live on the GPU it was created on: launching from another current device would
+    // hand that GPU's kernels pointers into this one's memory
+    int cur_dev = -1;
+    if (cudaGetDevice(&cur_dev) != cudaSuccess) {
+        cudaGetLastError();
+        return TRT_DFT_ERR_CUDA;
+    }
+    if (cur_dev != plan->device) return TRT_DFT_ERR_INVALID_ARG;
     // complex tensors need 8-byte alignment (float2 accesses), real tensors 4-byte
     const bool inv = plan->pd.direction == TRT_DFT_INVERSE;
     const uintptr_t cptr = (uintptr_t)(inv ? in : (const void*)out);
@@ -458,6 +466,11 @@ int trt_dft_exec_host(trt_dft_plan_t plan, const void* host_in, void* host_out)
     if (!plan) return TRT_DFT_ERR_INVALID_ARG;
     if (plan->launches.empty()) return TRT_DFT_OK;
     if (!host_in || !host_out) return TRT_DFT_ERR_INVALID_ARG;
+    int cur_dev = -1;
+    if (cudaGetDevice(&cur_dev) != cudaSuccess || cur_dev != plan->device) {
+        cudaGetLastError();
+        return TRT_DFT_ERR_INVALID_ARG;      // device buffers below must live on the plan's GPU
+    }
     std::lock_guard<std::mutex> lock(plan->host_mu);
     const size_t in_bytes = (size_t)plan->pd.in_floats * 4, out_bytes = (size_t)plan->pd.out_floats * 4;
     const int64_t batch = plan->pd.batch;
@@ -467,6 +480,8 @@ int trt_dft_exec_host(trt_dft_plan_t plan, const void* host_in, void* host_out)
         int nchunks = (in_bytes + out_bytes) >= ((size_t)64 << 20) ? 16 : 1;   // measured at cfg3: 4 -> 82, 8 -> 89, 16 -> 91, 32 -> 89 GB/s
         if (const char* e = getenv("TRT_DFT_HOST_CHUNKS")) nchunks = std::max(1, std::min(32, atoi(e)));   // tuning override
         if (nchunks > batch) nchunks = (int)batch;
+        // a c2c plan's `batch` (outer * inner) is not a contiguous leading dimension of [outer][n][inner]: one chunk
+        if (plan->c2c) nchunks = 1;
         plan->h_chunk = (batch + nchunks - 1) / nchunks;
         const int64_t tail = batch % plan->h_chunk;
         bool ok = cudaMalloc(&plan->h_in, in_bytes) == cudaSuccess && cudaMalloc(&plan->h_out, out_bytes) == cudaSuccess;
@@ -480,6 +495,24 @@ int trt_dft_exec_host(trt_dft_plan_t plan, const void* host_in, void* host_out)
         for (int i = 0; ok && i < 3; ++i) ok = cudaStreamCreateWithFlags(&plan->h_streams[i], cudaStreamNonBlocking) == cudaSuccess;
         for (int i = 0; ok && i < 64; ++i) ok = cudaEventCreateWithFlags(&plan->h_events[i], cudaEventDisableTiming) == cudaSuccess;
         if (!ok) {
+            // leave nothing half-built behind: the next call starts the set-up again from scratch
+            cudaGetLastError();
+            if (plan->h_sub) trt_dft_plan_destroy(plan->h_sub);
+            if (plan->h_sub_tail) trt_dft_plan_destroy(plan->h_sub_tail);
+            plan->h_sub = plan->h_sub_tail = nullptr;
+            for (cudaStream_t& st : plan->h_streams) {
+                if (st) cudaStreamDestroy(st);
+                st = nullptr;
+            }
+            for (cudaEvent_t& ev : plan->h_events) {
+                if (ev) cudaEventDestroy(ev);
+                ev = nullptr;
+            }
+            for (void** p : {&plan->h_in, &plan->h_out, &plan->h_ws}) {
+                if (*p) cudaFree(*p);
+                *p = nullptr;
+            }
+            plan->h_chunk = 0;
             cudaGetLastError();
             return TRT_DFT_ERR_ALLOC;
         }

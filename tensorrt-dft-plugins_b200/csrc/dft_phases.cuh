@@ -144,6 +144,11 @@ DFT_HD void fft_step_dispatch(int radix, float2* buf, int nlines, int pitch, int
         DFT_CASE(11)
         DFT_CASE(13)
         DFT_CASE(16)
+        DFT_CASE(17)
+        DFT_CASE(19)
+        DFT_CASE(23)
+        DFT_CASE(29)
+        DFT_CASE(31)
 #undef DFT_CASE
         default:
             break;

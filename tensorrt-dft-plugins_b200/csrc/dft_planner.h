@@ -48,7 +48,7 @@ struct PlanDesc {
 };
 
 // ---- radix schedule --------------------------------------------------------------------------
-static const int kRadices[] = {16, 13, 11, 10, 9, 8, 7, 6, 5, 4, 3, 2};
+static const int kRadices[] = {16, 13, 11, 10, 9, 8, 7, 6, 5, 4, 3, 2, 17, 19, 23, 29, 31};
 
 inline void factor_search(int n, int start, std::vector<int>& cur, std::vector<int>& best)
 {
@@ -75,7 +75,7 @@ inline void factor_search(int n, int start, std::vector<int>& cur, std::vector<i
 inline bool is_pow2(int n) { return n > 0 && (n & (n - 1)) == 0; }
 inline int phys_index(int p, bool pad) { return pad ? p + (p >> 4) + (p >> 8) : p; }
 
-// false when n has a prime factor outside {2,3,5,7,11,13} or needs too many steps.
+// false when n has a prime factor above 31 or needs too many steps.
 inline bool make_line_fft(int n, bool rows, LineFFT* f)
 {
     memset(f, 0, sizeof(*f));
@@ -83,7 +83,7 @@ inline bool make_line_fft(int n, bool rows, LineFFT* f)
     if (n < 1) return false;
     if (n == 1) return true;
     int m = n;
-    for (int p : {2, 3, 5, 7, 11, 13})
+    for (int p : {2, 3, 5, 7, 11, 13, 17, 19, 23, 29, 31})
         while (m % p == 0) m /= p;
     if (m != 1) return false;
     std::vector<int> cur, best;
@@ -535,9 +535,15 @@ inline int build_c2c_plan(PlanDesc* pd, int direction, int64_t n, int64_t outer,
         if (pd->launches.size() == before)   // n == 1 and nothing to do but copy / scale
             P.add_naive(MODE_NAIVE_COLS, outer * n * inner, 0, 1, inner, 1, direction == 1, BUF_IN, BUF_OUT, scale);
     } else {
-        P.add_naive(MODE_NAIVE_COLS, outer * n * inner, 0, (int)n, inner, (int)n, direction == 1, BUF_IN, BUF_OUT, scale);
+        // The naive kernel re-reads whole columns while other threads store results, so it must never run with
+        // src == dst.  `in` may equal `out` for this plan type: go through the workspace and copy back.
+        pd->ws_bytes = (size_t)outer * n * inner * 8;
+        P.add_naive(MODE_NAIVE_COLS, outer * n * inner, 0, (int)n, inner, (int)n, direction == 1, BUF_IN, BUF_WS, scale);
+        P.add_naive(MODE_NAIVE_COLS, outer * n * inner, 0, 1, inner, 1, direction == 1, BUF_WS, BUF_OUT, 1.0f);
     }
-    pd->description = pd->launches[0].name;
+    std::string d;
+    for (size_t i = 0; i < pd->launches.size(); ++i) d += (i ? " ; " : "") + pd->launches[i].name;
+    pd->description = d;
     return 0;
 }
 

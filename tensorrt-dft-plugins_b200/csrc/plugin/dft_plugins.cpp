@@ -9,9 +9,13 @@
 //   * enqueue is a few lines over trt_dft_exec -- no cuFFT, no cuBLAS, no separate scale pass;
 //   * nothing asserts: bad attributes / blobs make the creator return nullptr, failures in
 //     enqueue return non-zero;
-//   * plans are looked up from the descriptors passed to each call, so a clone() or a
-//     deserialised plugin works even before configurePlugin ran on that instance (the reference's
-//     clones are unusable until then, :73-83), and getWorkspaceSize is derived from its arguments.
+//   * plans live in one process-wide cache keyed by (op, signal_ndim, dims, batch, device), filled by
+//     configurePlugin (where the reference builds its cuFFT plan, :131-178).  A clone() or a
+//     deserialised plugin therefore finds the plan of the instance that was configured, and its first
+//     enqueue is a pure lookup (the reference's clones are unusable until configured, :73-83).  enqueue
+//     itself never allocates while the stream is being captured: a shape nobody configured is then an
+//     error instead of a cudaMalloc inside the capture;
+//   * getWorkspaceSize is derived from its arguments.
 //
 // Compiled against the real <NvInfer.h> when TENSORRT_INCLUDE_DIR is given to build.py; otherwise
 // against the stand-in trt_min/NvInfer.h (test aid -- see the warning in that file).
@@ -21,10 +25,14 @@
 #include <stdio.h>
 #include <string.h>
 
+#include <cuda_runtime_api.h>
+#include <dlfcn.h>
+
 #include <map>
 #include <mutex>
 #include <new>
 #include <string>
+#include <tuple>
 #include <vector>
 
 #include "../../../include/trt_dft.h"
@@ -62,13 +70,53 @@ bool split_dims(Dims const& d, int32_t signal_ndim, int64_t* batch, int64_t out[
     return true;
 }
 
+// Fixed-size key of one plan: no heap traffic on the enqueue path.
+struct PlanKey {
+    int32_t direction, signal_ndim, device;
+    int64_t batch, d0, d1, d2;
+    auto tie() const { return std::tie(direction, signal_ndim, device, batch, d0, d1, d2); }
+    bool operator<(PlanKey const& o) const { return tie() < o.tie(); }
+    bool operator==(PlanKey const& o) const { return tie() == o.tie(); }
+};
+
+// Process-wide plan cache.  Plans are immutable once built and usable from any stream, so every plugin
+// instance (configured original, builder clone, deserialised runtime copy, per-context clone) shares them.
+// Entries stay until the process exits: a plan is a few KB of tables, and a handle that enqueue may be using
+// on another thread must not disappear under it.
+class PlanCache {
+public:
+    static PlanCache& get()
+    {
+        static PlanCache* c = new PlanCache();     // never destroyed: outlives the CUDA runtime's own teardown
+        return *c;
+    }
+    // may_create = false: lookup only (enqueue during stream capture)
+    trt_dft_plan_t find_or_create(PlanKey const& k, bool may_create) noexcept
+    {
+        std::lock_guard<std::mutex> lock(mu_);
+        try {
+            auto it = plans_.find(k);
+            if (it != plans_.end()) return it->second;
+            if (!may_create) return nullptr;
+            int64_t dims[3] = {k.d0, k.d1, k.d2};
+            trt_dft_plan_t p = nullptr;
+            if (trt_dft_plan_create(&p, k.direction, k.signal_ndim, dims, k.batch) != TRT_DFT_OK) return nullptr;
+            plans_[k] = p;
+            return p;
+        } catch (...) {
+            return nullptr;
+        }
+    }
+
+private:
+    std::mutex mu_;
+    std::map<PlanKey, trt_dft_plan_t> plans_;
+};
+
 class DftPlugin final : public IPluginV2DynamicExt {
 public:
     DftPlugin(Op op, Attributes a) : op_(op), attrs_(a) {}
-    ~DftPlugin() noexcept override
-    {
-        for (auto& kv : plans_) trt_dft_plan_destroy(kv.second);
-    }
+    ~DftPlugin() noexcept override = default;
 
     // --- identity ---------------------------------------------------------------------------------
     AsciiChar const* getPluginType() const noexcept override { return op_name(op_); }
@@ -125,7 +173,10 @@ public:
     IPluginV2DynamicExt* clone() const noexcept override
     {
         DftPlugin* p = new (std::nothrow) DftPlugin(op_, attrs_);
-        if (p) p->ns_ = ns_;
+        if (p) {
+            p->ns_ = ns_;
+            p->dynamic_ = dynamic_;
+        }
         return p;
     }
 
@@ -135,7 +186,18 @@ public:
         // Build the plan for the configured shape now, so that enqueue only launches.
         if (nbInputs != 1 || nbOutputs != 1 || !in || !out) return;
         if (in[0].desc.type != DataType::kFLOAT || out[0].desc.type != DataType::kFLOAT) return;
-        (void)plan_for(in[0].desc, out[0].desc);
+        // With a dynamic-shape profile (min != max) build the plans of the profile's corner shapes as well, so
+        // that those shapes never allocate in enqueue; shapes in between are planned on first use.
+        dynamic_ = false;
+        Dims const& smin = op_ == Op::kRfft ? in[0].min : out[0].min;
+        Dims const& smax = op_ == Op::kRfft ? in[0].max : out[0].max;
+        if (smin.nbDims == smax.nbDims)
+            for (int32_t i = 0; i < smin.nbDims; ++i) dynamic_ = dynamic_ || smin.d[i] != smax.d[i];
+        (void)plan_for(signal_desc(in[0].desc, out[0].desc).dims, /*may_create=*/true);
+        if (dynamic_) {
+            (void)plan_for(smin, true);
+            (void)plan_for(smax, true);
+        }
     }
 
     size_t getWorkspaceSize(PluginTensorDesc const* inputs, int32_t nbInputs, PluginTensorDesc const* outputs,
@@ -144,15 +206,38 @@ public:
         if (nbInputs != 1 || nbOutputs != 1 || !inputs || !outputs) return 0;
         int64_t batch = 0, dims[3] = {1, 1, 1};
         if (!split_dims(signal_desc(inputs[0], outputs[0]).dims, attrs_.signal_ndim, &batch, dims)) return 0;
-        return trt_dft_query_workspace_bytes(direction(), attrs_.signal_ndim, dims, batch);   // host-only arithmetic
+        size_t need = trt_dft_query_workspace_bytes(direction(), attrs_.signal_ndim, dims, batch);   // host-only arithmetic
+        if (dynamic_) {
+            // TensorRT asks for the profile's largest shape only, but a smaller shape may pick another kind of
+            // plan (fused kernels need nothing, un-fused inverses one complex tensor, lengths outside the radix
+            // set two).  Two complex tensors of the largest shape bound every plan of every smaller shape.
+            int64_t cplx = batch * 8;
+            for (int32_t i = 0; i < attrs_.signal_ndim; ++i) cplx *= (i == attrs_.signal_ndim - 1) ? dims[i] / 2 + 1 : dims[i];
+            const size_t bound = 2 * (((size_t)cplx + 255) / 256 * 256);
+            if (bound > need) need = bound;
+        }
+        return need;
     }
 
     int32_t enqueue(PluginTensorDesc const* inputDesc, PluginTensorDesc const* outputDesc, void const* const* inputs,
                     void* const* outputs, void* workspace, cudaStream_t stream) noexcept override
     {
         if (!inputDesc || !outputDesc || !inputs || !outputs) return 1;
-        trt_dft_plan_t plan = plan_for(inputDesc[0], outputDesc[0]);
-        if (!plan) return 1;
+        Dims const& sd = signal_desc(inputDesc[0], outputDesc[0]).dims;
+        trt_dft_plan_t plan = plan_for(sd, /*may_create=*/false);       // the normal case: a lookup, nothing else
+        if (!plan) {
+            // A shape no instance was configured for (dynamic shapes between the profile's corners).  Building a
+            // plan allocates and copies tables, which is not allowed inside a stream capture: refuse there.
+            cudaStreamCaptureStatus cs = cudaStreamCaptureStatusNone;
+            if (cudaStreamIsCapturing(stream, &cs) != cudaSuccess || cs != cudaStreamCaptureStatusNone) {
+                cudaGetLastError();
+                fprintf(stderr, "[trt_dft_plugins] %s enqueue: no plan for this shape and the stream is being captured; "
+                                "run the shape once outside the capture (or configure it) first\n", op_name(op_));
+                return 1;
+            }
+            plan = plan_for(sd, /*may_create=*/true);
+            if (!plan) return 1;
+        }
         return trt_dft_exec(plan, inputs[0], outputs[0], workspace, stream) == TRT_DFT_OK ? 0 : 1;
     }
 
@@ -171,29 +256,33 @@ private:
         return op_ == Op::kRfft ? in : out;
     }
 
-    trt_dft_plan_t plan_for(PluginTensorDesc const& in, PluginTensorDesc const& out) noexcept
+    // signal dims -> plan.  The instance remembers the last plan it used (TensorRT drives one instance from one
+    // thread at a time), so a steady-state enqueue touches neither the shared cache nor its mutex.
+    trt_dft_plan_t plan_for(Dims const& signal_dims, bool may_create) noexcept
     {
         int64_t batch = 0, dims[3] = {1, 1, 1};
-        if (!split_dims(signal_desc(in, out).dims, attrs_.signal_ndim, &batch, dims)) return nullptr;
-        std::vector<int64_t> key{batch, dims[0], dims[1], dims[2]};
-        std::lock_guard<std::mutex> lock(mu_);
-        try {
-            auto it = plans_.find(key);
-            if (it != plans_.end()) return it->second;
-            trt_dft_plan_t p = nullptr;
-            if (trt_dft_plan_create(&p, direction(), attrs_.signal_ndim, dims, batch) != TRT_DFT_OK) return nullptr;
-            plans_[key] = p;
-            return p;
-        } catch (...) {
+        if (!split_dims(signal_dims, attrs_.signal_ndim, &batch, dims)) return nullptr;
+        int dev = 0;
+        if (cudaGetDevice(&dev) != cudaSuccess) {
+            cudaGetLastError();
             return nullptr;
         }
+        const PlanKey key{direction(), attrs_.signal_ndim, dev, batch, dims[0], dims[1], dims[2]};
+        if (last_plan_ && key == last_key_) return last_plan_;
+        trt_dft_plan_t p = PlanCache::get().find_or_create(key, may_create);
+        if (p) {
+            last_key_ = key;
+            last_plan_ = p;
+        }
+        return p;
     }
 
     Op op_;
     Attributes attrs_;
     std::string ns_;
-    std::mutex mu_;
-    std::map<std::vector<int64_t>, trt_dft_plan_t> plans_;
+    bool dynamic_ = false;              // configured with a dynamic-shape profile (min != max)
+    PlanKey last_key_{};
+    trt_dft_plan_t last_plan_ = nullptr;
 };
 
 class DftPluginCreator final : public IPluginCreator {
@@ -278,12 +367,34 @@ DftPluginCreator& irfft_creator()
 extern "C" nvinfer1::IPluginRegistry* getPluginRegistry() noexcept __attribute__((weak));
 
 namespace {
+// A library compiled against the stand-in header (no TensorRT at build time) has plugin classes whose
+// virtual-table layout was never checked against a real libnvinfer.  Handing such objects to a real
+// TensorRT would crash or misdispatch, so in that build the creators are only given to a host that
+// identifies itself as the test double (tests/mock_trt exports `trt_dft_mock_host`).
+bool host_may_have_creators()
+{
+#if defined(TRT_MIN_STAND_IN)
+    if (dlsym(RTLD_DEFAULT, "trt_dft_mock_host") != nullptr) return true;
+    static bool warned = false;
+    if (!warned && getPluginRegistry) {
+        warned = true;
+        fprintf(stderr,
+                "[trt_dft_plugins] this libtrt_dft_plugins.so was built WITHOUT TensorRT headers (stand-in NvInfer.h); "
+                "the Rfft / Irfft creators are not registered.  Rebuild with TENSORRT_INCLUDE_DIR=<dir with NvInfer.h>.\n");
+    }
+    return false;
+#else
+    return true;
+#endif
+}
+
 // Load-time registration, the behaviour the reference gets from its two static PluginRegistrar
 // objects (:575-576): after dlopen, "Rfft" and "Irfft" are in the global registry under namespace "".
 struct RegisterAtLoad {
     RegisterAtLoad()
     {
         if (!getPluginRegistry) return;
+        if (!host_may_have_creators()) return;
         nvinfer1::IPluginRegistry* reg = getPluginRegistry();
         if (!reg) return;
         reg->registerCreator(trt_dft::rfft_creator(), "");
@@ -297,7 +408,7 @@ struct RegisterAtLoad {
 extern "C" __attribute__((visibility("default"))) nvinfer1::IPluginCreator* const* getPluginCreators(int32_t& nbCreators)
 {
     static nvinfer1::IPluginCreator* const creators[2] = {&trt_dft::rfft_creator(), &trt_dft::irfft_creator()};
-    nbCreators = 2;
+    nbCreators = host_may_have_creators() ? 2 : 0;
     return creators;
 }
 extern "C" __attribute__((visibility("default"))) void setLoggerFinder(void*) {}

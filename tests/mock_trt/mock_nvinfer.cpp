@@ -127,6 +127,9 @@ bool infer(IPluginV2DynamicExt* p, Dims const& in, Dims* out)
 }  // namespace
 
 extern "C" nvinfer1::IPluginRegistry* getPluginRegistry() noexcept { return &g_registry; }
+// Marks this process's "TensorRT" as the test double: a plugin library built against the stand-in header
+// registers its creators only when it finds this symbol (see RegisterAtLoad in csrc/plugin/dft_plugins.cpp).
+extern "C" int trt_dft_mock_host = 1;
 
 extern "C" {
 
@@ -282,6 +285,80 @@ int mock_lifecycle(const char* op, int32_t nd, int32_t nb_in, const int32_t* in_
     ctx->destroy();
     rt->destroy();
     return rc == 0 ? 0 : 7;
+}
+
+// getWorkspaceSize after a dynamic-shape configurePlugin (profile min != max); asked, as TensorRT does, about the
+// profile's largest shape.
+size_t mock_dynamic_workspace(const char* op, int32_t nd, int32_t nb_in, const int32_t* min_dims, const int32_t* max_dims)
+{
+    IPluginV2DynamicExt* p = create(op, 0, 1, nd);
+    if (!p) return (size_t)-1;
+    Dims imin = make_dims(nb_in, min_dims), imax = make_dims(nb_in, max_dims), omin{}, omax{};
+    infer(p, imin, &omin);
+    infer(p, imax, &omax);
+    PluginTensorDesc di{imax, DataType::kFLOAT, TensorFormat::kLINEAR, 1.f}, dox{omax, DataType::kFLOAT, TensorFormat::kLINEAR, 1.f};
+    DynamicPluginTensorDesc din{di, imin, imax}, dout{dox, omin, omax};
+    p->configurePlugin(&din, 1, &dout, 1);
+    const size_t w = p->getWorkspaceSize(&di, 1, &dox, 1);
+    p->destroy();
+    return w;
+}
+
+// What TensorRT does with CUDA graphs: the plugin that was configured (and timed) is one instance, the
+// execution context enqueues a clone that never saw configurePlugin, inside a stream capture.  The clone's
+// enqueue must then be launch-only (no allocation, no synchronisation), or the capture fails.
+// Steps: configure + one ordinary enqueue on the original; clone; capture clone->enqueue; also ask the clone
+// for a shape nobody configured while capturing (must return non-zero WITHOUT breaking the capture);
+// instantiate, launch the graph `replays` times.  Returns 0, or a step number on failure.
+int mock_capture_clone(const char* op, int32_t nd, int32_t nb_in, const int32_t* in_dims, const void* d_in, void* d_out,
+                       int32_t replays)
+{
+    IPluginV2DynamicExt* orig = create(op, 0, 1, nd);
+    if (!orig) return 1;
+    Dims in = make_dims(nb_in, in_dims), out{};
+    if (!infer(orig, in, &out)) return 2;
+    PluginTensorDesc io[2] = {{in, DataType::kFLOAT, TensorFormat::kLINEAR, 1.f}, {out, DataType::kFLOAT, TensorFormat::kLINEAR, 1.f}};
+    DynamicPluginTensorDesc din{io[0], in, in}, dout{io[1], out, out};
+    orig->configurePlugin(&din, 1, &dout, 1);
+    const size_t ws_bytes = orig->getWorkspaceSize(&io[0], 1, &io[1], 1);
+    void* ws = nullptr;
+    if (ws_bytes && cudaMalloc(&ws, ws_bytes) != cudaSuccess) return 3;
+    cudaStream_t st = nullptr;
+    if (cudaStreamCreateWithFlags(&st, cudaStreamNonBlocking) != cudaSuccess) return 4;
+    void const* ins[1] = {d_in};
+    void* outs[1] = {d_out};
+    int rc = 0;
+    if (orig->enqueue(&io[0], &io[1], ins, outs, ws, st) != 0) rc = 5;       // the builder's timing run
+    cudaStreamSynchronize(st);
+    IPluginV2DynamicExt* ctx = orig->clone();                                // never configured
+    if (!ctx) rc = rc ? rc : 6;
+    cudaGraph_t graph = nullptr;
+    cudaGraphExec_t exec = nullptr;
+    if (!rc && cudaStreamBeginCapture(st, cudaStreamCaptureModeThreadLocal) != cudaSuccess) rc = 7;
+    if (!rc) {
+        if (ctx->enqueue(&io[0], &io[1], ins, outs, ws, st) != 0) rc = 8;
+        // a shape no instance has a plan for: must be refused, and the capture must survive it
+        int32_t odd[8];
+        for (int32_t i = 0; i < nb_in; ++i) odd[i] = in_dims[i];
+        odd[0] += 3;
+        Dims in2 = make_dims(nb_in, odd), out2{};
+        infer(ctx, in2, &out2);
+        PluginTensorDesc io2[2] = {{in2, DataType::kFLOAT, TensorFormat::kLINEAR, 1.f}, {out2, DataType::kFLOAT, TensorFormat::kLINEAR, 1.f}};
+        if (ctx->enqueue(&io2[0], &io2[1], ins, outs, ws, st) == 0) rc = rc ? rc : 9;
+        if (cudaStreamEndCapture(st, &graph) != cudaSuccess || !graph) rc = rc ? rc : 10;
+    }
+    if (!rc && cudaGraphInstantiate(&exec, graph, 0) != cudaSuccess) rc = 11;
+    for (int32_t i = 0; !rc && i < replays; ++i)
+        if (cudaGraphLaunch(exec, st) != cudaSuccess) rc = 12;
+    if (cudaStreamSynchronize(st) != cudaSuccess) rc = rc ? rc : 13;
+    if (exec) cudaGraphExecDestroy(exec);
+    if (graph) cudaGraphDestroy(graph);
+    cudaGetLastError();
+    if (ctx) ctx->destroy();
+    orig->destroy();
+    cudaStreamDestroy(st);
+    if (ws) cudaFree(ws);
+    return rc;
 }
 
 }  // extern "C"

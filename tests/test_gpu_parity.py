@@ -326,3 +326,135 @@ def test_specialised_shapes_with_unaligned_buffers(capi, shape, nd, off_floats):
         i.exec_ptr(out.data_ptr(), back[off_floats:].data_ptr(), ws.data_ptr())
         torch.cuda.synchronize()
         assert O.rel_l2(back[off_floats:].view(*shape).cpu().numpy(), x.numpy()) <= RT_TOL
+
+
+# ---- BASELINE configs 4 and 5 at sizes that cross the 32-bit boundaries -------------------------------------
+def _check_images(got_dev, want_fn, which, tol):
+    for b in which:
+        want = want_fn(b)
+        err = O.rel_l2(got_dev[b].cpu().numpy(), want.numpy())
+        assert err <= tol, f"image {b}: rel-L2 {err:.3e}"
+
+
+def test_cfg4_shape_with_offsets_beyond_2_31_bytes(capi):
+    """BASELINE config 4's image size (720 x 1440) at a batch whose last images start beyond 2^31 BYTES and beyond
+    2^31 ELEMENTS/4 of both tensors (600 images: 2.49 GB per side; SURVEY Q12 -- the reference's batch is an
+    int32).  First, a middle and the LAST image are checked against fp64 torch.fft in both directions; the rest is
+    covered by a checksum identity (sum over the batch of the transforms = transform of the sum, linearity)."""
+    n, H, W = 600, 720, 1440
+    g = torch.Generator(device="cuda").manual_seed(4)
+    x = torch.randn(n, H, W, device="cuda", generator=g)
+    assert x.numel() * 4 > 2**31 and (n - 1) * H * W * 4 > 2**31
+    f = capi.Plan(capi.FORWARD, (H, W), n)
+    y = torch.full((n, H, W // 2 + 1, 2), float("nan"), device="cuda")
+    wsf = torch.empty(max(f.workspace_bytes, 16), dtype=torch.uint8, device="cuda")
+    f.exec(x, y, workspace=wsf)
+    torch.cuda.synchronize()
+    which = (0, 1, n // 2, n - 2, n - 1)
+    _check_images(y, lambda b: O.torch_rfftn(x[b].cpu(), 2, dtype=torch.float64), which, FWD_TOL)
+    assert not torch.isnan(y).any()
+    # linearity over the whole batch: catches any image that was skipped, duplicated or misplaced
+    ysum = y.double().sum(dim=0)
+    fsum = capi.rfftn(x.double().sum(dim=0).float().unsqueeze(0), 2)[0].double()
+    assert ((ysum - fsum).norm() / fsum.norm()).item() <= 1e-5
+    del ysum, fsum, wsf
+    i = capi.Plan(capi.INVERSE, (H, W), n)
+    ws = torch.empty(max(i.workspace_bytes, 16), dtype=torch.uint8, device="cuda")
+    xr = torch.full((n, H, W), float("nan"), device="cuda")
+    y_before = y[n - 1].clone()
+    i.exec(y, xr, workspace=ws)
+    torch.cuda.synchronize()
+    assert torch.equal(y[n - 1], y_before)                           # input never written (dft_plugins.cpp:193)
+    _check_images(xr, lambda b: O.torch_irfftn(y[b].cpu(), 2, dtype=torch.float64), which, FWD_TOL)
+    per_img = (xr - x).flatten(1).double().norm(dim=1) / x.flatten(1).double().norm(dim=1)
+    assert float(per_img.max()) <= RT_TOL, f"worst image {int(per_img.argmax())}"
+    del x, y, xr, ws
+    torch.cuda.empty_cache()
+
+
+def test_cfg5_full_size_both_directions(capi):
+    """BASELINE config 5 on one GPU, [4, 8192, 8192]: every image's round trip, one image (the last) in full
+    against fp64 torch.fft in both directions."""
+    B, H, W = 4, 8192, 8192
+    g = torch.Generator(device="cuda").manual_seed(5)
+    x = torch.randn(B, H, W, device="cuda", generator=g)
+    f = capi.Plan(capi.FORWARD, (H, W), B)
+    i = capi.Plan(capi.INVERSE, (H, W), B)
+    ws = torch.empty(max(f.workspace_bytes, i.workspace_bytes, 16), dtype=torch.uint8, device="cuda")
+    y = torch.full((B, H, W // 2 + 1, 2), float("nan"), device="cuda")
+    f.exec(x, y, workspace=ws)
+    torch.cuda.synchronize()
+    want = O.torch_rfftn(x[B - 1].cpu(), 2, dtype=torch.float64)
+    assert O.rel_l2(y[B - 1].cpu().numpy(), want.numpy()) <= FWD_TOL
+    assert not torch.isnan(y).any()
+    xr = torch.full((B, H, W), float("nan"), device="cuda")
+    i.exec(y, xr, workspace=ws)
+    torch.cuda.synchronize()
+    want_x = O.torch_irfftn(y[B - 1].cpu(), 2, dtype=torch.float64)
+    assert O.rel_l2(xr[B - 1].cpu().numpy(), want_x.numpy()) <= FWD_TOL
+    per_img = (xr - x).flatten(1).double().norm(dim=1) / x.flatten(1).double().norm(dim=1)
+    assert float(per_img.max()) <= RT_TOL, f"worst image {int(per_img.argmax())}"
+    del x, y, xr, ws
+    torch.cuda.empty_cache()
+
+
+def test_reference_irfft2_cases_at_the_reference_defaults(capi):
+    """tests/test_dft.py:184 asserts torch.allclose at the defaults (rtol 1e-5, atol 1e-8).  fp32 cannot promise an
+    absolute 1e-8 on elements that cancel to ~0 (the CPU oracle itself is only reproducible to ~1e-7 there), so
+    the parametrised test above states atol 1e-6.  This one records how the 8 cases fare at the defaults, and every
+    element that misses them must be off by less than 1e-6 absolute (a few fp32 ulps of the O(1) intermediates)."""
+    passed = 0
+    for name in REF:
+        y = torch.from_numpy(GOLD[name + "_rfft2"])
+        x = capi.irfftn(y.cuda(), 2).cpu()
+        want = torch.from_numpy(GOLD[name + "_irfft2"])
+        ok = torch.isclose(want, x)                                  # the reference's own criterion
+        passed += int(bool(ok.all()))
+        bad = ~ok
+        assert ((want - x)[bad].abs() < 1e-6).all(), name
+    print(f"irfft2 reference cases passing torch.allclose defaults: {passed} of {len(REF)}")
+
+
+def test_in_place_c2c_on_a_length_outside_the_radix_set(capi):
+    """Lengths with a prime factor above 31 run the naive column kernel, which must not run in place: the plan goes
+    through its workspace instead (many blocks, so a race would show)."""
+    torch.manual_seed(7)
+    outer, n, inner = 4, 74, 4000                                    # 74 = 2 * 37
+    z = torch.randn(outer, n, inner, 2)
+    want = torch.view_as_real(torch.fft.fft(torch.view_as_complex(z.double()), dim=1))
+    plan = capi.C2CPlan(capi.FORWARD, n, outer, inner)
+    assert plan.workspace_bytes == outer * n * inner * 8
+    zd = z.cuda()
+    plan.exec(zd, zd)
+    torch.cuda.synchronize()
+    assert O.rel_l2(zd.cpu().numpy(), want.numpy()) <= FWD_TOL
+    # the strided 8192-point axis (four-step) also needs its workspace: NULL must be refused, not dereferenced
+    p2 = capi.C2CPlan(capi.FORWARD, 8192, 1, 12)
+    assert p2.workspace_bytes > 0
+    w = torch.zeros(8192 * 12 * 2, device="cuda")
+    with pytest.raises(capi.DftError):
+        p2.exec_ptr(w.data_ptr(), w.data_ptr(), 0)
+
+
+def test_exec_host_with_a_c2c_plan(capi):
+    """trt_dft_exec_host on a c2c plan large enough for the chunked host pipeline (>= 64 MiB): the batch of a c2c plan
+    is not a contiguous leading dimension, so it must run as one piece."""
+    torch.manual_seed(8)
+    outer, n, inner = 3, 720, 2100                                   # 2 x 36 MB
+    z = torch.randn(outer, n, inner, 2)
+    out = torch.empty_like(z)
+    plan = capi.C2CPlan(capi.FORWARD, n, outer, inner)
+    plan.exec_host(z, out)
+    want = torch.view_as_real(torch.fft.fft(torch.view_as_complex(z[1].double()), dim=0))
+    assert O.rel_l2(out[1].numpy(), want.numpy()) <= FWD_TOL
+
+
+def test_exec_refuses_a_plan_from_another_device(capi):
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs two GPUs")
+    p = capi.Plan(capi.FORWARD, (90, 180), 2)                        # built on device 0
+    with torch.cuda.device(1):
+        x = torch.zeros(2, 90, 180, device="cuda:1")
+        y = torch.zeros(2, 90, 91, 2, device="cuda:1")
+        with pytest.raises(capi.DftError):
+            p.exec_ptr(x.data_ptr(), y.data_ptr())

@@ -42,6 +42,7 @@ def mock():
     m.mock_workspace_size.restype = c_size_t
     m.mock_lifecycle.argtypes = [c_char_p, c_int32, c_int32, ctypes.POINTER(c_int32), c_void_p, c_void_p, c_void_p,
                                  c_int, ctypes.POINTER(c_int32), ctypes.POINTER(c_int32)]
+    m.mock_capture_clone.argtypes = [c_char_p, c_int32, c_int32, ctypes.POINTER(c_int32), c_void_p, c_void_p, c_int32]
     return m
 
 
@@ -213,3 +214,37 @@ def test_plugin_pair_at_baseline_shapes(mock, shape, nd, skip_configure):
     assert O.rel_l2(y.numpy(), want.numpy()) <= 1e-5
     xr = run_plugin(mock, b"Irfft", nd, y, skip_configure)
     assert O.rel_l2(xr.numpy(), x.numpy()) <= 1e-6
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("shape,nd", [((3, 5, 90, 180), 2), ((2, 180, 360), 2), ((6, 64), 1)])
+def test_unconfigured_clone_enqueues_inside_a_stream_capture(mock, shape, nd):
+    """The execution context's clone never sees configurePlugin (dft_plugins.cpp:73-83 makes such a clone unusable in
+    the reference; TensorRT configures it again).  Here the plan built when the ORIGINAL was configured
+    (dft_plugins.cpp:131-178 is where the reference builds its cuFFT plan) is shared, so the clone's first enqueue is
+    launch-only and can be captured in a CUDA graph; a shape nobody planned is refused inside the capture instead
+    of allocating there."""
+    from oracle import oracle as O
+    torch.manual_seed(1)
+    x = torch.randn(*shape)
+    want = O.torch_rfftn(x, nd, dtype=torch.float64)
+    for op, src, ref, tol in ((b"Rfft", x, want, 1e-5), (b"Irfft", want.float(), x, 1e-5)):
+        xd = src.cuda().contiguous()
+        y = torch.full(tuple(ref.shape), float("nan"), device="cuda")
+        rc = mock.mock_capture_clone(op, nd, xd.dim(), arr(tuple(xd.shape)), xd.data_ptr(), y.data_ptr(), 2)
+        assert rc == 0, f"step {rc}"
+        torch.cuda.synchronize()
+        assert O.rel_l2(y.cpu().numpy(), ref.numpy()) <= tol
+
+
+def test_dynamic_profile_workspace_bounds_every_smaller_shape(mock):
+    """A profile whose largest shape runs fused (no workspace) still has smaller shapes that need one (34 x 68 is
+    un-fused); once configured as dynamic, getWorkspaceSize returns a bound that covers them."""
+    m = mock
+    m.mock_dynamic_workspace.argtypes = [c_char_p, c_int32, c_int32, ctypes.POINTER(c_int32), ctypes.POINTER(c_int32)]
+    m.mock_dynamic_workspace.restype = c_size_t
+    lo, hi = (1, 2, 3, 2), (4, 128, 65, 2)
+    static_need = m.mock_workspace_size(b"Irfft", 2, 4, arr(hi))
+    dyn_need = m.mock_dynamic_workspace(b"Irfft", 2, 4, arr(lo), arr(hi))
+    assert static_need == 0                                   # fused at the largest shape
+    assert dyn_need >= 2 * 4 * 128 * 65 * 8                   # two complex tensors of the largest shape
