@@ -126,6 +126,182 @@ def time_cpu_pair(nimg_sample, repeats, threads):
     return best
 
 
+CONFIGS = {
+    "cfg1": ((4, 32, 64), 1), "cfg2": ((16, 64, 128, 128), 2), "cfg3": ((8, 768, 90, 180), 2),
+    "cfg4": ((64, 20, 720, 1440), 2), "cfg5": ((4, 8192, 8192), 2),
+}
+
+
+def algo_bytes(shape, nd):
+    """read the input once + write the output once, one direction."""
+    n = 1
+    for s in shape[:-1]:
+        n *= s
+    return n * shape[-1] * 4 + n * (shape[-1] // 2 + 1) * 8
+
+
+def time_config(capi, torch, name, iters, peak, batch_override=None):
+    """One BASELINE config through the C ABI on the current device: per-direction and pair times (CUDA events on
+    the launch stream, inputs resident in HBM), algorithmic GB/s, fraction of the measured peak, round trip."""
+    shape, nd = CONFIGS[name]
+    if batch_override is not None:
+        shape = (batch_override,) + shape[-nd:]
+    batch = 1
+    for s in shape[:-nd]:
+        batch *= s
+    dims = shape[-nd:]
+    g = torch.Generator(device="cuda").manual_seed(1)
+    x = torch.randn(*shape, device="cuda", generator=g)
+    y = torch.empty(shape[:-1] + (dims[-1] // 2 + 1, 2), device="cuda")
+    xr = torch.empty_like(x)
+    f = capi.Plan(capi.FORWARD, dims, batch)
+    i = capi.Plan(capi.INVERSE, dims, batch)
+    ws = torch.empty(max(f.workspace_bytes, i.workspace_bytes, 16), dtype=torch.uint8, device="cuda")
+    st = torch.cuda.current_stream().cuda_stream
+    fw = lambda: f.exec_ptr(x.data_ptr(), y.data_ptr(), ws.data_ptr(), st)
+    iv = lambda: i.exec_ptr(y.data_ptr(), xr.data_ptr(), ws.data_ptr(), st)
+    for _ in range(3):
+        fw(); iv()
+    torch.cuda.synchronize()
+    rt = ((xr - x).double().norm() / x.double().norm()).item()
+    small = x.numel() * 4 < (256 << 20)          # smaller than 2x L2: flush between timed launches is pointless at
+    res = {}                                     # these sizes (launch-bound); say so instead
+    for key, fn in (("fwd", fw), ("inv", iv), ("pair", lambda: (fw(), iv()))):
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(iters):
+            fn()
+        e1.record()
+        torch.cuda.synchronize()
+        res[key] = e0.elapsed_time(e1) / iters
+    ab = algo_bytes(shape, nd)
+    out = {"shape": list(shape), "fwd_ms": res["fwd"], "inv_ms": res["inv"], "pair_ms": res["pair"],
+           "fwd_GBs": ab / res["fwd"] / 1e6, "inv_GBs": ab / res["inv"] / 1e6, "pair_GBs": 2 * ab / res["pair"] / 1e6,
+           "frac_of_measured_peak": 2 * ab / res["pair"] / 1e6 / peak, "round_trip_rel_l2": rt, "iters": iters,
+           "algorithmic_bytes_per_direction": ab, "l2_resident": bool(small),
+           "launches": [f.num_launches, i.num_launches], "workspace_bytes": [f.workspace_bytes, i.workspace_bytes]}
+    del x, y, xr, ws, f, i
+    torch.cuda.empty_cache()
+    return out
+
+
+def cufft_sequence(torch, capi, names):
+    """The reference's own device path -- cufftXtMakePlanMany / cufftXtExec (+ cublasScalEx for the inverse), the calls
+    of dft_plugins.cpp:161-196, :454-468 -- timed by tools/cufft_ref_bench in a SUBPROCESS (comparator only: cuFFT is
+    never loaded into this process), plus one seeded cfg3-shaped batch pushed through both and compared."""
+    exe = ROOT / "tools" / "cufft_ref_bench"
+    if not exe.exists():
+        return {"unavailable": "tools/cufft_ref_bench not built"}
+    out = {}
+    for name in names:
+        shape, nd = CONFIGS[name]
+        batch = 1
+        for s in shape[:-nd]:
+            batch *= s
+        iters = 20 if name in ("cfg4", "cfg5") else 200
+        try:
+            r = subprocess.run([str(exe), str(iters), str(batch)] + [str(d) for d in shape[-nd:]], capture_output=True,
+                               text=True, timeout=180)
+            j = json.loads(r.stdout.strip().splitlines()[-1])
+            out[name] = {k: j[k] for k in ("fwd_ms", "inv_ms", "pair_ms", "pair_GBs", "ws_fwd", "ws_inv")}
+        except Exception as e:  # comparator trouble must not cost the headline line
+            out[name] = {"error": repr(e)[:200]}
+    # parity against the reference's actual arithmetic: 96 seeded images of 90 x 180
+    try:
+        import tempfile
+        import numpy as np
+        torch.manual_seed(1)
+        x = torch.randn(96, H, W)
+        with tempfile.TemporaryDirectory() as td:
+            fx, ff, fi = (os.path.join(td, n) for n in ("x.f32", "fwd.f32", "inv.f32"))
+            x.numpy().tofile(fx)
+            r = subprocess.run([str(exe), "check", fx, ff, fi, "96", str(H), str(W)], capture_output=True, text=True, timeout=120)
+            if r.returncode != 0:
+                raise RuntimeError(r.stderr[-200:])
+            yc = torch.from_numpy(np.fromfile(ff, dtype=np.float32)).view(96, H, MO, 2)
+            xc = torch.from_numpy(np.fromfile(fi, dtype=np.float32)).view(96, H, W)
+        yo = capi.rfftn(x.cuda(), 2).cpu()
+        xo = capi.irfftn(yc.cuda(), 2).cpu()           # same input as cuFFT's inverse saw
+        rel = lambda a, b: ((a.double() - b.double()).norm() / b.double().norm()).item()
+        out["parity_vs_cufft"] = {"sample": "[96,90,180] seed 1", "rfft2_rel_l2": rel(yo, yc), "irfft2_rel_l2": rel(xo, xc)}
+    except Exception as e:
+        out["parity_vs_cufft"] = {"error": repr(e)[:200]}
+    return out
+
+
+def cfg4_shard(capi, torch, dist, world, rank, dev, peak):
+    """BASELINE config 4, [64,20,720,1440], batch-sharded: each rank transforms 1280/N images (strong scaling of the
+    config's fixed total; no data-path collective).  Device-timed, max over ranks."""
+    nimg = 1280 // world
+    r = time_config(capi, torch, "cfg4", 5, peak, batch_override=nimg)
+    t = torch.tensor([r["fwd_ms"], r["inv_ms"], r["pair_ms"], r["round_trip_rel_l2"]], device=dev, dtype=torch.float64)
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ab = algo_bytes((1280, 720, 1440), 2)
+    return {"images_per_rank": nimg, "fwd_ms": t[0].item(), "inv_ms": t[1].item(), "pair_ms": t[2].item(),
+            "aggregate_pair_GBs": 2 * ab / t[2].item() / 1e6, "round_trip_rel_l2_max": t[3].item(), "scaling": "strong"}
+
+
+def pencil_bench(torch, dist, world, rank, dev, iters=10):
+    """BASELINE config 5, pencil-decomposed rfft2 of [4,8192,8192] over N GPUs: forward with the exchange fused into
+    the row kernel (stores to peer memory), the NCCL all-to-all variant beside it, the inverse, and the parity of this
+    rank's column band against a single-GPU transform of the same images."""
+    from trt_dft_plugins import capi
+    from trt_dft_plugins.pencil import PencilRfft2
+    B, Hh, Ww = 4, 8192, 8192
+    g = torch.Generator(device=dev).manual_seed(5)                  # same images on every rank, then slice
+    x_full = torch.randn(B, Hh, Ww, device=dev, generator=g)
+    p = PencilRfft2(B, Hh, Ww, device=dev)
+    x_loc = x_full[:, p.h0:p.h0 + p.hn].contiguous()
+    ref = capi.rfftn(x_full, 2)[:, :, p.c0:p.c0 + p.cn].contiguous()
+    del x_full
+    torch.cuda.empty_cache()
+
+    def timed(fn, n):
+        fn()
+        dist.barrier()
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(n):
+            fn()
+        e1.record()
+        torch.cuda.synchronize()
+        t = torch.tensor([e0.elapsed_time(e1) / n], device=dev, dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return t.item()
+
+    out = {"shape": [B, Hh, Ww]}
+    y = p.forward(x_loc)
+    torch.cuda.synchronize()
+    out["exchange"] = p.exchange_used
+    if getattr(p, "_peer_error", None):
+        out["peer_unavailable"] = p._peer_error
+    err = ((y - ref).double().norm() / ref.double().norm())
+    xb = p.inverse(y)
+    torch.cuda.synchronize()
+    err_rt = ((xb - x_loc).double().norm() / x_loc.double().norm())
+    t = torch.stack([err, err_rt])
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    out["rel_l2"], out["round_trip_rel_l2"] = t[0].item(), t[1].item()
+    out["ms"] = timed(lambda: p.forward(x_loc), iters)
+    yy = y.clone()
+    out["inverse_ms"] = timed(lambda: p.inverse(yy), iters)
+    pn = PencilRfft2(B, Hh, Ww, device=dev, exchange="nccl")
+    yn = pn.forward(x_loc)
+    torch.cuda.synchronize()
+    en = ((yn - ref).double().norm() / ref.double().norm()).reshape(1)
+    dist.all_reduce(en, op=dist.ReduceOp.MAX)
+    out["nccl_rel_l2"] = en.item()
+    out["nccl_ms"] = timed(lambda: pn.forward(x_loc), iters)
+    yr = pn.row_pass(x_loc)
+    z = pn.transpose(yr)
+    out["rows_ms"] = timed(lambda: pn.row_pass(x_loc), iters)
+    out["transpose_ms"] = timed(lambda: pn.transpose(yr), iters)
+    out["cols_ms"] = timed(lambda: pn.col_pass(z), iters)
+    out["algorithmic_GBs"] = algo_bytes((B, Hh, Ww), 2) / out["ms"] / 1e6
+    return out
+
+
 def run_reference(args):
     """--impl reference: the reference's CPU path (torch.fft), rank 0 only."""
     rank = int(os.environ.get("RANK", "0"))
@@ -183,6 +359,7 @@ def run_ours(args):
     xr = torch.empty(*SHAPE, device=dev)
     stream = torch.cuda.current_stream().cuda_stream
     launches_per_step = fwd.num_launches + inv.num_launches
+    plan_desc = [fwd.describe()[1], inv.describe()[1]]
 
     def step():
         fwd.exec_ptr(x.data_ptr(), y.data_ptr(), 0, stream)
@@ -229,6 +406,17 @@ def run_ours(args):
         b.record()
         torch.cuda.synchronize()
         kms[name] = a.elapsed_time(b) / args.steps
+    # sustained figure: the same step for long enough (>= 0.6 s) that the power cap, not the burst clocks, sets the pace
+    sus_steps = 1500
+    for _ in range(500):
+        step()
+    s0, s1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    s0.record()
+    for _ in range(sus_steps):
+        step()
+    s1.record()
+    torch.cuda.synchronize()
+    sustained_ms = s0.elapsed_time(s1) / sus_steps
     clocks = sampler.stop() if rank == 0 else None
 
     # end to end through the host-buffer C ABI call
@@ -247,14 +435,38 @@ def run_ours(args):
     e2e_s = time.perf_counter() - t0
 
     if world > 1:
-        t = torch.tensor([ms, e2e_s], device=dev, dtype=torch.float64)
+        t = torch.tensor([ms, e2e_s, sustained_ms], device=dev, dtype=torch.float64)
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        ms, e2e_s = t[0].item(), t[1].item()
+        ms, e2e_s, sustained_ms = t[0].item(), t[1].item(), t[2].item()
+    del xh, yh, xrh, x, y, xr
+    fwd.destroy()
+    inv.destroy()
+    torch.cuda.empty_cache()
+    peak, peak_src = measured_peak()
+
+    # ---- beyond the headline: the other BASELINE configs, the reference's cuFFT sequence, the multi-GPU paths ----
+    extras = {}
+    if world == 1:
+        try:
+            extras["all_configs"] = {n: time_config(capi, torch, n, 200 if n in ("cfg1", "cfg2") else 10, peak)
+                                     for n in ("cfg1", "cfg2", "cfg4", "cfg5")}
+        except Exception as e:
+            extras["all_configs"] = {"error": repr(e)[:300]}
+        torch.cuda.empty_cache()
+        extras["cufft_sequence"] = cufft_sequence(torch, capi, ["cfg1", "cfg2", "cfg3", "cfg4", "cfg5"])
+    else:
+        try:
+            extras["cfg4_shard"] = cfg4_shard(capi, torch, dist, world, rank, dev, peak)
+        except Exception as e:
+            extras["cfg4_shard"] = {"error": repr(e)[:300]}
+        try:
+            extras["pencil"] = pencil_bench(torch, dist, world, rank, dev)
+        except Exception as e:
+            extras["pencil"] = {"error": repr(e)[:300]}
 
     if rank == 0:
         pair_bytes = 2 * algo_bytes_one_direction(nimg)
         gbs = world * pair_bytes * args.steps / (ms * 1e-3) / 1e9
-        peak, peak_src = measured_peak()
         dom = max(kms, key=kms.get)
         ach = algo_bytes_one_direction(nimg) / (kms[dom] * 1e-3) / 1e9
         traffic = None
@@ -274,16 +486,21 @@ def run_ours(args):
             "pairs_per_s": world * nimg * args.steps / (ms * 1e-3),
             "frac_of_8TBs_spec": gbs / world / 8000.0,
             "kernel_ms": kms,
+            "sustained_ms_per_step": sustained_ms,
+            "sustained": {"steps": sus_steps, "preheat_steps": 500, "GBs": pair_bytes / sustained_ms / 1e6,
+                          "frac_of_8TBs_spec": pair_bytes / sustained_ms / 1e6 / 8000.0,
+                          "frac_of_measured_peak": pair_bytes / sustained_ms / 1e6 / peak},
             "roofline": {"bound": "hbm", "kernel": dom, "achieved": ach, "peak": peak, "unit": "GB/s",
                          "frac": ach / peak, "traffic": traffic, "peak_source": peak_src,
                          "algorithmic_bytes_per_launch": algo_bytes_one_direction(nimg)},
             "e2e": {"value": world * pair_bytes * e2e_steps / e2e_s / 1e9, "unit": "GB/s",
-                    "h2d_bytes_per_step": (x.numel() + y.numel()) * 4, "d2h_bytes_per_step": (y.numel() + xr.numel()) * 4,
+                    "h2d_bytes_per_step": pair_bytes // 2, "d2h_bytes_per_step": pair_bytes // 2,
                     "steps": e2e_steps, "api": "trt_dft_exec_host (pinned host buffers)"},
             "gpu_launches": launches_per_step * args.steps,
             "clocks": clocks,
-            "plan": [fwd.describe()[1], inv.describe()[1]],
+            "plan": plan_desc,
         }
+        line.update(extras)
         if world == 1:
             cores = os.cpu_count() or 1
             sample = 768

@@ -65,7 +65,9 @@ int trt_dft_plan_create(trt_dft_plan_t* plan, int direction, int rank, const int
  * cufftXtExec (dft_plugins.cpp:171-176, :192); it is exposed because the pencil-decomposed multi-GPU
  * rfft2 runs it after the all-to-all transpose.  direction TRT_DFT_FORWARD uses
  * exp(-i..), TRT_DFT_INVERSE exp(+i..).  `in` may equal `out` in trt_dft_exec (each tile is read
- * completely before it is written).  Needs no workspace.
+ * completely before it is written; lengths outside the radix set go through the workspace for that).  Query
+ * trt_dft_workspace_bytes: it is non-zero for long axes (>= 4096 points, run as a four-step FFT through a
+ * workspace copy of the tensor) and for lengths with a prime factor above 31.
  */
 int trt_dft_plan_create_c2c(trt_dft_plan_t* plan, int direction, int64_t n, int64_t outer, int64_t inner, float scale);
 
@@ -79,6 +81,29 @@ int trt_dft_plan_create_c2c(trt_dft_plan_t* plan, int direction, int64_t n, int6
  * Call before trt_dft_exec, not concurrently with it.
  */
 int trt_dft_plan_set_column_split(trt_dft_plan_t plan, int nparts, const int64_t* col_starts, int64_t rows_per_image);
+
+/*
+ * Multi-GPU pencil rfft2 with the exchange fused into the row pass (no counterpart in the single-GPU reference,
+ * dft_plugins.cpp:341).  Same column split as trt_dft_plan_set_column_split, but block j of every image is not
+ * packed into `out`: the row kernel stores it straight into rank j's column slab
+ *     peer_slabs[j][image][image_rows][col_starts[j+1] - col_starts[j]]   (interleaved complex fp32)
+ * at rows row_offset .. row_offset + rows_per_image - 1 -- ordinary global stores through a peer mapping of that
+ * GPU's memory (CUDA IPC / symmetric memory; peer_slabs[own rank] is simply local memory).  `out` of trt_dft_exec
+ * is then unused (pass any valid pointer).  The caller synchronises the ranks (all rows written before any rank
+ * starts its column pass, and nobody overwrites a slab that is still being read).  nparts <= 8.
+ */
+int trt_dft_plan_set_peer_column_split(trt_dft_plan_t plan, int nparts, const int64_t* col_starts, int64_t rows_per_image,
+                                       int64_t image_rows, int64_t row_offset, void* const* peer_slabs);
+
+/*
+ * The mirror image for the pencil irfft2: a trt_dft_plan_create_c2c plan over data[outer][n][inner] stores output row
+ * q of every image into the row band of the rank that owns it,
+ *     peer_bands[j][image][row_starts[j+1] - row_starts[j]][dest_pitch]   for row_starts[j] <= q < row_starts[j+1],
+ * at columns dest_col_offset .. dest_col_offset + inner - 1, again with ordinary stores to peer memory; `out` is then
+ * unused.  row_starts has nparts+1 entries from 0 to n.  nparts = 0 restores the ordinary output.
+ */
+int trt_dft_plan_set_peer_row_split(trt_dft_plan_t plan, int nparts, const int64_t* row_starts, int64_t dest_pitch,
+                                    int64_t dest_col_offset, void* const* peer_bands);
 
 /* Replaces the workSize out-parameter of cufftXtMakePlanMany (dft_plugins.cpp:175) that
  * getWorkspaceSize reports (:114-129).  0 for every single-kernel plan. */

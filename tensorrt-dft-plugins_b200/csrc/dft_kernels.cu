@@ -353,6 +353,56 @@ int trt_dft_plan_set_column_split(trt_dft_plan_t plan, int nparts, const int64_t
     k.pack_n = nparts;
     for (int j = 0; nparts > 0 && j <= nparts; ++j) k.pack_c0[j] = (int)col_starts[j];   // (nparts == 0: back to plain rows, col_starts may be null)
     k.pack_hn = (int)rows_per_image;
+    k.pack_peer_on = 0;
+    return TRT_DFT_OK;
+}
+
+int trt_dft_plan_set_peer_column_split(trt_dft_plan_t plan, int nparts, const int64_t* col_starts, int64_t rows_per_image,
+                                       int64_t image_rows, int64_t row_offset, void* const* peer_slabs)
+{
+    if (nparts < 1 || !peer_slabs || image_rows < 1 || row_offset < 0 || row_offset + rows_per_image > image_rows ||
+        image_rows > (1LL << 30))
+        return TRT_DFT_ERR_INVALID_ARG;
+    for (int j = 0; j < nparts && j < 8; ++j)
+        if (!peer_slabs[j] || ((uintptr_t)peer_slabs[j] & 7)) return TRT_DFT_ERR_INVALID_ARG;
+    const int rc = trt_dft_plan_set_column_split(plan, nparts, col_starts, rows_per_image);
+    if (rc != TRT_DFT_OK) return rc;
+    KParams& k = plan->launches[0].kp;
+    k.pack_peer_on = 1;
+    k.pack_H = (int)image_rows;
+    k.pack_h0 = (int)row_offset;
+    for (int j = 0; j < 8; ++j) k.pack_peer[j] = j < nparts ? (float2*)peer_slabs[j] : nullptr;
+    return TRT_DFT_OK;
+}
+
+int trt_dft_plan_set_peer_row_split(trt_dft_plan_t plan, int nparts, const int64_t* row_starts, int64_t dest_pitch,
+                                    int64_t dest_col_offset, void* const* peer_bands)
+{
+    if (!plan || !plan->c2c || nparts < 0 || nparts > 8) return TRT_DFT_ERR_INVALID_ARG;
+    if (plan->launches.empty()) return TRT_DFT_OK;
+    ResolvedLaunch& last = plan->launches.back();                 // the pass that writes the result
+    if (last.kp.mode != dft::MODE_C2C_COLS || last.kp.n1split > 1) return TRT_DFT_ERR_UNSUPPORTED;
+    KParams& k = last.kp;
+    if (nparts == 0) {
+        k.split_n = 0;
+        return TRT_DFT_OK;
+    }
+    // second pass of a four-step FFT: rows and columns of the image are folded differently (KParams::split_n2)
+    const bool four = plan->launches.size() == 2 && plan->launches[0].kp.n1split > 1;
+    const long long n2 = four ? plan->launches[0].kp.H : 1;
+    const long long n_axis = (long long)k.H * n2, inner = k.inner / n2;
+    if (!row_starts || !peer_bands || row_starts[0] != 0 || row_starts[nparts] != n_axis || dest_pitch < 1 || dest_col_offset < 0 ||
+        dest_col_offset + inner > dest_pitch || dest_pitch > (1LL << 30))
+        return TRT_DFT_ERR_INVALID_ARG;
+    k.split_n2 = (int)n2;
+    k.split_inner = (int)inner;
+    for (int j = 0; j < nparts; ++j)
+        if (row_starts[j + 1] < row_starts[j] || !peer_bands[j] || ((uintptr_t)peer_bands[j] & 7)) return TRT_DFT_ERR_INVALID_ARG;
+    k.split_n = nparts;
+    for (int j = 0; j <= nparts; ++j) k.split_r0[j] = (int)row_starts[j];
+    k.split_pitch = (int)dest_pitch;
+    k.split_c0 = (int)dest_col_offset;
+    for (int j = 0; j < 8; ++j) k.split_peer[j] = j < nparts ? (float2*)peer_bands[j] : nullptr;
     return TRT_DFT_OK;
 }
 

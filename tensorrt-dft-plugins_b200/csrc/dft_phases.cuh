@@ -38,6 +38,60 @@ DFT_HD int fdiv(int x, unsigned magic)   // floor(x / d) for the d that produced
 // skewed shared-memory position of logical element p of a power-of-two row (pad != 0)
 DFT_HD int phys(int p, int pad) { return pad ? p + (p >> 4) + (p >> 8) : p; }
 
+// Column-split ("packed for all-to-all") address of element (global row R, column k); see KParams::pack_n.
+DFT_HD float2* packed_ptr(const KParams& p, float2* out, int R, int k, int Mo)
+{
+    const int b = R / p.pack_hn, rl = R - b * p.pack_hn;
+    // fully unrolled with constant indices: a run-time index into p.pack_c0 would push the kernel's
+    // private KParams copy into local memory
+    int c0 = p.pack_c0[0], cn = p.pack_c0[1] - p.pack_c0[0];
+    float2* peer = p.pack_peer[0];
+#if defined(__CUDA_ARCH__)
+#pragma unroll
+#endif
+    for (int t = 1; t < 8; ++t) {
+        if (t < p.pack_n && k >= p.pack_c0[t]) {
+            c0 = p.pack_c0[t];
+            cn = p.pack_c0[t + 1] - p.pack_c0[t];
+            peer = p.pack_peer[t];
+        }
+    }
+    if (p.pack_peer_on)   // straight into the owning rank's slab [image][pack_H][cn]
+        return peer + ((long long)b * p.pack_H + p.pack_h0 + rl) * cn + (k - c0);
+    return out + (long long)b * p.pack_hn * Mo + (long long)p.pack_hn * c0 + (long long)rl * cn + (k - c0);
+}
+
+// Row-split address of element (pass row qp, pass column jj) of image o_ of a strided-axis pass (see KParams::split_n).
+DFT_HD float2* split_row_ptr(const KParams& p, long long o_, int q);
+DFT_HD float2* split_elem_ptr(const KParams& p, long long o_, int qp, long long jj)
+{
+    int q = qp;
+    long long c = jj;
+    if (p.split_n2 > 1) {
+        const int k2 = (int)(jj / p.split_inner);
+        c = jj - (long long)k2 * p.split_inner;
+        q = qp * p.split_n2 + k2;
+    }
+    return split_row_ptr(p, o_, q) + c;
+}
+// ... and of its row q (image rows), at this rank's first column
+DFT_HD float2* split_row_ptr(const KParams& p, long long o_, int q)
+{
+    int r0 = p.split_r0[0], rn = p.split_r0[1] - p.split_r0[0];
+    float2* peer = p.split_peer[0];
+#if defined(__CUDA_ARCH__)
+#pragma unroll
+#endif
+    for (int t = 1; t < 8; ++t) {
+        if (t < p.split_n && q >= p.split_r0[t]) {
+            r0 = p.split_r0[t];
+            rn = p.split_r0[t + 1] - p.split_r0[t];
+            peer = p.split_peer[t];
+        }
+    }
+    return peer + (o_ * rn + (q - r0)) * p.split_pitch + p.split_c0;
+}
+
 // ---- one radix-R step over all lines of the tile -------------------------------------------
 // ROWS (COLS=false): line l, logical element e at buf[l*pitch + phys(e)].
 // COLS (COLS=true) : line = (img, col) with ncols columns per image; element e at

@@ -122,25 +122,6 @@ DFT_HD void program_i2d(const KParams& p, long long tile, float2* buf, const flo
     ctx.sync();
 }
 
-// Column-split ("packed for all-to-all") position of element (global row R, column k); see KParams::pack_n.
-DFT_HD long long packed_index(const KParams& p, int R, int k, int Mo)
-{
-    const int b = R / p.pack_hn, rl = R - b * p.pack_hn;
-    // fully unrolled with constant indices: a run-time index into p.pack_c0 would push the kernel's
-    // private KParams copy into local memory
-    int c0 = p.pack_c0[0], cn = p.pack_c0[1] - p.pack_c0[0];
-#if defined(__CUDA_ARCH__)
-#pragma unroll
-#endif
-    for (int t = 1; t < 8; ++t) {
-        if (t < p.pack_n && k >= p.pack_c0[t]) {
-            c0 = p.pack_c0[t];
-            cn = p.pack_c0[t + 1] - p.pack_c0[t];
-        }
-    }
-    return (long long)b * p.pack_hn * Mo + (long long)p.pack_hn * c0 + (long long)rl * cn + (k - c0);
-}
-
 // ---- MODE_F1D: G rows per tile, W = 2M --------------------------------------------------------
 // LOAD = false: the tile is already in `buf` (the pipelined kernel's producer warps put it there).
 template <class Ctx, bool LOAD = true>
@@ -196,8 +177,8 @@ DFT_HD void program_f1d(const KParams& p, long long tile, float2* buf, const flo
         } else {
             float2* ob = (float2*)out;
             const int R = (int)first + r;
-            ob[packed_index(p, R, k, Mo)] = x1;
-            if (kk != k) ob[packed_index(p, R, kk, Mo)] = x2;
+            *packed_ptr(p, ob, R, k, Mo) = x1;
+            if (kk != k) *packed_ptr(p, ob, R, kk, Mo) = x2;
         }
     }
     ctx.sync();
@@ -337,7 +318,15 @@ DFT_HD void program_cols(const KParams& p, long long tile, float2* buf, const fl
     float2* dst = (float2*)out + o_ * N * p.inner + col0;
     const float sc = p.scale;
     const bool four = p.n1split > 1;
-    if (fixed_col) {
+    if (p.split_n) {
+        // rows go to the rank that owns them (never combined with the four-step first pass, which writes the workspace)
+        for (int idx = ctx.tid; idx < total; idx += ctx.nthr) {
+            const int q = idx / ncol;
+            const int j = idx - q * ncol;
+            const float2 z = buf[DFT_LDT(p.perm_col + q) * P + j];
+            *split_elem_ptr(p, o_, q, col0 + j) = float2{z.x * sc, z.y * sc};
+        }
+    } else if (fixed_col) {
         float2* d0 = dst + (long long)n0 * p.inner + j0;
         const long long dstep2 = (long long)rstep * p.inner;
         if (!four) {

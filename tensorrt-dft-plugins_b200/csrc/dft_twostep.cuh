@@ -44,7 +44,9 @@ DFT_HD void reg_fft(float2 (&v)[RA * RB])
 // Columns j >= ncol of a partial tile are computed on whatever the tile holds and dropped.
 template <int R1A, int R1B, int R2A, int R2B, int TM, bool FOUR, class Ctx>
 DFT_HD void cols_two_step(float2* buf, int P, const float2* tw /* w_N^j */, float2* dst, long long inner, int ncol, float scale,
-                          bool inverse, const float2* tw4 /* four-step: w_Ntot^j, else null */, int n1, Ctx& ctx)
+                          bool inverse, const float2* tw4 /* four-step: w_Ntot^j, else null */, int n1, Ctx& ctx,
+                          const KParams* split = nullptr /* rows go to their owning ranks (KParams::split_n) */,
+                          long long split_img = 0, long long split_col0 = 0)
 {
     constexpr int R1 = R1A * R1B, R2 = R2A * R2B, N = R1 * R2;
     // step A
@@ -80,7 +82,14 @@ DFT_HD void cols_two_step(float2* buf, int P, const float2* tw /* w_N^j */, floa
                 v[k2] = cmul(v[k2], DFT_LDT(t4 + k2 * t4s));
             });
         }
-        if (j < ncol) {
+        if (j < ncol && split) {
+            static_for<0, R2>([&](auto kc) {
+                constexpr int k2 = decltype(kc)::value;
+                const int q = k1 + R1 * k2;
+                const int qq = inverse ? (q == 0 ? 0 : N - q) : q;
+                *split_elem_ptr(*split, split_img, qq, split_col0 + j) = float2{v[k2].x * scale, v[k2].y * scale};
+            });
+        } else if (j < ncol) {
             // output row q = k1 + R1*k2, or (N - q) mod N for the inverse
             // one pointer walks down (or, for the inverse, up) the output rows
             const long long step = inverse ? -(long long)R1 * inner : (long long)R1 * inner;

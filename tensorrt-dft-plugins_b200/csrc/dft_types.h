@@ -149,6 +149,28 @@ struct KParams {
     int pack_n;
     int pack_c0[9];
     int pack_hn;
+    // Peer variant of the same (multi-GPU pencil rfft2, exchange fused into the row pass): block j does not go into
+    // `out` but straight into rank j's column slab [image][pack_H rows][cn_j columns] at pack_peer[j] (a pointer into
+    // that GPU's memory, written with ordinary stores); this rank's rows start at row pack_h0 of every image.
+    // pack_peer_on == 0: blocks go into `out` as described above.
+    int pack_peer_on;
+    int pack_H;
+    int pack_h0;
+    float2* pack_peer[8];
+    // MODE_C2C_COLS, mirror image of the above (pencil irfft2, exchange fused into the column pass): output row q of
+    // every image belongs to the rank j with split_r0[j] <= q < split_r0[j+1] and is stored into that rank's row band
+    // [image][rows of rank j][split_pitch columns] at split_peer[j], starting at column split_c0 (this rank's first
+    // column).  split_n == 0: rows go into `out`.
+    int split_n;
+    int split_r0[9];
+    int split_pitch;
+    int split_c0;
+    // When this launch is the second pass of a four-step FFT it sees the tensor as [outer][N1][N2 * inner]: its row q'
+    // and column j' are row q' * split_n2 + j' / split_inner, column j' % split_inner of the image.  Ordinary pass:
+    // split_n2 == 1.
+    int split_n2;
+    int split_inner;
+    float2* split_peer[8];
     // MODE_C2C_COLS as the first pass of a four-step FFT of a long axis Ntot = n1split * N:
     // slab o_ = (o_hi, n1) gathers rows n1 + n1split*n2 (n2 = 0..N-1) of image o_hi, stores them as the
     // contiguous rows n1*N + k2 and multiplies row k2 by w_Ntot^(n1*k2) (tw_four, Ntot entries).

@@ -1,18 +1,32 @@
-"""Pencil (slab) decomposed rfft2 for grids too large for one GPU pass -- BASELINE config 5,
-`[4, 8192, 8192]` over 2/4/8 GPUs.
+"""Pencil (slab) decomposed rfft2 / irfft2 for grids too large for one GPU pass -- BASELINE config 5,
+`[4, 8192, 8192]` over 2/4/8 GPUs.  The reference is single-GPU
+(/root/reference/src/dft_plugins/dft_plugins.cpp:341, "assuming single GPU for now"); this is the part that removes
+that limit.
 
 Layout.  Every rank holds a contiguous band of ROWS of every image, x_local [B, H_r, W].
-  1. local row pass      R2C along W                          -> [B, H_r, W/2+1] complex
-  2. all-to-all transpose (the only exchange on the path): rank r receives, from every rank s, the
-     columns [c0_r, c1_r) of s's rows                          -> [B, H, C_r] complex on rank r
-  3. local column pass   C2C of length H along the row axis     (data[outer=B][n=H][inner=C_r])
-The result stays distributed by columns: rank r owns spectrum[:, :, c0_r:c1_r].  W/2+1 is odd for
-every even W, so the column split is uneven (all_to_all_single with explicit split sizes).
+  forward  1. local row pass      R2C along W                          -> [B, H_r, W/2+1] complex
+           2. transpose (the only exchange on the path): rank r ends up with the columns [c0_r, c1_r) of ALL rows
+                                                                         -> [B, H, C_r] complex on rank r
+           3. local column pass   C2C of length H along the row axis     (data[outer=B][n=H][inner=C_r])
+  inverse  the same three steps backwards: column pass (C2C inverse), transpose back to row bands, row pass C2R
+           (scaled by 1/(H*W)).
+The spectrum stays distributed by columns: rank r owns spectrum[:, :, c0_r:c1_r].  W/2+1 is odd for every even W,
+so the column split is uneven.
 
-The transforms are injected (`row_fft`, `col_fft`) so that the exchange logic can be tested on CPU
-with the gloo backend; on GPUs they default to the library's plans (trt_dft_plugins.capi) and the
-exchange runs over NCCL / NVLink.
+Three ways to run the exchange, same results:
+  * "peer"  (default on GPUs when peer memory can be mapped): the exchange is FUSED INTO THE KERNELS.  Every rank's
+            column slab (forward) / row band (inverse) lives in peer-mapped memory (torch symmetric memory, or CUDA IPC
+            handles as fallback), and the row kernel's epilogue (trt_dft_plan_set_peer_column_split) / the column
+            kernel's epilogue (trt_dft_plan_set_peer_row_split) stores each value straight into the owning rank's
+            memory with ordinary global stores over NVLink -- no pack, no send buffer, no NCCL in the data path, and
+            the transfer overlaps the transform tile by tile.  Only two GPU-side barriers per call remain.
+            (Plain stores only: TMA multicast loads here read only this GPU's memory, since on B200 a TMA multicast
+            load from another GPU's memory hung the GPU.  Nothing on this path loads from a peer at all.)
+  * "nccl"  the row pass writes blocks split by destination (trt_dft_plan_set_column_split) and one
+            all_to_all_single per image lands them in place; kept as fallback and as the parity check of "peer".
+  * injected transforms (`row_fft`, `col_fft`): plain torch exchange, so that the logic can be tested on CPU with gloo.
 """
+import ctypes
 from typing import Callable, Optional
 
 import torch
@@ -21,9 +35,51 @@ import torch.distributed as dist
 from .multi_gpu import shard_batch
 
 
+class PeerBuffer:
+    """`nfloats` fp32 of device memory on every rank of the group, each rank's copy mapped into every other rank's
+    address space.  ptrs[r] is rank r's buffer as seen from this process; barrier() is a GPU-side barrier on the
+    current stream (all ranks' earlier work on their streams, peer stores included, is complete and visible after it)."""
+
+    def __init__(self, nfloats: int, device, group=None):
+        self.group = group if group is not None else dist.group.WORLD
+        self.world = dist.get_world_size(self.group)
+        self.rank = dist.get_rank(self.group)
+        self.kind = None
+        self._keep = []
+        try:
+            import torch.distributed._symmetric_memory as symm
+            self.local = symm.empty(nfloats, dtype=torch.float32, device=device)
+            self._hdl = symm.rendezvous(self.local, self.group)
+            self.ptrs = [int(p) for p in self._hdl.buffer_ptrs]
+            self.kind = "symmetric_memory"
+        except Exception as e:  # no fabric / fd passing in this container: classic CUDA IPC handles through torch
+            self._hdl = None
+            self._why = repr(e)[:200]
+            self.local = torch.empty(nfloats, dtype=torch.float32, device=device)
+            handle = self.local.untyped_storage()._share_cuda_()
+            handles = [None] * self.world
+            dist.all_gather_object(handles, handle, group=self.group)
+            self.ptrs = []
+            for r, h in enumerate(handles):
+                if r == self.rank:
+                    self.ptrs.append(self.local.data_ptr())
+                    continue
+                st = torch.UntypedStorage._new_shared_cuda(*h)
+                self._keep.append(st)
+                self.ptrs.append(st.data_ptr())
+            self.kind = "cuda_ipc"
+        self._flag = torch.zeros(1, device=device)
+
+    def barrier(self):
+        if self._hdl is not None:
+            self._hdl.barrier(channel=0)
+        else:
+            dist.all_reduce(self._flag, group=self.group)      # stream-ordered on every rank: a GPU-side barrier
+
+
 class PencilRfft2:
     def __init__(self, B: int, H: int, W: int, group=None, device=None,
-                 row_fft: Optional[Callable] = None, col_fft: Optional[Callable] = None):
+                 row_fft: Optional[Callable] = None, col_fft: Optional[Callable] = None, exchange: str = "auto"):
         self.B, self.H, self.W, self.Mo = int(B), int(H), int(W), int(W) // 2 + 1
         self.group = group
         self.world = dist.get_world_size(group) if dist.is_initialized() else 1
@@ -35,6 +91,10 @@ class PencilRfft2:
         self.c0, self.cn = self.col_spans[self.rank]
         self._row_fft, self._col_fft = row_fft, col_fft
         self._plans = None
+        assert exchange in ("auto", "peer", "nccl")
+        self.exchange = exchange
+        self._peer = None
+        self.exchange_used = None
 
     # ---- default GPU transforms ---------------------------------------------------------------
     def _gpu_plans(self):
@@ -60,7 +120,7 @@ class PencilRfft2:
         cols.exec(z, z)                      # in place: each column tile is read completely before it is written
         return z
 
-    # ---- the exchange ----------------------------------------------------------------------------
+    # ---- the exchange as separate steps (CPU tests, un-fused GPU baseline) ------------------------
     def transpose(self, y_rows):
         """[B, H_r, Mo, 2] on every rank  ->  [B, H, C_r, 2] on every rank."""
         if self.world == 1:
@@ -78,18 +138,133 @@ class PencilRfft2:
             off += n
         return z
 
+    def transpose_back(self, z_cols):
+        """[B, H, C_r, 2] on every rank  ->  [B, H_r, Mo, 2] on every rank (inverse of `transpose`)."""
+        if self.world == 1:
+            return z_cols
+        B = self.B
+        send = torch.cat([z_cols[:, h0:h0 + hn].reshape(-1) for (h0, hn) in self.row_spans])
+        in_splits = [B * hn * self.cn * 2 for (_, hn) in self.row_spans]
+        out_splits = [B * self.hn * cn_s * 2 for (_, cn_s) in self.col_spans]
+        recv = torch.empty(sum(out_splits), dtype=z_cols.dtype, device=z_cols.device)
+        dist.all_to_all_single(recv, send, output_split_sizes=out_splits, input_split_sizes=in_splits, group=self.group)
+        y = torch.empty(B, self.hn, self.Mo, 2, dtype=z_cols.dtype, device=z_cols.device)
+        off = 0
+        for (c0_s, cn_s), n in zip(self.col_spans, out_splits):
+            y[:, :, c0_s:c0_s + cn_s] = recv[off:off + n].view(B, self.hn, cn_s, 2)
+            off += n
+        return y
+
+    # ---- public entry points -------------------------------------------------------------------
+    def _injected(self, x):
+        return self._row_fft is not None or self._col_fft is not None or not x.is_cuda
+
     def forward(self, x_local):
-        """x_local: this rank's row band [B, H_r, W] (fp32).  Returns its column band [B, H, C_r, 2]."""
+        """x_local: this rank's row band [B, H_r, W] (fp32).  Returns its column band [B, H, C_r, 2].  With the peer
+        exchange the result is a view of the rank's peer-mapped slab: it stays valid until the next forward()."""
         assert tuple(x_local.shape) == (self.B, self.hn, self.W)
-        if self._row_fft is not None or self._col_fft is not None or not x_local.is_cuda or self.world == 1:
+        if self._injected(x_local):
             return self.col_pass(self.transpose(self.row_pass(x_local)))
+        if self._use_peer(x_local.device):
+            return self._forward_peer(x_local)
+        self.exchange_used = "nccl" if self.world > 1 else "local"
         return self._forward_fused(x_local)
 
-    # ---- GPU path: pack fused into the row pass, one all-to-all per image straight into place ----------
+    def inverse(self, z_cols, inv_row_fft: Optional[Callable] = None, inv_col_fft: Optional[Callable] = None):
+        """z_cols: this rank's column band of the spectrum [B, H, C_r, 2].  Returns its row band of the real image
+        [B, H_r, W], scaled by 1/(H*W) (Irfft semantics, dft_plugins.cpp:457-468)."""
+        assert tuple(z_cols.shape) == (self.B, self.H, self.cn, 2)
+        if inv_row_fft is not None or inv_col_fft is not None or not z_cols.is_cuda:
+            return inv_row_fft(self.transpose_back(inv_col_fft(z_cols)))
+        if self._use_peer(z_cols.device):
+            return self._inverse_peer(z_cols)
+        return self._inverse_nccl(z_cols)
+
+    # ---- GPU path 1: exchange fused into the kernels, stores to peer memory ------------------------------
+    def _use_peer(self, device):
+        if self.exchange == "nccl" or self.world == 1 and self.exchange != "peer":
+            return False
+        if self._peer is None:
+            try:
+                self._setup_peer(device)
+            except Exception as e:
+                if self.exchange == "peer":
+                    raise
+                self._peer = False
+                self._peer_error = repr(e)[:300]
+        return bool(self._peer)
+
+    def _setup_peer(self, device):
+        from . import capi
+        L = capi.lib()
+        L.trt_dft_plan_set_peer_column_split.restype = ctypes.c_int
+        L.trt_dft_plan_set_peer_column_split.argtypes = [ctypes.c_void_p, ctypes.c_int, ctypes.POINTER(ctypes.c_int64), ctypes.c_int64,
+                                                         ctypes.c_int64, ctypes.c_int64, ctypes.POINTER(ctypes.c_void_p)]
+        L.trt_dft_plan_set_peer_row_split.restype = ctypes.c_int
+        L.trt_dft_plan_set_peer_row_split.argtypes = [ctypes.c_void_p, ctypes.c_int, ctypes.POINTER(ctypes.c_int64), ctypes.c_int64,
+                                                      ctypes.c_int64, ctypes.POINTER(ctypes.c_void_p)]
+        cn_max = max(cn for _, cn in self.col_spans)
+        hn_max = max(hn for _, hn in self.row_spans)
+        if self.world > 1:
+            slab = PeerBuffer(self.B * self.H * cn_max * 2, device, self.group)       # forward target / inverse source
+            band = PeerBuffer(self.B * hn_max * self.Mo * 2, device, self.group)      # inverse target
+            slab_ptrs, band_ptrs, kind = slab.ptrs, band.ptrs, slab.kind
+        else:                                      # one rank: "peer" memory is local memory; same kernels, same code
+            slab = _LocalBuffer(self.B * self.H * cn_max * 2, device)
+            band = _LocalBuffer(self.B * hn_max * self.Mo * 2, device)
+            slab_ptrs, band_ptrs, kind = [slab.local.data_ptr()], [band.local.data_ptr()], "local"
+        # forward: rows of all B images in one launch, blocks stored into the owners' slabs
+        rows = capi.Plan(capi.FORWARD, (self.W,), self.B * self.hn)
+        starts = (ctypes.c_int64 * (self.world + 1))(*([c0 for (c0, _) in self.col_spans] + [self.Mo]))
+        parr = (ctypes.c_void_p * self.world)(*slab_ptrs)
+        rc = L.trt_dft_plan_set_peer_column_split(rows.handle, self.world, starts, self.hn, self.H, self.h0, parr)
+        if rc != 0:
+            raise capi.DftError(f"trt_dft_plan_set_peer_column_split failed with status {rc}")
+        cols = capi.C2CPlan(capi.FORWARD, self.H, self.B, self.cn)
+        # inverse: columns (C2C, +i sign, scaled by 1/H) store their rows into the owners' row bands; the C2R row pass
+        # scales by 1/W, together the Irfft plugin's 1/(H*W)
+        icols = capi.C2CPlan(capi.INVERSE, self.H, self.B, self.cn, scale=1.0 / self.H)
+        rstarts = (ctypes.c_int64 * (self.world + 1))(*([h0 for (h0, _) in self.row_spans] + [self.H]))
+        barr = (ctypes.c_void_p * self.world)(*band_ptrs)
+        rc = L.trt_dft_plan_set_peer_row_split(icols.handle, self.world, rstarts, self.Mo, self.c0, barr)
+        if rc != 0:
+            raise capi.DftError(f"trt_dft_plan_set_peer_row_split failed with status {rc}")
+        irows = capi.Plan(capi.INVERSE, (self.W,), self.B * self.hn)
+        self._peer = {"slab": slab, "band": band, "rows": rows, "cols": cols, "icols": icols, "irows": irows, "kind": kind}
+
+    def _forward_peer(self, x_local):
+        P = self._peer
+        slab, rows, cols = P["slab"], P["rows"], P["cols"]
+        z = slab.local[: self.B * self.H * self.cn * 2].view(self.B, self.H, self.cn, 2)
+        slab.barrier()                    # nobody is still reading (or returning) last call's slabs
+        rows.exec_ptr(x_local.data_ptr(), z.data_ptr(), 0, torch.cuda.current_stream(x_local.device).cuda_stream)
+        slab.barrier()                    # every rank's row blocks have landed everywhere
+        cols.exec(z, z)
+        self.exchange_used = "peer:" + P["kind"]
+        return z
+
+    def _inverse_peer(self, z_cols):
+        P = self._peer
+        band, icols, irows = P["band"], P["icols"], P["irows"]
+        y = band.local[: self.B * self.hn * self.Mo * 2].view(self.B, self.hn, self.Mo, 2)
+        band.barrier()                    # nobody is still reading last call's row bands
+        icols.exec(z_cols.contiguous(), self._dummy_out(z_cols))          # every output row goes to its owner's band
+        band.barrier()                    # every rank's columns have landed everywhere
+        x = torch.empty(self.B, self.hn, self.W, dtype=torch.float32, device=z_cols.device)
+        irows.exec(y, x)
+        self.exchange_used = "peer:" + P["kind"]
+        return x
+
+    def _dummy_out(self, like):
+        # trt_dft_exec wants a valid `out` of the plan's size even when every row goes to a peer band
+        if getattr(self, "_dummy", None) is None or self._dummy.numel() != like.numel():
+            self._dummy = torch.empty_like(like)
+        return self._dummy
+
+    # ---- GPU path 2: pack fused into the row pass, one NCCL all-to-all per image straight into place --------
     def _fused_plans(self):
         if getattr(self, "_fplans", None) is None:
             from . import capi
-            import ctypes
             rows = capi.Plan(capi.FORWARD, (self.W,), self.hn)                   # one image's row band per launch
             L = capi.lib()
             L.trt_dft_plan_set_column_split.restype = ctypes.c_int
@@ -128,3 +303,27 @@ class PencilRfft2:
                 works[b].wait()
             cols.exec(z[b], z[b])
         return z
+
+    def _inverse_nccl(self, z_cols):
+        from . import capi
+        if getattr(self, "_iplans", None) is None:
+            self._iplans = (capi.C2CPlan(capi.INVERSE, self.H, self.B, self.cn, scale=1.0 / self.H),
+                            capi.Plan(capi.INVERSE, (self.W,), self.B * self.hn))
+        icols, irows = self._iplans
+        t = torch.empty_like(z_cols)
+        icols.exec(z_cols.contiguous(), t)
+        y = self.transpose_back(t)
+        x = torch.empty(self.B, self.hn, self.W, dtype=torch.float32, device=z_cols.device)
+        irows.exec(y.contiguous(), x)
+        self.exchange_used = "nccl" if self.world > 1 else "local"
+        return x
+
+
+class _LocalBuffer:
+    def __init__(self, nfloats, device):
+        self.local = torch.empty(nfloats, dtype=torch.float32, device=device)
+        self.ptrs = [self.local.data_ptr()]
+        self.kind = "local"
+
+    def barrier(self):
+        pass

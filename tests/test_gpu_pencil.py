@@ -23,3 +23,77 @@ def test_fused_pencil_forward_matches_single_plan(B, H, W):
     assert O.rel_l2(z.cpu().numpy(), ref.cpu().numpy()) <= 1e-6
     want = O.torch_rfftn(x[B - 1].cpu(), 2, dtype=torch.float64)
     assert O.rel_l2(z[B - 1].cpu().numpy(), want.numpy()) <= 1e-5
+
+
+@pytest.mark.parametrize("B,H,W", [(2, 720, 1440), (1, 8192, 8192), (3, 96, 200), (2, 34, 64)])
+def test_peer_store_kernels_forward_and_inverse_on_one_gpu(B, H, W):
+    """The kernels of the peer exchange (row pass storing column blocks into the owners' slabs, column pass storing
+    rows into the owners' row bands) with the one rank's "peer" memory being local memory: forward against the
+    single-plan rfft2, inverse back to the image."""
+    from trt_dft_plugins import capi
+    from trt_dft_plugins.pencil import PencilRfft2
+    torch.manual_seed(12)
+    x = torch.randn(B, H, W, device="cuda")
+    p = PencilRfft2(B, H, W, exchange="peer")
+    z = p.forward(x)
+    assert p.exchange_used == "peer:local"
+    torch.cuda.synchronize()
+    ref = capi.rfftn(x, 2)
+    assert O.rel_l2(z.cpu().numpy(), ref.cpu().numpy()) <= 1e-6
+    xb = p.inverse(z)
+    torch.cuda.synchronize()
+    assert O.rel_l2(xb.cpu().numpy(), x.cpu().numpy()) <= 1e-6
+
+
+def test_peer_split_addresses_with_several_destinations_on_one_gpu():
+    """Several 'ranks' emulated on one GPU: each destination is its own local buffer.  Pins the address arithmetic of
+    trt_dft_plan_set_peer_column_split / _row_split (uneven splits, an empty part, row offset inside the image)."""
+    import ctypes
+    from trt_dft_plugins import capi
+    L = capi.lib()
+    L.trt_dft_plan_set_peer_column_split.restype = ctypes.c_int
+    L.trt_dft_plan_set_peer_column_split.argtypes = [ctypes.c_void_p, ctypes.c_int, ctypes.POINTER(ctypes.c_int64), ctypes.c_int64,
+                                                     ctypes.c_int64, ctypes.c_int64, ctypes.POINTER(ctypes.c_void_p)]
+    L.trt_dft_plan_set_peer_row_split.restype = ctypes.c_int
+    L.trt_dft_plan_set_peer_row_split.argtypes = [ctypes.c_void_p, ctypes.c_int, ctypes.POINTER(ctypes.c_int64), ctypes.c_int64,
+                                                  ctypes.c_int64, ctypes.POINTER(ctypes.c_void_p)]
+    torch.manual_seed(13)
+    for (B, H, W, hn, h0) in ((2, 720, 1440, 300, 111), (1, 8192, 8192, 1024, 4096), (2, 60, 100, 17, 3)):
+        Mo = W // 2 + 1
+        starts = [0, Mo // 3, Mo // 3, Mo - 7, Mo]                 # 4 destinations, one empty
+        x = torch.randn(B, hn, W, device="cuda")                   # this "rank"'s row band
+        slabs = [torch.full((B, H, max(starts[j + 1] - starts[j], 1), 2), float("nan"), device="cuda") for j in range(4)]
+        rows = capi.Plan(capi.FORWARD, (W,), B * hn)
+        rc = L.trt_dft_plan_set_peer_column_split(rows.handle, 4, (ctypes.c_int64 * 5)(*starts), hn, H, h0,
+                                                  (ctypes.c_void_p * 4)(*[s.data_ptr() for s in slabs]))
+        assert rc == 0
+        dummy = torch.empty(B * hn * Mo * 2, device="cuda")
+        rows.exec_ptr(x.data_ptr(), dummy.data_ptr(), 0, torch.cuda.current_stream().cuda_stream)
+        torch.cuda.synchronize()
+        plain = capi.rfftn(x, 1)                                   # [B, hn, Mo, 2]
+        for j in range(4):
+            cn = starts[j + 1] - starts[j]
+            if cn == 0:
+                continue
+            got = slabs[j][:, h0:h0 + hn]
+            assert O.rel_l2(got.cpu().numpy(), plain[:, :, starts[j]:starts[j + 1]].cpu().numpy()) <= 1e-6
+            assert torch.isnan(slabs[j][:, :h0]).all() and torch.isnan(slabs[j][:, h0 + hn:]).all()   # nothing else touched
+        # mirror: a column band [B, H, cn] -> rows scattered into 4 row bands at column offset c0
+        cn, c0 = 37, 5
+        z = torch.randn(B, H, cn, 2, device="cuda")
+        rstarts = [0, H // 4, H // 4, H - 3, H]
+        bands = [torch.full((B, max(rstarts[j + 1] - rstarts[j], 1), Mo, 2), float("nan"), device="cuda") for j in range(4)]
+        cols = capi.C2CPlan(capi.INVERSE, H, B, cn, scale=0.5)
+        rc = L.trt_dft_plan_set_peer_row_split(cols.handle, 4, (ctypes.c_int64 * 5)(*rstarts), Mo, c0,
+                                               (ctypes.c_void_p * 4)(*[b.data_ptr() for b in bands]))
+        assert rc == 0
+        cols.exec(z, torch.empty_like(z))
+        torch.cuda.synchronize()
+        want = 0.5 * torch.view_as_real(torch.fft.ifft(torch.view_as_complex(z.double()), dim=1, norm="forward"))
+        for j in range(4):
+            rn = rstarts[j + 1] - rstarts[j]
+            if rn == 0:
+                continue
+            got = bands[j][:, :, c0:c0 + cn]
+            assert O.rel_l2(got.cpu().numpy(), want[:, rstarts[j]:rstarts[j + 1]].cpu().numpy()) <= 1e-5
+            assert torch.isnan(bands[j][:, :, :c0]).all() and torch.isnan(bands[j][:, :, c0 + cn:]).all()

@@ -28,7 +28,12 @@ def _worker(rank, world, port, out_dir):
     y = p.forward(full[:, p.h0:p.h0 + p.hn].contiguous())
     want = torch.view_as_real(torch.fft.rfft2(full, dim=(-2, -1)))[:, :, p.c0:p.c0 + p.cn]
     err = ((y - want).norm() / want.norm()).item()
-    torch.save({"err": err, "shape": tuple(y.shape), "cn": p.cn}, os.path.join(out_dir, f"r{rank}.pt"))
+    # and back: column band of the spectrum -> row band of the image (irfft2 semantics, scaled by 1/(H*W))
+    inv_col = lambda z: torch.view_as_real(torch.fft.ifft(torch.view_as_complex(z.contiguous()), dim=1))
+    inv_row = lambda t: torch.fft.irfft(torch.view_as_complex(t.contiguous()), n=W, dim=-1)
+    xb = p.inverse(y.contiguous(), inv_row_fft=inv_row, inv_col_fft=inv_col)
+    err_inv = ((xb - full[:, p.h0:p.h0 + p.hn]).norm() / full[:, p.h0:p.h0 + p.hn].norm()).item()
+    torch.save({"err": err, "err_inv": err_inv, "shape": tuple(y.shape), "cn": p.cn}, os.path.join(out_dir, f"r{rank}.pt"))
     dist.barrier()
     dist.destroy_process_group()
 
@@ -39,3 +44,4 @@ def test_pencil_transpose_two_ranks(tmp_path):
     r0, r1 = torch.load(tmp_path / "r0.pt"), torch.load(tmp_path / "r1.pt")
     assert r0["cn"] + r1["cn"] == 7 and r0["shape"] == (3, 10, 4, 2) and r1["shape"] == (3, 10, 3, 2)
     assert r0["err"] < 1e-6 and r1["err"] < 1e-6
+    assert r0["err_inv"] < 1e-6 and r1["err_inv"] < 1e-6
