@@ -70,7 +70,7 @@ DFT_HD void cols_two_step(float2* buf, int P, const float2* tw /* w_N^j */, floa
         static_for<1, R2>([&](auto ac) {
             constexpr int a = decltype(ac)::value;
             twp += k1;
-            v[a] = cmul(p[a * P], DFT_LDT(twp));
+            v[a] = cmul(p[a * P], DFT_LDS(twp));            // (the dispatch guarantees this table sits in shared memory)
         });
         reg_fft<R2A, R2B>(v);
         if (FOUR && tw4) {
