@@ -176,6 +176,18 @@ DFT_HD void fft_step(float2* buf, int nlines, int pitch, int N, int L, const flo
     }
 }
 
+#if defined(__CUDACC__)
+#define DFT_NOINLINE_HD __host__ __device__ __noinline__
+#else
+#define DFT_NOINLINE_HD
+#endif
+template <int R, bool COLS>
+DFT_NOINLINE_HD void fft_step_big(float2* buf, int nlines, int pitch, int N, int L, const float2* tw, int ncols, int img_stride,
+                                  unsigned mmag, unsigned bmag, unsigned lmag, int pad, int ord, int tid, int nthr, const float2* tw_t)
+{
+    fft_step<R, COLS>(buf, nlines, pitch, N, L, tw, ncols, img_stride, mmag, bmag, lmag, pad, ord, tid, nthr, tw_t);
+}
+
 template <bool COLS>
 DFT_HD void fft_step_dispatch(int radix, float2* buf, int nlines, int pitch, int N, int L,
                               const float2* tw, int ncols, int img_stride, unsigned mmag, unsigned bmag,
@@ -185,6 +197,12 @@ DFT_HD void fft_step_dispatch(int radix, float2* buf, int nlines, int pitch, int
 #define DFT_CASE(R)                                                                     \
     case R:                                                                             \
         fft_step<R, COLS>(buf, nlines, pitch, N, L, tw, ncols, img_stride, mmag, bmag, lmag, pad, ord, tid, nthr, tw_t); \
+        break;
+// the large prime radices need more registers than the kernels' launch bounds leave: kept out of line, so that their
+// spills stay inside them and the common radices keep the register allocation they had without them
+#define DFT_CASE_BIG(R)                                                                 \
+    case R:                                                                             \
+        fft_step_big<R, COLS>(buf, nlines, pitch, N, L, tw, ncols, img_stride, mmag, bmag, lmag, pad, ord, tid, nthr, tw_t); \
         break;
         DFT_CASE(2)
         DFT_CASE(3)
@@ -198,12 +216,13 @@ DFT_HD void fft_step_dispatch(int radix, float2* buf, int nlines, int pitch, int
         DFT_CASE(11)
         DFT_CASE(13)
         DFT_CASE(16)
-        DFT_CASE(17)
-        DFT_CASE(19)
-        DFT_CASE(23)
-        DFT_CASE(29)
-        DFT_CASE(31)
+        DFT_CASE_BIG(17)
+        DFT_CASE_BIG(19)
+        DFT_CASE_BIG(23)
+        DFT_CASE_BIG(29)
+        DFT_CASE_BIG(31)
 #undef DFT_CASE
+#undef DFT_CASE_BIG
         default:
             break;
     }

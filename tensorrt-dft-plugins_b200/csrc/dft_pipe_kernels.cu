@@ -227,7 +227,7 @@ struct GeoTwo : GeoLine<N_, S0, S1, S2, 1> {
         const int n1 = (int)(o_ % n1s);
         dft::cols_two_step<R1A, R1B, R2A, R2B, TM_, FOUR_>(buf, p.P, p.tw_col, dst, p.inner, ncol, p.scale, p.inverse != 0,
                                                     p.n1split > 1 ? p.tw_four : nullptr, n1, ctx,
-                                                    (p.split_n && p.n1split <= 1) ? &p : nullptr, o_, col0);
+                                                    p, p.split_n != 0 && p.n1split <= 1, o_, col0);
     }
 };
 // Registered row length (M packed complex points) with the two-step register-resident row programs.

@@ -45,8 +45,8 @@ DFT_HD void reg_fft(float2 (&v)[RA * RB])
 template <int R1A, int R1B, int R2A, int R2B, int TM, bool FOUR, class Ctx>
 DFT_HD void cols_two_step(float2* buf, int P, const float2* tw /* w_N^j */, float2* dst, long long inner, int ncol, float scale,
                           bool inverse, const float2* tw4 /* four-step: w_Ntot^j, else null */, int n1, Ctx& ctx,
-                          const KParams* split = nullptr /* rows go to their owning ranks (KParams::split_n) */,
-                          long long split_img = 0, long long split_col0 = 0)
+                          const KParams& kp, bool split /* rows go to their owning ranks (KParams::split_n) */,
+                          long long split_img, long long split_col0)
 {
     constexpr int R1 = R1A * R1B, R2 = R2A * R2B, N = R1 * R2;
     // step A
@@ -87,7 +87,7 @@ DFT_HD void cols_two_step(float2* buf, int P, const float2* tw /* w_N^j */, floa
                 constexpr int k2 = decltype(kc)::value;
                 const int q = k1 + R1 * k2;
                 const int qq = inverse ? (q == 0 ? 0 : N - q) : q;
-                *split_elem_ptr(*split, split_img, qq, split_col0 + j) = float2{v[k2].x * scale, v[k2].y * scale};
+                *split_elem_ptr(kp, split_img, qq, split_col0 + j) = float2{v[k2].x * scale, v[k2].y * scale};
             });
         } else if (j < ncol) {
             // output row q = k1 + R1*k2, or (N - q) mod N for the inverse
