@@ -185,6 +185,39 @@ def time_config(capi, torch, name, iters, peak, batch_override=None):
     return out
 
 
+def truncated_bench(capi, torch, peak, iters=200):
+    """Truncated-mode rfft2 + irfft2 at the headline shape: only the kept low modes cross HBM on the complex side.
+    Its own algorithmic bytes: real image once + kept block once per direction."""
+    nimg, out = SHAPE[0] * SHAPE[1], {}
+    g = torch.Generator(device="cuda").manual_seed(1)
+    x = torch.randn(nimg, H, W, device="cuda", generator=g)
+    xr = torch.empty_like(x)
+    st = torch.cuda.current_stream().cuda_stream
+    for kh, kw in ((45, 91), (22, 45), (12, 24)):
+        f = capi.TruncatedPlan(capi.FORWARD, (H, W), nimg, kh, kw)
+        i = capi.TruncatedPlan(capi.INVERSE, (H, W), nimg, kh, kw)
+        y = torch.empty(nimg, 2 * kh, kw, 2, device="cuda")
+        step = lambda: (f.exec_ptr(x.data_ptr(), y.data_ptr(), 0, st), i.exec_ptr(y.data_ptr(), xr.data_ptr(), 0, st))
+        for _ in range(5):
+            step()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        torch.cuda.synchronize()
+        e0.record()
+        for _ in range(iters):
+            step()
+        e1.record()
+        torch.cuda.synchronize()
+        ms = e0.elapsed_time(e1) / iters
+        ab = 2 * nimg * (H * W * 4 + 2 * kh * kw * 8)
+        out[f"keep_{2 * kh}x{kw}"] = {"pair_ms": ms, "algorithmic_bytes_per_pair": ab, "GBs": ab / ms / 1e6,
+                                      "frac_of_measured_peak": ab / ms / 1e6 / peak,
+                                      "speedup_vs_full_pair_bytes": 2 * algo_bytes_one_direction(nimg) / ab}
+        del f, i, y
+    del x, xr
+    torch.cuda.empty_cache()
+    return out
+
+
 def cufft_sequence(torch, capi, names):
     """The reference's own device path -- cufftXtMakePlanMany / cufftXtExec (+ cublasScalEx for the inverse), the calls
     of dft_plugins.cpp:161-196, :454-468 -- timed by tools/cufft_ref_bench in a SUBPROCESS (comparator only: cuFFT is
@@ -453,6 +486,10 @@ def run_ours(args):
         except Exception as e:
             extras["all_configs"] = {"error": repr(e)[:300]}
         torch.cuda.empty_cache()
+        try:
+            extras["truncated_modes"] = truncated_bench(capi, torch, peak)
+        except Exception as e:
+            extras["truncated_modes"] = {"error": repr(e)[:300]}
         extras["cufft_sequence"] = cufft_sequence(torch, capi, ["cfg1", "cfg2", "cfg3", "cfg4", "cfg5"])
     else:
         try:

@@ -83,6 +83,23 @@ int trt_dft_plan_create_c2c(trt_dft_plan_t* plan, int direction, int64_t n, int6
 int trt_dft_plan_set_column_split(trt_dft_plan_t plan, int nparts, const int64_t* col_starts, int64_t rows_per_image);
 
 /*
+ * Truncated-mode rfft2 / irfft2 for spectral layers (FNO / AFNO: "why FFT plugins for TensorRT",
+ * /root/reference/README.md:3) that keep only a corner of low modes.  No counterpart in the reference, whose
+ * Rfft / Irfft always move the full one-sided spectrum (README.md:9-14); this is what fusing the layer's mode
+ * selection into the transform buys: the discarded modes never touch HBM.
+ *   dims = {H, W} (logical real size), kept modes = rows [0, keep_h) and [H - keep_h, H), columns [0, keep_w)
+ *   of the one-sided spectrum [H][W/2+1];  1 <= keep_h <= H/2, 1 <= keep_w <= W/2+1.
+ *   FORWARD : in  [batch][H][W] real            -> out [batch][2*keep_h][keep_w] complex
+ *             == torch.fft.rfft2(x)[..., rows, :keep_w] with rows = cat(0..keep_h-1, H-keep_h..H-1)
+ *   INVERSE : in  [batch][2*keep_h][keep_w] complex -> out [batch][H][W] real, scaled by 1/(H*W)
+ *             == torch.fft.irfft2 of the spectrum that holds `in` at those modes and zeros elsewhere.
+ * Shapes with fused register-resident kernels (90 x 180) run one kernel that bulk-copies only the kept block
+ * (no workspace; in/out must be 16-byte aligned); every other shape runs the full transform through the workspace
+ * plus a crop / zero-pad kernel (query trt_dft_workspace_bytes).  Executed with trt_dft_exec / trt_dft_exec_host.
+ */
+int trt_dft_plan_create_truncated(trt_dft_plan_t* plan, int direction, const int64_t* dims, int64_t batch, int64_t keep_h, int64_t keep_w);
+
+/*
  * Multi-GPU pencil rfft2 with the exchange fused into the row pass (no counterpart in the single-GPU reference,
  * dft_plugins.cpp:341).  Same column split as trt_dft_plan_set_column_split, but block j of every image is not
  * packed into `out`: the row kernel stores it straight into rank j's column slab

@@ -90,6 +90,15 @@ struct trt_dft_plan_s {
     bool c2c = false;                     // trt_dft_plan_create_c2c: complex on both sides
     void* pool = nullptr;                 // one device allocation holding every table
     std::vector<ResolvedLaunch> launches;
+    // truncated-mode plan (trt_dft_plan_create_truncated): kept block [2*kh][kw] on the complex side
+    bool trunc = false;
+    int kh = 0, kw = 0, tH = 0, tW = 0;
+    dft::trunc_fwd_fn t_fwd = nullptr;    // fused kernels that move only the kept modes ...
+    dft::trunc_inv_fn t_inv = nullptr;
+    int t_threads = 0, t_smem = 0, t_grid = 0;
+    float t_scale = 1.f;
+    trt_dft_plan_t t_full = nullptr;      // ... or the full transform through the workspace plus a crop / pad kernel
+    size_t t_full_ws_off = 0;             // where the full plan's own workspace starts inside ours
     // trt_dft_exec_host scratch (lazily allocated, reused across calls)
     std::mutex host_mu;
     void* h_in = nullptr;
@@ -161,6 +170,72 @@ int trt_dft_plan_create_c2c(trt_dft_plan_t* plan_out, int direction, int64_t n, 
     }
     pl->c2c = true;
     return realize_plan(pl, plan_out);
+}
+
+int trt_dft_plan_create_truncated(trt_dft_plan_t* plan_out, int direction, const int64_t* dims, int64_t batch, int64_t keep_h, int64_t keep_w)
+{
+    if (!plan_out) return TRT_DFT_ERR_INVALID_ARG;
+    *plan_out = nullptr;
+    if (!dims || (direction != 0 && direction != 1) || batch < 0 || dims[0] < 1 || dims[1] < 1 || dims[0] > (1LL << 30) || dims[1] > (1LL << 30))
+        return TRT_DFT_ERR_INVALID_ARG;
+    const int64_t H = dims[0], W = dims[1], MO = W / 2 + 1;
+    if (keep_h < 1 || 2 * keep_h > H || keep_w < 1 || keep_w > MO) return TRT_DFT_ERR_INVALID_ARG;
+    trt_dft_plan_s* pl = new (std::nothrow) trt_dft_plan_s();
+    if (!pl) return TRT_DFT_ERR_ALLOC;
+    pl->trunc = true;
+    pl->kh = (int)keep_h;
+    pl->kw = (int)keep_w;
+    pl->tH = (int)H;
+    pl->tW = (int)W;
+    pl->pd.direction = direction;
+    pl->pd.rank = 2;
+    pl->pd.dims[0] = H;
+    pl->pd.dims[1] = W;
+    pl->pd.batch = batch;
+    const int64_t real_floats = batch * H * W, kept_floats = batch * 2 * keep_h * keep_w * 2;
+    pl->pd.in_floats = direction == TRT_DFT_INVERSE ? kept_floats : real_floats;
+    pl->pd.out_floats = direction == TRT_DFT_INVERSE ? real_floats : kept_floats;
+    pl->t_scale = (float)(1.0 / ((double)H * (double)W));
+    int num_sms = 0;
+    if (cudaGetDevice(&pl->device) != cudaSuccess ||
+        cudaDeviceGetAttribute(&num_sms, cudaDevAttrMultiProcessorCount, pl->device) != cudaSuccess) {
+        cudaGetLastError();
+        delete pl;
+        return TRT_DFT_ERR_CUDA;
+    }
+    char desc[192];
+    const SpecEntry* e = (batch > 0 && !getenv("TRT_DFT_NO_SPEC")) ? find_spec((int)H, (int)W) : nullptr;
+    if (e && e->trunc_fwd && e->trunc_inv) {
+        pl->t_fwd = e->trunc_fwd;
+        pl->t_inv = e->trunc_inv;
+        pl->t_threads = e->NT;
+        pl->t_smem = direction == TRT_DFT_INVERSE ? e->smem_i : e->smem_f;
+        const void* fn = direction == TRT_DFT_INVERSE ? (const void*)e->trunc_inv : (const void*)e->trunc_fwd;
+        if (cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, pl->t_smem) != cudaSuccess) {
+            cudaGetLastError();
+            delete pl;
+            return TRT_DFT_ERR_CUDA;
+        }
+        pl->t_grid = (int)std::min<long long>(batch, num_sms);
+        snprintf(desc, sizeof desc, "truncated_%s<%d,%d> keep=%dx%d images=%lld [fused, kept modes only] grid=%dx%d", direction ? "irfft2" : "rfft2",
+                 (int)H, (int)W, 2 * pl->kh, pl->kw, (long long)batch, pl->t_grid, pl->t_threads);
+    } else if (batch > 0) {
+        const int rc = trt_dft_plan_create(&pl->t_full, direction, 2, dims, batch);
+        if (rc != TRT_DFT_OK) {
+            delete pl;
+            return rc;
+        }
+        const size_t full_bytes = ((size_t)batch * H * MO * 8 + 255) / 256 * 256;
+        pl->t_full_ws_off = full_bytes;
+        pl->pd.ws_bytes = full_bytes + trt_dft_workspace_bytes(pl->t_full);
+        snprintf(desc, sizeof desc, "truncated_%s<%d,%d> keep=%dx%d images=%lld [full transform through the workspace + %s]",
+                 direction ? "irfft2" : "rfft2", (int)H, (int)W, 2 * pl->kh, pl->kw, (long long)batch, direction ? "zero-pad" : "crop");
+    } else {
+        snprintf(desc, sizeof desc, "empty");
+    }
+    pl->pd.description = desc;
+    *plan_out = pl;
+    return TRT_DFT_OK;
 }
 
 // Device side of plan creation: tables to the GPU, kernel attributes, grid sizes.
@@ -444,12 +519,60 @@ int trt_dft_plan_describe(trt_dft_plan_t plan, char* buf, size_t len)
         strncpy(buf, d.c_str(), len - 1);
         buf[len - 1] = 0;
     }
+    if (plan->trunc) return plan->pd.batch == 0 ? 0 : (plan->t_fwd ? 1 : 1 + (int)plan->t_full->launches.size());
     return (int)plan->launches.size();
+}
+
+static int exec_truncated(trt_dft_plan_t plan, const void* in, void* out, void* workspace, void* stream)
+{
+    if (plan->pd.batch == 0) return TRT_DFT_OK;
+    if (!in || !out) return TRT_DFT_ERR_INVALID_ARG;
+    int cur_dev = -1;
+    if (cudaGetDevice(&cur_dev) != cudaSuccess || cur_dev != plan->device) {
+        cudaGetLastError();
+        return TRT_DFT_ERR_INVALID_ARG;
+    }
+    const bool inv = plan->pd.direction == TRT_DFT_INVERSE;
+    cudaStream_t st = (cudaStream_t)stream;
+    const bool aligned = ((((uintptr_t)in) | ((uintptr_t)out)) & 15) == 0;
+    if (plan->t_fwd && aligned) {
+        if (!inv)
+            plan->t_fwd<<<plan->t_grid, plan->t_threads, plan->t_smem, st>>>((const float*)in, (float*)out, plan->pd.batch, plan->kh, plan->kw);
+        else
+            plan->t_inv<<<plan->t_grid, plan->t_threads, plan->t_smem, st>>>((const float*)in, (float*)out, plan->pd.batch, plan->kh, plan->kw,
+                                                                            plan->t_scale);
+        if (cudaPeekAtLastError() != cudaSuccess) {
+            cudaGetLastError();
+            return TRT_DFT_ERR_CUDA;
+        }
+        return TRT_DFT_OK;
+    }
+    if (!plan->t_full) return TRT_DFT_ERR_INVALID_ARG;      // fused kernels only, and the buffers are not 16-byte aligned
+    if (!workspace || ((uintptr_t)workspace & 15)) return TRT_DFT_ERR_WORKSPACE;
+    if (((uintptr_t)(inv ? in : (const void*)out)) & 7) return TRT_DFT_ERR_INVALID_ARG;
+    void* full = workspace;
+    void* inner_ws = (unsigned char*)workspace + plan->t_full_ws_off;
+    const int MO = plan->tW / 2 + 1;
+    if (!inv) {
+        const int rc = trt_dft_exec(plan->t_full, in, full, inner_ws, stream);
+        if (rc != TRT_DFT_OK) return rc;
+        dft::launch_crop_modes(full, out, plan->pd.batch, plan->tH, MO, plan->kh, plan->kw, stream);
+    } else {
+        dft::launch_pad_modes(in, full, plan->pd.batch, plan->tH, MO, plan->kh, plan->kw, stream);
+        const int rc = trt_dft_exec(plan->t_full, full, out, inner_ws, stream);
+        if (rc != TRT_DFT_OK) return rc;
+    }
+    if (cudaPeekAtLastError() != cudaSuccess) {
+        cudaGetLastError();
+        return TRT_DFT_ERR_CUDA;
+    }
+    return TRT_DFT_OK;
 }
 
 int trt_dft_exec(trt_dft_plan_t plan, const void* in, void* out, void* workspace, void* stream)
 {
     if (!plan) return TRT_DFT_ERR_INVALID_ARG;
+    if (plan->trunc) return exec_truncated(plan, in, out, workspace, stream);
     if (plan->launches.empty()) return TRT_DFT_OK;
     if (!in || !out) return TRT_DFT_ERR_INVALID_ARG;
     // the plan's tables live on the GPU it was created on: launching from another current device would
@@ -499,6 +622,7 @@ int trt_dft_plan_destroy(trt_dft_plan_t plan)
 {
     if (!plan) return TRT_DFT_OK;
     int rc = TRT_DFT_OK;
+    if (plan->t_full) trt_dft_plan_destroy(plan->t_full);
     if (plan->h_sub) trt_dft_plan_destroy(plan->h_sub);
     if (plan->h_sub_tail) trt_dft_plan_destroy(plan->h_sub_tail);
     for (cudaStream_t st : plan->h_streams)
@@ -514,7 +638,7 @@ int trt_dft_plan_destroy(trt_dft_plan_t plan)
 int trt_dft_exec_host(trt_dft_plan_t plan, const void* host_in, void* host_out)
 {
     if (!plan) return TRT_DFT_ERR_INVALID_ARG;
-    if (plan->launches.empty()) return TRT_DFT_OK;
+    if (plan->launches.empty() && !(plan->trunc && plan->pd.batch > 0)) return TRT_DFT_OK;
     if (!host_in || !host_out) return TRT_DFT_ERR_INVALID_ARG;
     int cur_dev = -1;
     if (cudaGetDevice(&cur_dev) != cudaSuccess || cur_dev != plan->device) {
@@ -531,7 +655,7 @@ int trt_dft_exec_host(trt_dft_plan_t plan, const void* host_in, void* host_out)
         if (const char* e = getenv("TRT_DFT_HOST_CHUNKS")) nchunks = std::max(1, std::min(32, atoi(e)));   // tuning override
         if (nchunks > batch) nchunks = (int)batch;
         // a c2c plan's `batch` (outer * inner) is not a contiguous leading dimension of [outer][n][inner]: one chunk
-        if (plan->c2c) nchunks = 1;
+        if (plan->c2c || plan->trunc) nchunks = 1;
         plan->h_chunk = (batch + nchunks - 1) / nchunks;
         const int64_t tail = batch % plan->h_chunk;
         bool ok = cudaMalloc(&plan->h_in, in_bytes) == cudaSuccess && cudaMalloc(&plan->h_out, out_bytes) == cudaSuccess;

@@ -15,4 +15,8 @@ kernel_fn tile_kernel_for(int mode, int threads);           // nullptr: unknown 
 pipe_fn pipe_kernel_for(int mode);                          // nullptr: mode has no pipelined variant
 pipe_fn pipe_kernel_for_geo(const KParams& k, bool tables_in_smem);   // nullptr: schedule not registered
 
+// dft_trunc.cu: kept modes <-> full one-sided spectrum (fallback of the truncated-mode plans)
+void launch_crop_modes(const void* full, void* kept, long long nimg, int H, int MO, int kh, int kw, void* stream);
+void launch_pad_modes(const void* kept, void* full, long long nimg, int H, int MO, int kh, int kw, void* stream);
+
 }  // namespace dft

@@ -546,6 +546,232 @@ __global__ void __launch_bounds__(C::THREADS, 1)
     if (!C::IOW && gt == 0) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
 }
 
+// ---- truncated modes (spectral layers keep a corner of low modes) --------------------------------------------------
+// FNO / AFNO style layers use only the modes rows q in [0, kh) u [H - kh, H), columns k in [0, kw) of the one-sided
+// spectrum.  The truncated forward never writes the discarded modes and the truncated inverse never reads them: the
+// kept block [2*kh][kw] travels as ONE dense bulk copy (16*kh*kw bytes per image instead of H*MO*8), so the complex
+// side of the traffic shrinks by H*MO / (2*kh*kw).  Arithmetic as in the full kernels; columns k >= kw are skipped.
+namespace reg2d {
+
+// kept-row index of spectrum row q, or -1
+__device__ __forceinline__ int kept_row(int q, int H, int kh) { return q < kh ? q : (q >= H - kh ? q - (H - 2 * kh) : -1); }
+
+// I/O warp of group g for the truncated kernels: loads of LOADB bytes and stores of STOREB bytes per image, each as one
+// bulk copy (the small side is a few KB; the large side is the dense real image).  A stage is refilled once its store
+// has been read out of shared memory.
+template <class C, int STAGE>
+__device__ __forceinline__ void io_loop_trunc(int g, const unsigned char* __restrict__ in, unsigned char* __restrict__ out, long long nimg,
+                                              unsigned char* stages, unsigned full0, unsigned done0, unsigned loadb, unsigned storeb)
+{
+    constexpr int NG = C::NG, NS = C::NS;
+    auto load = [&](long long tile, int s) {
+        asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(full0 + 8 * s), "r"(loadb) : "memory");
+        asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+                         pipe::s32(stages + (size_t)s * STAGE)),
+                     "l"(in + tile * (long long)loadb), "r"(loadb), "r"(full0 + 8 * s)
+                     : "memory");
+    };
+    if (g == 0)
+        for (int s = 0; s < NS; ++s) {
+            const long long tile = blockIdx.x + s * (long long)gridDim.x;
+            if (tile >= nimg) break;
+            load(tile, s);
+        }
+    long long it = g;
+    for (long long tile = blockIdx.x + (long long)g * gridDim.x; tile < nimg; tile += (long long)NG * gridDim.x, it += NG) {
+        const int s = (int)(it % NS);
+        pipe::mbar_wait(done0 + 8 * (g * NS + s), (unsigned)((it / C::LCM) & 1));
+        asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(out + tile * (long long)storeb),
+                     "r"(pipe::s32(stages + (size_t)s * STAGE)), "r"(storeb)
+                     : "memory");
+        asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+        const long long next = tile + (long long)NS * gridDim.x;
+        if (next < nimg) {
+            asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
+            load(next, s);
+        }
+    }
+    asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
+}
+
+}  // namespace reg2d
+
+template <class C>
+__global__ void __launch_bounds__(C::THREADS, 1)
+    reg_rfft2_trunc_kernel(const float* __restrict__ in, float* __restrict__ out, long long nimg, int kh, int kw)
+{
+    static_assert(C::IOW, "the truncated kernels use the I/O-warp layout");
+    constexpr int H = C::H, M = C::M, MO = C::MO, GT = C::GT, NG = C::NG, NS = C::NS, WPP = C::WPP, Hh = C::Hh;
+    extern __shared__ __align__(128) unsigned char smem_raw[];
+    unsigned char* stages = smem_raw;
+    float2* tws = reinterpret_cast<float2*>(smem_raw + NS * C::STAGE_F);
+    const unsigned full0 = pipe::s32(tws + C::NTAB_F);
+    const unsigned done0 = full0 + 8 * NS;
+    const int tid = threadIdx.x;
+    for (int i = tid; i < C::NTAB_F; i += C::THREADS) tws[i] = float2{reg2d::g_split_table<C>.x[i], reg2d::g_split_table<C>.y[i]};
+    if (tid == 0) {
+        for (int s = 0; s < NS; ++s) pipe::mbar_init(full0 + 8 * s, 1);
+        for (int s = 0; s < NG * NS; ++s) pipe::mbar_init(done0 + 8 * s, GT / 32);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        pipe::fence_async();
+    }
+    __syncthreads();
+    if (tid >= NG * GT) {
+        if ((tid & 31) == 0)
+            reg2d::io_loop_trunc<C, C::STAGE_F>((tid - NG * GT) >> 5, reinterpret_cast<const unsigned char*>(in), reinterpret_cast<unsigned char*>(out),
+                                                nimg, stages, full0, done0, (unsigned)C::TILE_F, (unsigned)(16 * kh * kw));
+        return;
+    }
+    const int g = tid / GT;
+    const int gt = tid - g * GT;
+    const int warp = gt >> 5;
+    const int p = warp / WPP;
+    const int line = (warp - p * WPP) * 32 + (gt & 31);
+    const float sg = p ? -1.f : 1.f;
+    const int lrow = line < H ? line : H - 1, lcol = line < MO ? line : MO - 1;
+    const bool col_warp_live = (warp - p * WPP) * 32 < kw;      // this warp holds at least one kept column
+    const int bar_id = 1 + g;
+    long long it = g;
+    for (long long tile = blockIdx.x + (long long)g * gridDim.x; tile < nimg; tile += (long long)NG * gridDim.x, it += NG) {
+        const int s = (int)(it % NS);
+        float2* buf = reinterpret_cast<float2*>(stages + (size_t)s * C::STAGE_F);
+        pipe::mbar_wait(full0 + 8 * s, (unsigned)((it / NS) & 1));
+        {
+            float2 z[C::Mh];
+            reg2d::load_fold<C::Mh>(z, reinterpret_cast<const float4*>(buf) + lrow * (M / 2), sg);
+            pipe::group_sync(bar_id, GT);
+            reg2d::line_fft<C::RA, C::RB>(z);
+            reg2d::split_store<C>(z, buf + lrow, p, tws + p * (C::NPAIR + 1));
+        }
+        pipe::group_sync(bar_id, GT);
+        {
+            float2 y[Hh];
+            if (col_warp_live) {
+                reg2d::load_fold<Hh>(y, reinterpret_cast<const float4*>(buf) + lcol * (H / 2), sg);
+                reg2d::line_fft<C::CA, C::CB>(y);
+            }
+            pipe::group_sync(bar_id, GT);               // every column has been read: the kept block may overwrite the tile
+            if (col_warp_live && line < kw) {
+                float2* dst = buf + line;               // kept block, dense [2*kh][kw]
+                static_for<0, Hh>([&](auto kc) {
+                    constexpr int k2 = decltype(kc)::value;
+                    constexpr int c0 = ((Hh + 1) * k2) % H;
+                    const int q = (c0 < Hh) ? c0 + Hh * p : c0 - Hh * p;      // output row of Y[k2]
+                    const int qi = reg2d::kept_row(q, H, kh);
+                    if (qi >= 0) dst[qi * kw] = y[k2];
+                });
+            }
+            pipe::fence_async();
+            __syncwarp();
+            if ((gt & 31) == 0) pipe::mbar_arrive(done0 + 8 * (g * NS + s));
+        }
+    }
+}
+
+template <class C>
+__global__ void __launch_bounds__(C::THREADS, 1)
+    reg_irfft2_trunc_kernel(const float* __restrict__ in, float* __restrict__ out, long long nimg, int kh, int kw, float scale)
+{
+    static_assert(C::IOW, "the truncated kernels use the I/O-warp layout");
+    constexpr int H = C::H, M = C::M, Mh = C::Mh, MO = C::MO, PI = C::PI, GT = C::GT, NG = C::NG, NS = C::NS, WPP = C::WPP, Hh = C::Hh;
+    constexpr int NTW = C::NPAIR + 1;
+    extern __shared__ __align__(128) unsigned char smem_raw[];
+    unsigned char* stages = smem_raw;
+    float2* twm = reinterpret_cast<float2*>(smem_raw + NS * C::STAGE_I);
+    const unsigned full0 = pipe::s32(twm + C::NTAB_I);
+    const unsigned done0 = full0 + 8 * NS;
+    const int tid = threadIdx.x;
+    for (int i = tid; i < C::NTAB_I; i += C::THREADS)
+        twm[i] = float2{scale * reg2d::g_merge_table<C>.x[i], scale * reg2d::g_merge_table<C>.y[i]};
+    if (tid == 0) {
+        for (int s = 0; s < NS; ++s) pipe::mbar_init(full0 + 8 * s, 1);
+        for (int s = 0; s < NG * NS; ++s) pipe::mbar_init(done0 + 8 * s, GT / 32);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        pipe::fence_async();
+    }
+    __syncthreads();
+    if (tid >= NG * GT) {
+        if ((tid & 31) == 0)
+            reg2d::io_loop_trunc<C, C::STAGE_I>((tid - NG * GT) >> 5, reinterpret_cast<const unsigned char*>(in), reinterpret_cast<unsigned char*>(out),
+                                                nimg, stages, full0, done0, (unsigned)(16 * kh * kw), (unsigned)C::TILE_F);
+        return;
+    }
+    const int g = tid / GT;
+    const int gt = tid - g * GT;
+    const int warp = gt >> 5, lane = gt & 31;
+    const int pc = warp / WPP;
+    const int col = (warp - pc * WPP) * 32 + lane;
+    const int lcol = col < MO ? col : MO - 1;
+    const float sgc = pc ? -1.f : 1.f;
+    const int pr = lane >> 4;
+    const int row = warp * 16 + (lane & 15);
+    const int lrow = row < H ? row : H - 1;
+    const float sgr = pr ? -1.f : 1.f;
+    const int bar_id = 1 + g;
+    long long it = g;
+    for (long long tile = blockIdx.x + (long long)g * gridDim.x; tile < nimg; tile += (long long)NG * gridDim.x, it += NG) {
+        const int s = (int)(it % NS);
+        float2* buf = reinterpret_cast<float2*>(stages + (size_t)s * C::STAGE_I);
+        pipe::mbar_wait(full0 + 8 * s, (unsigned)((it / NS) & 1));
+        {
+            // columns: kept rows of column k from the dense kept block [2*kh][kw]; every other mode is zero
+            float2 y[Hh];
+            const bool live = lcol < kw;
+            const float2* src = buf + (live ? lcol : 0);
+            static_for<0, Hh>([&](auto nc) {
+                constexpr int n2 = decltype(nc)::value;
+                constexpr int ia = (H - 2 * n2) % H, ib = (2 * H - Hh - 2 * n2) % H;      // index-reversed line (see load_fold_rev)
+                const int qa = reg2d::kept_row(ia, H, kh), qb = reg2d::kept_row(ib, H, kh);
+                float2 a = float2{0.f, 0.f}, b = float2{0.f, 0.f};
+                if (live && qa >= 0) a = src[qa * kw];
+                if (live && qb >= 0) b = src[qb * kw];
+                y[n2] = float2{fmaf(sgc, b.x, a.x), fmaf(sgc, b.y, a.y)};
+            });
+            pipe::group_sync(bar_id, GT);               // the kept block has been read: the transposed tile may overwrite it
+            reg2d::line_fft<C::CA, C::CB>(y);
+            if (pc == 0) reg2d::store_rows_t<C, 0>(y, buf + lcol * PI);
+            else reg2d::store_rows_t<C, 1>(y, buf + lcol * PI);
+        }
+        pipe::group_sync(bar_id, GT);
+        {
+            float2 z[Mh];
+            const float2* pa = buf + lrow + pr * (Mh * PI);
+            const float2* pb = buf + lrow - pr * (Mh * PI);
+            const float2* tw = twm + pr * NTW;
+            {
+                const float2 u = pa[0], v = pb[M * PI];
+                z[0] = float2{scale * (u.x + v.x), scale * (pr ? -(u.y + v.y) : (u.x - v.x))};
+            }
+            static_for<1, NTW>([&](auto kc) {
+                constexpr int k2 = decltype(kc)::value;
+                const float2 a = pa[2 * k2 * PI], b = pb[(M - 2 * k2) * PI];
+                const float2 t = tw[k2];
+                const float sx = a.x + b.x, sy = a.y - b.y;
+                const float dx = a.x - b.x, dy = a.y + b.y;
+                const float ux = t.x * dx - t.y * dy, uy = t.x * dy + t.y * dx;
+                z[Mh - k2] = float2{fmaf(scale, sx, ux), fmaf(scale, sy, uy)};
+                z[k2] = float2{fmaf(scale, sx, -ux), fmaf(-scale, sy, uy)};
+            });
+            pipe::group_sync(bar_id, GT);
+            reg2d::line_fft<C::RA, C::RB>(z);
+            float2* op = buf + lrow * M + pr * Mh;
+            float2* om = buf + lrow * M - pr * Mh;
+            static_for<0, Mh>([&](auto nc) {
+                constexpr int n2 = decltype(nc)::value;
+                constexpr int c0 = ((Mh + 1) * n2) % M;
+                const float ox = __shfl_xor_sync(0xffffffffu, z[n2].x, 16);
+                const float oy = __shfl_xor_sync(0xffffffffu, z[n2].y, 16);
+                const float2 r = float2{fmaf(sgr, z[n2].x, ox), fmaf(sgr, z[n2].y, oy)};
+                if constexpr (c0 < Mh) op[c0] = r;
+                else om[c0] = r;
+            });
+            pipe::fence_async();
+            __syncwarp();
+            if ((gt & 31) == 0) pipe::mbar_arrive(done0 + 8 * (g * NS + s));
+        }
+    }
+}
+
 #endif  // __CUDACC__
 
 

@@ -30,8 +30,11 @@ SpecEntry make_pipe()
 template <class C>
 SpecEntry make_reg()
 {
-    return SpecEntry{C::H, C::W, C::RA, C::RB, C::CA, C::CB, C::THREADS, C::SMEM_F, C::SMEM_I,
-                     reg_rfft2_kernel<C>, reg_irfft2_kernel<C>, true};
+    SpecEntry e{C::H, C::W, C::RA, C::RB, C::CA, C::CB, C::THREADS, C::SMEM_F, C::SMEM_I,
+                reg_rfft2_kernel<C>, reg_irfft2_kernel<C>, true};
+    e.trunc_fwd = reg_rfft2_trunc_kernel<C>;
+    e.trunc_inv = reg_irfft2_trunc_kernel<C>;
+    return e;
 }
 
 }  // namespace

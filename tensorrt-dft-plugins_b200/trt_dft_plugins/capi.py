@@ -13,7 +13,9 @@ FORWARD, INVERSE = 0, 1
 SYMBOLS = [
     "trt_dft_version", "trt_dft_error_string", "trt_dft_plan_create", "trt_dft_workspace_bytes",
     "trt_dft_exec", "trt_dft_plan_destroy", "trt_dft_exec_host", "trt_dft_plan_describe",
-    "trt_dft_plan_input_floats", "trt_dft_plan_output_floats",
+    "trt_dft_plan_input_floats", "trt_dft_plan_output_floats", "trt_dft_plan_create_c2c", "trt_dft_plan_set_column_split",
+    "trt_dft_query_workspace_bytes", "trt_dft_exec_static_ws", "trt_dft_plan_create_truncated",
+    "trt_dft_plan_set_peer_column_split", "trt_dft_plan_set_peer_row_split",
 ]
 
 _bound = None
@@ -195,3 +197,28 @@ class C2CPlan(Plan):
         self._ws = None
         _check(L.trt_dft_plan_create_c2c(ctypes.byref(self._h), self.direction, int(n), int(outer), int(inner),
                                          float(scale)), "trt_dft_plan_create_c2c")
+
+
+class TruncatedPlan(Plan):
+    """rfft2 / irfft2 that moves only the kept low modes (trt_dft_plan_create_truncated): rows [0, keep_h) and
+    [H - keep_h, H), columns [0, keep_w) of the one-sided spectrum, as a dense [batch, 2*keep_h, keep_w, 2] tensor."""
+
+    def __init__(self, direction: int, dims, batch: int, keep_h: int, keep_w: int):
+        L = lib()
+        L.trt_dft_plan_create_truncated.restype = c_int
+        L.trt_dft_plan_create_truncated.argtypes = [ctypes.POINTER(c_void_p), c_int, ctypes.POINTER(c_int64), c_int64, c_int64, c_int64]
+        self.direction = int(direction)
+        self.dims = tuple(int(d) for d in dims)
+        assert len(self.dims) == 2
+        self.batch = int(batch)
+        self.keep_h, self.keep_w = int(keep_h), int(keep_w)
+        self._h = c_void_p()
+        self._ws = None
+        arr = (c_int64 * 2)(*self.dims)
+        _check(L.trt_dft_plan_create_truncated(ctypes.byref(self._h), self.direction, arr, self.batch, self.keep_h, self.keep_w),
+               "trt_dft_plan_create_truncated")
+
+
+def kept_rows(H: int, keep_h: int):
+    """Row indices of the kept modes, in the order the truncated plans store them."""
+    return list(range(keep_h)) + list(range(H - keep_h, H))

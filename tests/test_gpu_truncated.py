@@ -1,0 +1,84 @@
+"""Truncated-mode rfft2 / irfft2 (trt_dft_plan_create_truncated) against the oracle: torch.fft.rfft2 + slicing, and
+torch.fft.irfft2 of the zero-padded spectrum (fp64 on the CPU; tolerance as everywhere, rel-L2 <= 1e-5).  Covers the
+fused kept-modes-only kernels (90 x 180) and the crop / zero-pad route of every other shape."""
+import pytest
+import torch
+
+from oracle import oracle as O
+
+pytestmark = pytest.mark.gpu
+
+CASES = [
+    # (batch, H, W, keep_h, keep_w)
+    (7, 90, 180, 12, 20), (300, 90, 180, 45, 91), (149, 90, 180, 1, 1), (5, 90, 180, 30, 33), (64, 90, 180, 20, 64),
+    (6, 128, 128, 16, 16), (3, 64, 64, 8, 12), (2, 720, 1440, 32, 48), (4, 34, 74, 5, 7), (3, 60, 120, 30, 61),
+]
+
+
+def oracle_truncated(x, kh, kw):
+    from trt_dft_plugins.capi import kept_rows
+    H = x.shape[-2]
+    full = torch.fft.rfft2(x.double(), dim=(-2, -1), norm="backward")
+    return torch.view_as_real(full[..., kept_rows(H, kh), :kw].contiguous())
+
+
+def oracle_padded_inverse(kept, H, W, kh, kw):
+    from trt_dft_plugins.capi import kept_rows
+    full = torch.zeros(kept.shape[0], H, W // 2 + 1, dtype=torch.complex128)
+    full[:, kept_rows(H, kh), :kw] = torch.view_as_complex(kept.double().contiguous())
+    return torch.fft.irfft2(full, s=(H, W), dim=(-2, -1), norm="backward")
+
+
+@pytest.mark.parametrize("batch,H,W,kh,kw", CASES)
+def test_truncated_forward_and_inverse(batch, H, W, kh, kw):
+    from trt_dft_plugins import capi
+    g = torch.Generator().manual_seed(batch * 1000 + kh)
+    x = torch.randn(batch, H, W, generator=g)
+    f = capi.TruncatedPlan(capi.FORWARD, (H, W), batch, kh, kw)
+    out = torch.full((batch, 2 * kh, kw, 2), float("nan"), device="cuda")
+    xd = x.cuda()
+    f.exec(xd, out)
+    torch.cuda.synchronize()
+    want = oracle_truncated(x, kh, kw)
+    assert not torch.isnan(out).any()
+    err = (out.cpu().double() - want).flatten(1).norm(dim=1) / want.flatten(1).norm(dim=1)
+    assert float(err.max()) <= 1e-5, f"worst image {int(err.argmax())}: {float(err.max()):.3e}"
+    assert torch.equal(xd.cpu(), x)                                      # input never written
+    # inverse on a random (not Hermitian-consistent) kept block
+    s = torch.randn(batch, 2 * kh, kw, 2, generator=g)
+    i = capi.TruncatedPlan(capi.INVERSE, (H, W), batch, kh, kw)
+    back = torch.full((batch, H, W), float("nan"), device="cuda")
+    i.exec(s.cuda(), back)
+    torch.cuda.synchronize()
+    want_x = oracle_padded_inverse(s, H, W, kh, kw)
+    err = (back.cpu().double() - want_x).flatten(1).norm(dim=1) / want_x.flatten(1).norm(dim=1)
+    assert float(err.max()) <= 1e-5, f"worst image {int(err.argmax())}: {float(err.max()):.3e}"
+
+
+def test_truncated_plan_describes_its_route_and_rejects_bad_sizes():
+    from trt_dft_plugins import capi
+    p = capi.TruncatedPlan(capi.FORWARD, (90, 180), 8, 12, 20)
+    assert "kept modes only" in p.describe()[1] and p.workspace_bytes == 0 and p.num_launches == 1
+    assert p.input_floats == 8 * 90 * 180 and p.output_floats == 8 * 24 * 20 * 2
+    q = capi.TruncatedPlan(capi.INVERSE, (128, 128), 8, 16, 16)
+    assert "zero-pad" in q.describe()[1] and q.workspace_bytes >= 8 * 128 * 65 * 8
+    for kh, kw in ((0, 4), (46, 4), (4, 0), (4, 92)):
+        with pytest.raises(capi.DftError):
+            capi.TruncatedPlan(capi.FORWARD, (90, 180), 8, kh, kw)
+    e = capi.TruncatedPlan(capi.FORWARD, (90, 180), 0, 4, 4)
+    assert e.num_launches == 0
+
+
+def test_full_keep_equals_the_ordinary_transform():
+    from trt_dft_plugins import capi
+    torch.manual_seed(3)
+    x = torch.randn(200, 90, 180, device="cuda")
+    full = capi.rfftn(x, 2)
+    t = torch.empty(200, 90, 91, 2, device="cuda")
+    capi.TruncatedPlan(capi.FORWARD, (90, 180), 200, 45, 91).exec(x, t)
+    torch.cuda.synchronize()
+    assert torch.equal(t, full)                 # same arithmetic, only the store differs
+    back = torch.empty_like(x)
+    capi.TruncatedPlan(capi.INVERSE, (90, 180), 200, 45, 91).exec(full, back)
+    torch.cuda.synchronize()
+    assert torch.equal(back, capi.irfftn(full, 2))
