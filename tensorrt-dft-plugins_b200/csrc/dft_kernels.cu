@@ -205,7 +205,10 @@ int trt_dft_plan_create_truncated(trt_dft_plan_t* plan_out, int direction, const
     }
     char desc[192];
     const SpecEntry* e = (batch > 0 && !getenv("TRT_DFT_NO_SPEC")) ? find_spec((int)H, (int)W) : nullptr;
-    if (e && e->trunc_fwd && e->trunc_inv) {
+    // The fused kernels pay for compacting / expanding the kept block in shared memory; measured on B200 they win while
+    // the block is at most ~60 % of the spectrum, beyond that the full kernels plus a crop / zero-pad pass are faster.
+    const bool small_keep = 2 * keep_h * keep_w * 10 <= H * MO * 6 || getenv("TRT_DFT_TRUNC_FUSED");
+    if (e && e->trunc_fwd && e->trunc_inv && small_keep) {
         pl->t_fwd = e->trunc_fwd;
         pl->t_inv = e->trunc_inv;
         pl->t_threads = e->NT;

@@ -31,6 +31,7 @@
 #include <stdint.h>
 
 #include "dft_butterflies.cuh"
+#include "dft_phases.cuh"
 #include "dft_pipe2d.cuh"
 
 namespace dft {
@@ -60,6 +61,10 @@ struct RegCfg {
     static constexpr int STAGE_F = (MO * H * 8 + 127) / 128 * 128;     // transposed [MO][H]
     static constexpr int PI = (H % 2 == 0) ? H + 1 : H;                // inverse transpose pitch: odd
     static constexpr int STAGE_I = (MO * PI * 8 + 127) / 128 * 128;
+    // truncated inverse: the kept block [2*kh][kw] is loaded so that it ENDS at element TAIL of the stage (even: 16-byte
+    // aligned start), which lets it be expanded in place into the spectrum tile [q][k] front to back
+    static constexpr int TAIL = (MO * PI) / 2 * 2;
+    static_assert(TAIL >= H * MO + 2 && TAIL * 8 <= STAGE_I, "kept block must fit behind the spectrum tile's expansion front");
     static constexpr int NPAIR = (Mh - 1) / 2;
     static constexpr int NTAB_I = 2 * (NPAIR + 1);         // inverse merge twiddles, per parity
     static constexpr int NTAB_F = 2 * (NPAIR + 1);         // forward split twiddles, per parity
@@ -211,25 +216,39 @@ struct MergeTable {
 template <class C>
 __device__ const MergeTable<C> g_merge_table{};
 
+// ---- truncated modes (spectral layers keep a corner of low modes) --------------------------------------------------
+// FNO / AFNO style layers use only the modes rows q in [0, kh) u [H - kh, H), columns k in [0, kw) of the one-sided
+// spectrum.  The truncated forward never writes the discarded modes and the truncated inverse never reads them: the
+// kept block [2*kh][kw] travels as ONE dense bulk copy (16*kh*kw bytes per image instead of H*MO*8), so the complex
+// side of the traffic shrinks by H*MO / (2*kh*kw).  Arithmetic as in the full kernels; columns k >= kw are skipped.
+
+// kept-row index of spectrum row q, or -1
+__device__ __forceinline__ int kept_row(int q, int H, int kh) { return q < kh ? q : (q >= H - kh ? q - (H - 2 * kh) : -1); }
+
+
+
 // I/O warp of group g (one thread): for the group's images in order, wait until the result is staged, store
 // it, and refill the stage.  The store leaves in KP pieces (one bulk group each) and piece j of the next
 // image is requested as soon as pieces 0..j have been read out, so the stage's drain and its refill overlap
 // instead of adding up -- a stage in transit is what a group waits for.  done[g][s] is private to the
 // (group, stage) pair, whose uses are LCM images apart, so its phase parity is (it / LCM) & 1.
-template <class C, int STAGE, int LOAD_BYTES, int STORE_BYTES>
+// LOAD_BYTES / STORE_BYTES are compile-time constants in the full kernels (everything below folds) and run-time values in
+// the truncated-mode kernels, where one side is the small kept block.
+template <class C, int STAGE>
 __device__ __forceinline__ void io_loop(int g, const unsigned char* __restrict__ in, unsigned char* __restrict__ out, long long nimg,
-                                        unsigned char* stages, unsigned full0, unsigned done0)
+                                        unsigned char* stages, unsigned full0, unsigned done0, const int LOAD_BYTES, const int STORE_BYTES,
+                                        const int LOAD_AT = 0 /* byte offset of the loaded block inside its stage */)
 {
     constexpr int NG = C::NG, NS = C::NS, KP = 4;
-    constexpr int SP = (STORE_BYTES / KP + 15) / 16 * 16;      // store piece (the last one is shorter)
-    constexpr int LP0 = (LOAD_BYTES / KP) / 16 * 16;
-    constexpr int LP = LP0 < SP ? LP0 : SP;                    // load piece  (the last one is longer)
-    static_assert(LP <= SP, "load piece j must lie inside store pieces 0..j");
+    const int SP = (STORE_BYTES / KP + 15) / 16 * 16;          // store piece (the last one is shorter, possibly empty)
+    const int LP0 = (LOAD_BYTES / KP) / 16 * 16;
+    const int LP = LP0 < SP ? LP0 : SP;                        // load piece  (the last one is longer): piece j lies inside store pieces 0..j
     auto load_piece = [&](long long tile, int s, int j) {
         const unsigned off = (unsigned)(j * LP);
         const unsigned bytes = (j == KP - 1) ? (unsigned)(LOAD_BYTES - (KP - 1) * LP) : (unsigned)LP;
+        if (bytes == 0) return;
         asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
-                         pipe::s32(stages + (size_t)s * STAGE) + off),
+                         pipe::s32(stages + (size_t)s * STAGE) + (unsigned)LOAD_AT + off),
                      "l"(in + tile * (long long)LOAD_BYTES + off), "r"(bytes), "r"(full0 + 8 * s)
                      : "memory");
     };
@@ -250,12 +269,13 @@ __device__ __forceinline__ void io_loop(int g, const unsigned char* __restrict__
         pipe::mbar_wait(done0 + 8 * (g * NS + s), (unsigned)((it / C::LCM) & 1));
 #pragma unroll
         for (int j = 0; j < KP; ++j) {
-            const unsigned off = (unsigned)(j * SP);
-            const unsigned bytes = (j == KP - 1) ? (unsigned)(STORE_BYTES - (KP - 1) * SP) : (unsigned)SP;
-            asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(out + tile * (long long)STORE_BYTES + off),
-                         "r"(pipe::s32(stages + (size_t)s * STAGE) + off), "r"(bytes)
-                         : "memory");
-            asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+            const int off = j * SP < STORE_BYTES ? j * SP : STORE_BYTES;
+            const int end = (j == KP - 1 || (j + 1) * SP > STORE_BYTES) ? STORE_BYTES : (j + 1) * SP;
+            if (end > off)
+                asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(out + tile * (long long)STORE_BYTES + off),
+                             "r"(pipe::s32(stages + (size_t)s * STAGE) + (unsigned)off), "r"((unsigned)(end - off))
+                             : "memory");
+            asm volatile("cp.async.bulk.commit_group;" ::: "memory");       // (an empty group completes at once)
         }
         const long long next = tile + (long long)NS * gridDim.x;   // the image that uses this stage next
         if (next < nimg) {
@@ -277,11 +297,14 @@ __device__ __forceinline__ void io_loop(int g, const unsigned char* __restrict__
 }  // namespace reg2d
 
 // ---- forward ---------------------------------------------------------------------------------
-template <class C>
-__global__ void __launch_bounds__(C::THREADS, 1)
-    reg_rfft2_kernel(const float* __restrict__ in, float* __restrict__ out, long long nimg,
-                     const float2* __restrict__ /*tables*/, float /*scale*/)
+// TR: truncated modes (see above io_loop): only rows [0, kh) u [H - kh, H), columns [0, kw) of the spectrum leave
+// the kernel, as a dense [2*kh][kw] block; columns past kw are not transformed at all.
+template <class C, bool TR>
+__device__ __forceinline__ void reg_rfft2_body(const float* __restrict__ in, float* __restrict__ out, long long nimg, const int kh, const int kw)
 {
+    static_assert(!TR || C::IOW, "the truncated kernels use the I/O-warp layout");
+    // (truncated: the two halves of an image's work are no longer equal, so the groups run free instead of taking turns)
+    constexpr int PPX = TR ? 0 : C::PP;
     constexpr int H = C::H, M = C::M, MO = C::MO, GT = C::GT, NG = C::NG, NS = C::NS, WPP = C::WPP;
     extern __shared__ __align__(128) unsigned char smem_raw[];
     unsigned char* stages = smem_raw;
@@ -302,8 +325,9 @@ __global__ void __launch_bounds__(C::THREADS, 1)
     if constexpr (C::IOW) {
         if (tid >= NG * GT) {
             if ((tid & 31) == 0)
-                reg2d::io_loop<C, C::STAGE_F, C::TILE_F, C::TILE_I>((tid - NG * GT) >> 5, reinterpret_cast<const unsigned char*>(in),
-                                                                    reinterpret_cast<unsigned char*>(out), nimg, stages, full0, done0);
+                reg2d::io_loop<C, C::STAGE_F>((tid - NG * GT) >> 5, reinterpret_cast<const unsigned char*>(in),
+                                              reinterpret_cast<unsigned char*>(out), nimg, stages, full0, done0, C::TILE_F,
+                                              TR ? 16 * kh * kw : C::TILE_I);
             return;
         }
     }
@@ -341,13 +365,13 @@ __global__ void __launch_bounds__(C::THREADS, 1)
         }
     };
 
-    if (C::PP != 0 && g == 1) asm volatile("bar.arrive %0, %1;" ::"r"(3), "r"(2 * GT) : "memory");   // group 0 goes first
+    if (PPX != 0 && g == 1) asm volatile("bar.arrive %0, %1;" ::"r"(3), "r"(2 * GT) : "memory");   // group 0 goes first
     long long it = g;
     for (long long tile = blockIdx.x + (long long)g * gridDim.x; tile < nimg; tile += (long long)NG * gridDim.x, it += NG) {
         const int s = (int)(it % NS);
         float2* buf = reinterpret_cast<float2*>(stages + (size_t)s * C::STAGE_F);
         DFT_TR(it, 0);
-        if (C::PP == 1) pipe::group_sync(3 + g, 2 * GT);     // my turn
+        if (PPX == 1) pipe::group_sync(3 + g, 2 * GT);     // my turn
         pipe::mbar_wait(full0 + 8 * s, (unsigned)((it / NS) & 1));
         DFT_TR(it, 1);
 
@@ -363,17 +387,47 @@ __global__ void __launch_bounds__(C::THREADS, 1)
             reg2d::split_store<C>(z, buf + lrow, p, tws + p * (C::NPAIR + 1));
         }
         DFT_TR(it, 4);
-        if (C::PP == 1) asm volatile("bar.arrive %0, %1;" ::"r"(4 - g), "r"(2 * GT) : "memory");   // the other group's turn
+        if (PPX == 1) asm volatile("bar.arrive %0, %1;" ::"r"(4 - g), "r"(2 * GT) : "memory");   // the other group's turn
         pipe::group_sync(bar_id, GT);
         DFT_TR(it, 5);
         // columns: column k is a contiguous line of the transposed tile; the spectrum [q][k] overwrites it
-        {
+        // (truncated: a warp none of whose columns is kept skips the column transform)
+        if (!TR || (warp - p * WPP) * 32 < kw) {
             float2 y[C::Hh];
             reg2d::load_fold<C::Hh>(y, reinterpret_cast<const float4*>(buf) + lcol * (H / 2), sg);
             DFT_TR(it, 6);
             reg2d::line_fft<C::CA, C::CB>(y);
             pipe::group_sync(bar_id, GT);               // every column has been read
             reg2d::store_cols<C>(y, buf + lcol, p);
+        } else {
+            pipe::group_sync(bar_id, GT);
+        }
+        {
+            if constexpr (TR) {
+                // Compact the kept modes, rows [0, kh) u [H - kh, H) x columns [0, kw) of the tile [q][k] (pitch MO), into
+                // a dense block at the start of the stage, GT elements at a time: element e comes from an index >= e, so
+                // reading a chunk, a barrier, and writing it never overwrites anything that is still to be read.
+                pipe::group_sync(bar_id, GT);           // the spectrum tile is complete
+                const int total = 2 * kh * kw;
+                const unsigned kwm = dft::magic_of((unsigned)kw);
+                constexpr int EPT = 4;                  // elements per thread and chunk
+                for (int base = 0; base < total; base += EPT * GT) {
+                    float2 v[EPT];
+#pragma unroll
+                    for (int j = 0; j < EPT; ++j) {
+                        const int e = base + j * GT + gt;
+                        const int ec = e < total ? e : total - 1;
+                        const int qi = dft::fdiv(ec, kwm), k = ec - qi * kw;
+                        v[j] = buf[(qi < kh ? qi : qi + (H - 2 * kh)) * MO + k];
+                    }
+                    pipe::group_sync(bar_id, GT);
+#pragma unroll
+                    for (int j = 0; j < EPT; ++j) {
+                        const int e = base + j * GT + gt;
+                        if (e < total) buf[e] = v[j];
+                    }
+                }
+            }
             pipe::fence_async();
             if constexpr (C::IOW) {
                 __syncwarp();
@@ -398,12 +452,27 @@ __global__ void __launch_bounds__(C::THREADS, 1)
     if (!C::IOW && gt == 0) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
 }
 
-// ---- inverse ---------------------------------------------------------------------------------
 template <class C>
 __global__ void __launch_bounds__(C::THREADS, 1)
-    reg_irfft2_kernel(const float* __restrict__ in, float* __restrict__ out, long long nimg,
-                      const float2* __restrict__ /*tables*/, float scale)
+    reg_rfft2_kernel(const float* __restrict__ in, float* __restrict__ out, long long nimg,
+                     const float2* __restrict__ /*tables*/, float /*scale*/)
 {
+    reg_rfft2_body<C, false>(in, out, nimg, 0, 0);
+}
+template <class C>
+__global__ void __launch_bounds__(C::THREADS, 1)
+    reg_rfft2_trunc_kernel(const float* __restrict__ in, float* __restrict__ out, long long nimg, int kh, int kw)
+{
+    reg_rfft2_body<C, true>(in, out, nimg, kh, kw);
+}
+
+// ---- inverse ---------------------------------------------------------------------------------
+template <class C, bool TR>
+__device__ __forceinline__ void reg_irfft2_body(const float* __restrict__ in, float* __restrict__ out, long long nimg, float scale,
+                                                const int kh, const int kw)
+{
+    static_assert(!TR || C::IOW, "the truncated kernels use the I/O-warp layout");
+    constexpr int PPX = TR ? 0 : C::PP;
     constexpr int H = C::H, M = C::M, Mh = C::Mh, MO = C::MO, PI = C::PI, GT = C::GT, NG = C::NG, NS = C::NS, WPP = C::WPP;
     constexpr int NTW = C::NPAIR + 1;
     extern __shared__ __align__(128) unsigned char smem_raw[];
@@ -426,8 +495,9 @@ __global__ void __launch_bounds__(C::THREADS, 1)
     if constexpr (C::IOW) {
         if (tid >= NG * GT) {
             if ((tid & 31) == 0)
-                reg2d::io_loop<C, C::STAGE_I, C::TILE_I, C::TILE_F>((tid - NG * GT) >> 5, reinterpret_cast<const unsigned char*>(in),
-                                                                    reinterpret_cast<unsigned char*>(out), nimg, stages, full0, done0);
+                reg2d::io_loop<C, C::STAGE_I>((tid - NG * GT) >> 5, reinterpret_cast<const unsigned char*>(in),
+                                              reinterpret_cast<unsigned char*>(out), nimg, stages, full0, done0,
+                                              TR ? 16 * kh * kw : C::TILE_I, C::TILE_F, TR ? (C::TAIL - 2 * kh * kw) * 8 : 0);
             return;
         }
     }
@@ -466,17 +536,63 @@ __global__ void __launch_bounds__(C::THREADS, 1)
         }
     };
 
-    if (C::PP != 0 && g == 1) asm volatile("bar.arrive %0, %1;" ::"r"(3), "r"(2 * GT) : "memory");   // group 0 goes first
+    if (PPX != 0 && g == 1) asm volatile("bar.arrive %0, %1;" ::"r"(3), "r"(2 * GT) : "memory");   // group 0 goes first
     long long it = g;
     for (long long tile = blockIdx.x + (long long)g * gridDim.x; tile < nimg; tile += (long long)NG * gridDim.x, it += NG) {
         const int s = (int)(it % NS);
         float2* buf = reinterpret_cast<float2*>(stages + (size_t)s * C::STAGE_I);
-        if (C::PP == 1) pipe::group_sync(3 + g, 2 * GT);     // my turn
+        if (PPX == 1) pipe::group_sync(3 + g, 2 * GT);     // my turn
         pipe::mbar_wait(full0 + 8 * s, (unsigned)((it / NS) & 1));
 
         // columns: column k of the spectrum [q][k] -> registers; the transposed result [k][row], pitch PI,
         // overwrites the stage
-        {
+        if constexpr (TR) {
+            // The kept block [2*kh][kw] sits at elements [TAIL - total, TAIL) of the stage.  Expand it in place into the
+            // spectrum tile [q][k] (pitch MO), zeros everywhere else: an element's place in the tile never lies behind
+            // its place in the block, so chunks go front to back (read, barrier, write).
+            const int total = 2 * kh * kw, blk0 = C::TAIL - total;
+            const float4 z4 = float4{0.f, 0.f, 0.f, 0.f};
+            for (int i = gt; i < blk0 / 2; i += GT) reinterpret_cast<float4*>(buf)[i] = z4;      // ahead of the block: all zero for now
+            pipe::group_sync(bar_id, GT);
+            const unsigned kwm = dft::magic_of((unsigned)kw);
+            constexpr int EPT = 4;
+            for (int base = 0; base < total; base += EPT * GT) {
+                float2 v[EPT];
+#pragma unroll
+                for (int j = 0; j < EPT; ++j) {
+                    const int e = base + j * GT + gt;
+                    v[j] = buf[blk0 + (e < total ? e : total - 1)];
+                }
+                pipe::group_sync(bar_id, GT);
+#pragma unroll
+                for (int j = 0; j < EPT; ++j) {
+                    const int e = base + j * GT + gt;
+                    if (e < total) {
+                        const int qi = dft::fdiv(e, kwm), k = e - qi * kw;
+                        buf[(qi < kh ? qi : qi + (H - 2 * kh)) * MO + k] = v[j];
+                    }
+                }
+            }
+            pipe::group_sync(bar_id, GT);
+            // what is left of the block's own footprint and is not a kept mode goes back to zero
+            constexpr unsigned mom = dft::magic_u32((unsigned)MO);
+            for (int pos = blk0 + gt; pos < H * MO; pos += GT) {
+                const int q = dft::fdiv(pos, mom), k = pos - q * MO;
+                if (!(k < kw && (q < kh || q >= H - kh))) buf[pos] = float2{0.f, 0.f};
+            }
+            pipe::group_sync(bar_id, GT);
+        }
+        if (TR && (warp - pc * WPP) * 32 >= kw) {
+            // truncated: every column of this warp is zero, and so is its transform
+            refill();
+            pipe::group_sync(bar_id, GT);
+            float2* dst = buf + lcol * PI;
+            static_for<0, C::Hh>([&](auto kc) {
+                constexpr int k2 = decltype(kc)::value;
+                constexpr int r0 = ((C::Hh + 1) * k2) % H;                      // parity 0 writes row r0, parity 1 row (r0 + Hh) mod H
+                dst[pc ? (r0 + C::Hh) % H : r0] = float2{0.f, 0.f};
+            });
+        } else {
             float2 y[C::Hh];
             reg2d::load_fold_rev<C::Hh, MO>(y, buf + lcol, sgc);
             refill();                                   // the previous image's store has long since drained
@@ -485,7 +601,7 @@ __global__ void __launch_bounds__(C::THREADS, 1)
             if (pc == 0) reg2d::store_rows_t<C, 0>(y, buf + lcol * PI);
             else reg2d::store_rows_t<C, 1>(y, buf + lcol * PI);
         }
-        if (C::PP == 1) asm volatile("bar.arrive %0, %1;" ::"r"(4 - g), "r"(2 * GT) : "memory");   // the other group's turn
+        if (PPX == 1) asm volatile("bar.arrive %0, %1;" ::"r"(4 - g), "r"(2 * GT) : "memory");   // the other group's turn
         pipe::group_sync(bar_id, GT);
         // rows: Hermitian merge of this thread's parity -> FFT -> radix-2 step across the half warps
         {
@@ -546,230 +662,18 @@ __global__ void __launch_bounds__(C::THREADS, 1)
     if (!C::IOW && gt == 0) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
 }
 
-// ---- truncated modes (spectral layers keep a corner of low modes) --------------------------------------------------
-// FNO / AFNO style layers use only the modes rows q in [0, kh) u [H - kh, H), columns k in [0, kw) of the one-sided
-// spectrum.  The truncated forward never writes the discarded modes and the truncated inverse never reads them: the
-// kept block [2*kh][kw] travels as ONE dense bulk copy (16*kh*kw bytes per image instead of H*MO*8), so the complex
-// side of the traffic shrinks by H*MO / (2*kh*kw).  Arithmetic as in the full kernels; columns k >= kw are skipped.
-namespace reg2d {
-
-// kept-row index of spectrum row q, or -1
-__device__ __forceinline__ int kept_row(int q, int H, int kh) { return q < kh ? q : (q >= H - kh ? q - (H - 2 * kh) : -1); }
-
-// I/O warp of group g for the truncated kernels: loads of LOADB bytes and stores of STOREB bytes per image, each as one
-// bulk copy (the small side is a few KB; the large side is the dense real image).  A stage is refilled once its store
-// has been read out of shared memory.
-template <class C, int STAGE>
-__device__ __forceinline__ void io_loop_trunc(int g, const unsigned char* __restrict__ in, unsigned char* __restrict__ out, long long nimg,
-                                              unsigned char* stages, unsigned full0, unsigned done0, unsigned loadb, unsigned storeb)
-{
-    constexpr int NG = C::NG, NS = C::NS;
-    auto load = [&](long long tile, int s) {
-        asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(full0 + 8 * s), "r"(loadb) : "memory");
-        asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
-                         pipe::s32(stages + (size_t)s * STAGE)),
-                     "l"(in + tile * (long long)loadb), "r"(loadb), "r"(full0 + 8 * s)
-                     : "memory");
-    };
-    if (g == 0)
-        for (int s = 0; s < NS; ++s) {
-            const long long tile = blockIdx.x + s * (long long)gridDim.x;
-            if (tile >= nimg) break;
-            load(tile, s);
-        }
-    long long it = g;
-    for (long long tile = blockIdx.x + (long long)g * gridDim.x; tile < nimg; tile += (long long)NG * gridDim.x, it += NG) {
-        const int s = (int)(it % NS);
-        pipe::mbar_wait(done0 + 8 * (g * NS + s), (unsigned)((it / C::LCM) & 1));
-        asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(out + tile * (long long)storeb),
-                     "r"(pipe::s32(stages + (size_t)s * STAGE)), "r"(storeb)
-                     : "memory");
-        asm volatile("cp.async.bulk.commit_group;" ::: "memory");
-        const long long next = tile + (long long)NS * gridDim.x;
-        if (next < nimg) {
-            asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
-            load(next, s);
-        }
-    }
-    asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
-}
-
-}  // namespace reg2d
-
 template <class C>
 __global__ void __launch_bounds__(C::THREADS, 1)
-    reg_rfft2_trunc_kernel(const float* __restrict__ in, float* __restrict__ out, long long nimg, int kh, int kw)
+    reg_irfft2_kernel(const float* __restrict__ in, float* __restrict__ out, long long nimg,
+                      const float2* __restrict__ /*tables*/, float scale)
 {
-    static_assert(C::IOW, "the truncated kernels use the I/O-warp layout");
-    constexpr int H = C::H, M = C::M, MO = C::MO, GT = C::GT, NG = C::NG, NS = C::NS, WPP = C::WPP, Hh = C::Hh;
-    extern __shared__ __align__(128) unsigned char smem_raw[];
-    unsigned char* stages = smem_raw;
-    float2* tws = reinterpret_cast<float2*>(smem_raw + NS * C::STAGE_F);
-    const unsigned full0 = pipe::s32(tws + C::NTAB_F);
-    const unsigned done0 = full0 + 8 * NS;
-    const int tid = threadIdx.x;
-    for (int i = tid; i < C::NTAB_F; i += C::THREADS) tws[i] = float2{reg2d::g_split_table<C>.x[i], reg2d::g_split_table<C>.y[i]};
-    if (tid == 0) {
-        for (int s = 0; s < NS; ++s) pipe::mbar_init(full0 + 8 * s, 1);
-        for (int s = 0; s < NG * NS; ++s) pipe::mbar_init(done0 + 8 * s, GT / 32);
-        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
-        pipe::fence_async();
-    }
-    __syncthreads();
-    if (tid >= NG * GT) {
-        if ((tid & 31) == 0)
-            reg2d::io_loop_trunc<C, C::STAGE_F>((tid - NG * GT) >> 5, reinterpret_cast<const unsigned char*>(in), reinterpret_cast<unsigned char*>(out),
-                                                nimg, stages, full0, done0, (unsigned)C::TILE_F, (unsigned)(16 * kh * kw));
-        return;
-    }
-    const int g = tid / GT;
-    const int gt = tid - g * GT;
-    const int warp = gt >> 5;
-    const int p = warp / WPP;
-    const int line = (warp - p * WPP) * 32 + (gt & 31);
-    const float sg = p ? -1.f : 1.f;
-    const int lrow = line < H ? line : H - 1, lcol = line < MO ? line : MO - 1;
-    const bool col_warp_live = (warp - p * WPP) * 32 < kw;      // this warp holds at least one kept column
-    const int bar_id = 1 + g;
-    long long it = g;
-    for (long long tile = blockIdx.x + (long long)g * gridDim.x; tile < nimg; tile += (long long)NG * gridDim.x, it += NG) {
-        const int s = (int)(it % NS);
-        float2* buf = reinterpret_cast<float2*>(stages + (size_t)s * C::STAGE_F);
-        pipe::mbar_wait(full0 + 8 * s, (unsigned)((it / NS) & 1));
-        {
-            float2 z[C::Mh];
-            reg2d::load_fold<C::Mh>(z, reinterpret_cast<const float4*>(buf) + lrow * (M / 2), sg);
-            pipe::group_sync(bar_id, GT);
-            reg2d::line_fft<C::RA, C::RB>(z);
-            reg2d::split_store<C>(z, buf + lrow, p, tws + p * (C::NPAIR + 1));
-        }
-        pipe::group_sync(bar_id, GT);
-        {
-            float2 y[Hh];
-            if (col_warp_live) {
-                reg2d::load_fold<Hh>(y, reinterpret_cast<const float4*>(buf) + lcol * (H / 2), sg);
-                reg2d::line_fft<C::CA, C::CB>(y);
-            }
-            pipe::group_sync(bar_id, GT);               // every column has been read: the kept block may overwrite the tile
-            if (col_warp_live && line < kw) {
-                float2* dst = buf + line;               // kept block, dense [2*kh][kw]
-                static_for<0, Hh>([&](auto kc) {
-                    constexpr int k2 = decltype(kc)::value;
-                    constexpr int c0 = ((Hh + 1) * k2) % H;
-                    const int q = (c0 < Hh) ? c0 + Hh * p : c0 - Hh * p;      // output row of Y[k2]
-                    const int qi = reg2d::kept_row(q, H, kh);
-                    if (qi >= 0) dst[qi * kw] = y[k2];
-                });
-            }
-            pipe::fence_async();
-            __syncwarp();
-            if ((gt & 31) == 0) pipe::mbar_arrive(done0 + 8 * (g * NS + s));
-        }
-    }
+    reg_irfft2_body<C, false>(in, out, nimg, scale, 0, 0);
 }
-
 template <class C>
 __global__ void __launch_bounds__(C::THREADS, 1)
     reg_irfft2_trunc_kernel(const float* __restrict__ in, float* __restrict__ out, long long nimg, int kh, int kw, float scale)
 {
-    static_assert(C::IOW, "the truncated kernels use the I/O-warp layout");
-    constexpr int H = C::H, M = C::M, Mh = C::Mh, MO = C::MO, PI = C::PI, GT = C::GT, NG = C::NG, NS = C::NS, WPP = C::WPP, Hh = C::Hh;
-    constexpr int NTW = C::NPAIR + 1;
-    extern __shared__ __align__(128) unsigned char smem_raw[];
-    unsigned char* stages = smem_raw;
-    float2* twm = reinterpret_cast<float2*>(smem_raw + NS * C::STAGE_I);
-    const unsigned full0 = pipe::s32(twm + C::NTAB_I);
-    const unsigned done0 = full0 + 8 * NS;
-    const int tid = threadIdx.x;
-    for (int i = tid; i < C::NTAB_I; i += C::THREADS)
-        twm[i] = float2{scale * reg2d::g_merge_table<C>.x[i], scale * reg2d::g_merge_table<C>.y[i]};
-    if (tid == 0) {
-        for (int s = 0; s < NS; ++s) pipe::mbar_init(full0 + 8 * s, 1);
-        for (int s = 0; s < NG * NS; ++s) pipe::mbar_init(done0 + 8 * s, GT / 32);
-        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
-        pipe::fence_async();
-    }
-    __syncthreads();
-    if (tid >= NG * GT) {
-        if ((tid & 31) == 0)
-            reg2d::io_loop_trunc<C, C::STAGE_I>((tid - NG * GT) >> 5, reinterpret_cast<const unsigned char*>(in), reinterpret_cast<unsigned char*>(out),
-                                                nimg, stages, full0, done0, (unsigned)(16 * kh * kw), (unsigned)C::TILE_F);
-        return;
-    }
-    const int g = tid / GT;
-    const int gt = tid - g * GT;
-    const int warp = gt >> 5, lane = gt & 31;
-    const int pc = warp / WPP;
-    const int col = (warp - pc * WPP) * 32 + lane;
-    const int lcol = col < MO ? col : MO - 1;
-    const float sgc = pc ? -1.f : 1.f;
-    const int pr = lane >> 4;
-    const int row = warp * 16 + (lane & 15);
-    const int lrow = row < H ? row : H - 1;
-    const float sgr = pr ? -1.f : 1.f;
-    const int bar_id = 1 + g;
-    long long it = g;
-    for (long long tile = blockIdx.x + (long long)g * gridDim.x; tile < nimg; tile += (long long)NG * gridDim.x, it += NG) {
-        const int s = (int)(it % NS);
-        float2* buf = reinterpret_cast<float2*>(stages + (size_t)s * C::STAGE_I);
-        pipe::mbar_wait(full0 + 8 * s, (unsigned)((it / NS) & 1));
-        {
-            // columns: kept rows of column k from the dense kept block [2*kh][kw]; every other mode is zero
-            float2 y[Hh];
-            const bool live = lcol < kw;
-            const float2* src = buf + (live ? lcol : 0);
-            static_for<0, Hh>([&](auto nc) {
-                constexpr int n2 = decltype(nc)::value;
-                constexpr int ia = (H - 2 * n2) % H, ib = (2 * H - Hh - 2 * n2) % H;      // index-reversed line (see load_fold_rev)
-                const int qa = reg2d::kept_row(ia, H, kh), qb = reg2d::kept_row(ib, H, kh);
-                float2 a = float2{0.f, 0.f}, b = float2{0.f, 0.f};
-                if (live && qa >= 0) a = src[qa * kw];
-                if (live && qb >= 0) b = src[qb * kw];
-                y[n2] = float2{fmaf(sgc, b.x, a.x), fmaf(sgc, b.y, a.y)};
-            });
-            pipe::group_sync(bar_id, GT);               // the kept block has been read: the transposed tile may overwrite it
-            reg2d::line_fft<C::CA, C::CB>(y);
-            if (pc == 0) reg2d::store_rows_t<C, 0>(y, buf + lcol * PI);
-            else reg2d::store_rows_t<C, 1>(y, buf + lcol * PI);
-        }
-        pipe::group_sync(bar_id, GT);
-        {
-            float2 z[Mh];
-            const float2* pa = buf + lrow + pr * (Mh * PI);
-            const float2* pb = buf + lrow - pr * (Mh * PI);
-            const float2* tw = twm + pr * NTW;
-            {
-                const float2 u = pa[0], v = pb[M * PI];
-                z[0] = float2{scale * (u.x + v.x), scale * (pr ? -(u.y + v.y) : (u.x - v.x))};
-            }
-            static_for<1, NTW>([&](auto kc) {
-                constexpr int k2 = decltype(kc)::value;
-                const float2 a = pa[2 * k2 * PI], b = pb[(M - 2 * k2) * PI];
-                const float2 t = tw[k2];
-                const float sx = a.x + b.x, sy = a.y - b.y;
-                const float dx = a.x - b.x, dy = a.y + b.y;
-                const float ux = t.x * dx - t.y * dy, uy = t.x * dy + t.y * dx;
-                z[Mh - k2] = float2{fmaf(scale, sx, ux), fmaf(scale, sy, uy)};
-                z[k2] = float2{fmaf(scale, sx, -ux), fmaf(-scale, sy, uy)};
-            });
-            pipe::group_sync(bar_id, GT);
-            reg2d::line_fft<C::RA, C::RB>(z);
-            float2* op = buf + lrow * M + pr * Mh;
-            float2* om = buf + lrow * M - pr * Mh;
-            static_for<0, Mh>([&](auto nc) {
-                constexpr int n2 = decltype(nc)::value;
-                constexpr int c0 = ((Mh + 1) * n2) % M;
-                const float ox = __shfl_xor_sync(0xffffffffu, z[n2].x, 16);
-                const float oy = __shfl_xor_sync(0xffffffffu, z[n2].y, 16);
-                const float2 r = float2{fmaf(sgr, z[n2].x, ox), fmaf(sgr, z[n2].y, oy)};
-                if constexpr (c0 < Mh) op[c0] = r;
-                else om[c0] = r;
-            });
-            pipe::fence_async();
-            __syncwarp();
-            if ((gt & 31) == 0) pipe::mbar_arrive(done0 + 8 * (g * NS + s));
-        }
-    }
+    reg_irfft2_body<C, true>(in, out, nimg, scale, kh, kw);
 }
 
 #endif  // __CUDACC__
