@@ -272,6 +272,8 @@ DFT_HD void dft_reg(float2 (&v)[R])
         dft_pfa<3, 5>(v);
     } else if constexpr (R == 16) {
         dft_ct<4, 4>(v);
+    } else if constexpr (R == 32) {
+        dft_ct<4, 8>(v);
     } else {
         static_assert(R == 1, "unsupported radix");
     }

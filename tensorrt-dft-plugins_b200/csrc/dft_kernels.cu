@@ -306,8 +306,9 @@ static int realize_plan(trt_dft_plan_s* pl, trt_dft_plan_t* plan_out)
         if (l.perm_row_id >= 0) r.kp.perm_row = (const int*)(base + perm_off[l.perm_row_id]);
         if (l.perm_col_id >= 0) r.kp.perm_col = (const int*)(base + perm_off[l.perm_col_id]);
         if (l.tw_four_id >= 0) r.kp.tw_four = (const float2*)(base + tw_off[l.tw_four_id]);
-        if (r.kp.mode != dft::MODE_C2C_COLS) r.kp.threads = 256;
-        r.fn = dft::tile_kernel_for(r.kp.mode, r.kp.threads);
+        const bool small_rows = r.kp.mode == dft::MODE_SMALL_ROWS_R2C || r.kp.mode == dft::MODE_SMALL_ROWS_C2R;
+        if (r.kp.mode != dft::MODE_C2C_COLS && !small_rows) r.kp.threads = 256;
+        r.fn = small_rows ? dft::small_rows_kernel_for(r.kp.mode, r.kp.M) : dft::tile_kernel_for(r.kp.mode, r.kp.threads);
         r.src = l.src;
         r.dst = l.dst;
         if (!r.fn) {
@@ -336,7 +337,9 @@ static int realize_plan(trt_dft_plan_s* pl, trt_dft_plan_t* plan_out)
         }
         // the generic engine launch is always prepared: it is the route for buffers the
         // specialised kernels cannot take (not 16-byte aligned)
-        if (r.kp.mode >= dft::MODE_NAIVE_ROWS_R2C) {
+        if (small_rows) {
+            r.grid = (int)r.kp.ntiles;
+        } else if (r.kp.mode >= dft::MODE_NAIVE_ROWS_R2C) {
             r.kp.smem_bytes = 0;
             const long long blocks = (r.kp.nunits + 255) / 256;
             r.grid = (int)std::min<long long>(blocks, (long long)num_sms * 16);
@@ -416,9 +419,37 @@ static int realize_plan(trt_dft_plan_s* pl, trt_dft_plan_t* plan_out)
     return TRT_DFT_OK;
 }
 
+// A plan for a few short rows runs one thread per row and only writes plain rows: put it back on the tile engine.
+static int replan_on_the_engine(trt_dft_plan_t plan)
+{
+    trt_dft_plan_s* np = new (std::nothrow) trt_dft_plan_s();
+    if (!np) return TRT_DFT_ERR_ALLOC;
+    try {
+        if (dft::build_plan(&np->pd, plan->pd.direction, plan->pd.rank, plan->pd.dims, plan->pd.batch, dft::PLAN_NO_SMALL_ROWS)) {
+            delete np;
+            return TRT_DFT_ERR_INVALID_ARG;
+        }
+    } catch (...) {
+        delete np;
+        return TRT_DFT_ERR_ALLOC;
+    }
+    trt_dft_plan_t realized = nullptr;
+    const int rc = realize_plan(np, &realized);       // (frees np itself on failure)
+    if (rc != TRT_DFT_OK) return rc;
+    std::swap(plan->pd, realized->pd);
+    std::swap(plan->pool, realized->pool);
+    std::swap(plan->launches, realized->launches);
+    trt_dft_plan_destroy(realized);
+    return TRT_DFT_OK;
+}
+
 int trt_dft_plan_set_column_split(trt_dft_plan_t plan, int nparts, const int64_t* col_starts, int64_t rows_per_image)
 {
     if (!plan || nparts < 0 || nparts > 8 || (nparts > 0 && (!col_starts || rows_per_image < 1))) return TRT_DFT_ERR_INVALID_ARG;
+    if (nparts > 0 && plan->launches.size() == 1 && plan->launches[0].kp.mode == dft::MODE_SMALL_ROWS_R2C) {
+        const int rc = replan_on_the_engine(plan);
+        if (rc != TRT_DFT_OK) return rc;
+    }
     if (plan->launches.size() != 1 || plan->launches[0].kp.mode != dft::MODE_F1D) return TRT_DFT_ERR_UNSUPPORTED;
     KParams& k = plan->launches[0].kp;
     const int Mo = k.M + 1;
@@ -605,7 +636,8 @@ int trt_dft_exec(trt_dft_plan_t plan, const void* in, void* out, void* workspace
         const float* src = (const float*)sel(r.src);
         float* dst = (float*)sel(r.dst);
         // real rows that are not 8-byte aligned cannot be written/read as float2 pairs
-        if ((r.kp.mode == dft::MODE_I1D || r.kp.mode == dft::MODE_I2D) && ((uintptr_t)dst & 7)) return TRT_DFT_ERR_INVALID_ARG;
+        if ((r.kp.mode == dft::MODE_I1D || r.kp.mode == dft::MODE_I2D || r.kp.mode == dft::MODE_SMALL_ROWS_C2R) && ((uintptr_t)dst & 7))
+            return TRT_DFT_ERR_INVALID_ARG;
         if (r.spec && !(r.spec_needs_align16 && ((((uintptr_t)src) | ((uintptr_t)dst)) & 15)))
             r.spec<<<r.spec_grid, r.spec_nt, r.spec_smem, st>>>(src, dst, r.kp.nunits, r.spec_tab, r.kp.scale);
         else if (r.gpipe && (r.kp.pack_n == 0 || r.gpipe_pack))

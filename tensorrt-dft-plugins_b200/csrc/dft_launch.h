@@ -12,6 +12,7 @@ typedef void (*pipe_fn)(const KParams, const float*, float*, int, int, int, int)
 constexpr int kPipeCompute = 512, kPipeProducers = 64, kPipeThreads = kPipeCompute + kPipeProducers;
 
 kernel_fn tile_kernel_for(int mode, int threads);           // nullptr: unknown mode
+kernel_fn small_rows_kernel_for(int mode, int M);           // MODE_SMALL_ROWS_*: one thread per row; nullptr: M not instantiated
 pipe_fn pipe_kernel_for(int mode);                          // nullptr: mode has no pipelined variant
 pipe_fn pipe_kernel_for_geo(const KParams& k, bool tables_in_smem);   // nullptr: schedule not registered
 

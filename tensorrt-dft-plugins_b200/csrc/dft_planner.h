@@ -195,8 +195,11 @@ inline std::vector<float2> make_twiddles_steps(const LineFFT& f)
 }
 
 // ---- plan -------------------------------------------------------------------------------------
+enum PlanFlags : int { PLAN_NO_SMALL_ROWS = 1 };   // keep rows on the tile engine (needed for column-split output)
+
 struct Planner {
     PlanDesc* pd;
+    int flags = 0;
     int add_tw(std::vector<float2> t) { pd->tw_tables.push_back(std::move(t)); return (int)pd->tw_tables.size() - 1; }
     int add_perm(std::vector<int> t) { pd->perm_tables.push_back(std::move(t)); return (int)pd->perm_tables.size() - 1; }
 
@@ -225,6 +228,27 @@ struct Planner {
     {
         const bool even = (W % 2 == 0);
         const int M = even ? W / 2 : W;
+        // A handful of short rows is launch-latency bound: one thread per row, all in registers (BASELINE config 1).
+        if (even && (M == 2 || M == 4 || M == 8 || M == 16 || M == 32) && nrows <= 8192 && !(flags & PLAN_NO_SMALL_ROWS) && !getenv("TRT_DFT_NO_SMALL_ROWS")) {
+            KParams k = base(inverse ? MODE_SMALL_ROWS_C2R : MODE_SMALL_ROWS_R2C);
+            k.W = W;
+            k.M = M;
+            k.H = 1;
+            k.nunits = nrows;
+            k.ntiles = (nrows + 63) / 64;
+            k.threads = 64;
+            k.smem_bytes = 0;
+            k.scale = scale;
+            Launch l;
+            l.kp = k;
+            l.src = src;
+            l.dst = dst;
+            char nm[96];
+            snprintf(nm, sizeof nm, "%s<W=%d> rows=%lld [one thread per row, registers only]", inverse ? "small_rows_c2r" : "small_rows_r2c", W, nrows);
+            l.name = nm;
+            pd->launches.push_back(l);
+            return;
+        }
         KParams k = base(inverse ? (even ? MODE_I1D : MODE_I1D_ODD) : (even ? MODE_F1D : MODE_F1D_ODD));
         k.W = W;
         k.M = M;
@@ -400,7 +424,7 @@ inline bool line_supported(int n, bool rows_pitch_plus1)
 }
 
 // Returns 0 on success, nonzero TRT_DFT_ERR_* style code (1 = invalid argument).
-inline int build_plan(PlanDesc* pd, int direction, int rank, const int64_t* dims, int64_t batch)
+inline int build_plan(PlanDesc* pd, int direction, int rank, const int64_t* dims, int64_t batch, int flags = 0)
 {
     if (!pd || !dims || rank < 1 || rank > 3 || (direction != 0 && direction != 1) || batch < 0) return 1;
     for (int i = 0; i < rank; ++i)
@@ -431,7 +455,7 @@ inline int build_plan(PlanDesc* pd, int direction, int rank, const int64_t* dims
     const bool even = (W % 2 == 0);
     const int M = even ? W / 2 : W;
 
-    Planner P{pd};
+    Planner P{pd, flags};
     bool engine = line_supported(M, true);
     if (rank >= 2) engine = engine && line_supported(H, false);
     if (rank == 3) engine = engine && line_supported(D, false);

@@ -109,10 +109,92 @@ __global__ void __launch_bounds__(256) naive_kernel(const __grid_constant__ KPar
     }
 }
 
+// ---- a handful of short rows (BASELINE config 1, [4,32,64]): launch-latency bound -------------------------------------
+// One thread per row: the row's M = W/2 packed complex points live in registers from the global loads to the global
+// stores -- no shared memory, no barrier, no table, a single dependent chain load -> butterflies -> store.  The
+// accesses are not coalesced (consecutive threads are a whole row apart), which is irrelevant for the few KB this
+// kernel is planned for and is why the planner only picks it for small batches.
+template <int M, bool INV>
+__global__ void __launch_bounds__(64) small_rows_kernel(const __grid_constant__ KParams p, const float* __restrict__ in, float* __restrict__ out)
+{
+    using namespace dft;
+    constexpr int W = 2 * M;
+    const long long r = blockIdx.x * 64LL + threadIdx.x;
+    if (r >= p.nunits) return;
+    float2 z[M];
+    if (!INV) {
+        const float* src = in + r * W;
+        if ((((uintptr_t)src) & 15) == 0 && M % 2 == 0) {
+            static_for<0, M / 2>([&](auto ic) {
+                constexpr int i = decltype(ic)::value;
+                const float4 q = __ldg(reinterpret_cast<const float4*>(src) + i);
+                z[2 * i] = float2{q.x, q.y};
+                z[2 * i + 1] = float2{q.z, q.w};
+            });
+        } else {
+            static_for<0, M>([&](auto ic) {
+                constexpr int i = decltype(ic)::value;
+                z[i] = float2{__ldg(src + 2 * i), __ldg(src + 2 * i + 1)};
+            });
+        }
+        dft_reg<M>(z);
+        float2* o = reinterpret_cast<float2*>(out) + r * (M + 1);
+        o[0] = float2{z[0].x + z[0].y, 0.f};
+        o[M] = float2{z[0].x - z[0].y, 0.f};
+        static_for<1, M / 2 + 1>([&](auto kc) {
+            constexpr int k = decltype(kc)::value;
+            constexpr float wx = float(cx_cos2pi(k, W)), wy = float(-cx_sin2pi(k, W));      // w_W^k
+            const float2 a = z[k], b = z[M - k];
+            const float sx = a.x + b.x, sy = a.y - b.y, dx = a.x - b.x, dy = a.y + b.y;
+            const float tx = 0.5f * (wx * dx - wy * dy), ty = 0.5f * (wx * dy + wy * dx);
+            o[k] = float2{0.5f * sx + ty, 0.5f * sy - tx};
+            if constexpr (k != M - k) o[M - k] = float2{0.5f * sx - ty, -0.5f * sy - tx};
+        });
+    } else {
+        const float2* src = reinterpret_cast<const float2*>(in) + r * (M + 1);
+        {
+            const float a = __ldg(src).x, b = __ldg(src + M).x;       // the imaginary parts of DC / Nyquist are ignored
+            z[0] = float2{a + b, a - b};
+        }
+        static_for<1, M / 2 + 1>([&](auto kc) {
+            constexpr int k = decltype(kc)::value;
+            constexpr float wx = float(cx_cos2pi(k, W)), wy = float(-cx_sin2pi(k, W));
+            const float2 a = __ldg(src + k), b = __ldg(src + (M - k));
+            const float sx = a.x + b.x, sy = a.y - b.y, dx = a.x - b.x, dy = a.y + b.y;
+            const float ux = wx * dx + wy * dy, uy = wx * dy - wy * dx;
+            z[k] = float2{sx - uy, sy + ux};
+            if constexpr (k != M - k) z[M - k] = float2{sx + uy, -sy + ux};
+        });
+        dft_reg<M>(z);
+        const float sc = p.scale;
+        float2* o = reinterpret_cast<float2*>(out) + r * M;          // real row as pairs (x[2n], x[2n+1]) = y[(M - n) mod M]
+        static_for<0, M>([&](auto nc) {
+            constexpr int n = decltype(nc)::value;
+            constexpr int src_i = (M - n) % M;
+            o[n] = float2{z[src_i].x * sc, z[src_i].y * sc};
+        });
+    }
+}
 
 }  // namespace
 
 namespace dft {
+
+kernel_fn small_rows_kernel_for(int mode, int M)
+{
+    const bool inv = mode == MODE_SMALL_ROWS_C2R;
+    switch (M) {
+#define DFT_SMALL(M_) \
+    case M_: return inv ? (kernel_fn)small_rows_kernel<M_, true> : (kernel_fn)small_rows_kernel<M_, false>;
+        DFT_SMALL(2)
+        DFT_SMALL(4)
+        DFT_SMALL(8)
+        DFT_SMALL(16)
+        DFT_SMALL(32)
+#undef DFT_SMALL
+        default: return nullptr;
+    }
+}
 
 kernel_fn tile_kernel_for(int mode, int threads)
 {

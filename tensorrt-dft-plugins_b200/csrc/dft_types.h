@@ -113,6 +113,8 @@ enum Mode : int {
     MODE_NAIVE_ROWS_R2C = 7,
     MODE_NAIVE_ROWS_C2R = 8,
     MODE_NAIVE_COLS = 9,
+    MODE_SMALL_ROWS_R2C = 10,   // a few short rows (W = 2M <= 64): one thread per row, everything in registers
+    MODE_SMALL_ROWS_C2R = 11,
 };
 
 // One kernel launch.  All pointers are device pointers (host pointers in the emulator).

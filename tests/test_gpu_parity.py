@@ -72,6 +72,8 @@ def test_golden_extended(capi, name):
 SHAPES = [
     # BASELINE configs 1-3 in full
     ((4, 32, 64), 1), ((16, 64, 128, 128), 2), ((8, 768, 90, 180), 2),
+    # 1-D: a few short rows run one thread per row in registers (W = 4 .. 64, up to 8192 rows), one row more the engine
+    ((5, 4), 1), ((7, 8), 1), ((100, 16), 1), ((33, 32), 1), ((8192, 64), 1), ((8193, 64), 1),
     # 1-D
     ((3, 2), 1), ((3, 6), 1), ((5, 30), 1), ((2, 9), 1), ((2, 15), 1), ((3, 1), 1), ((2, 360), 1),
     ((1000, 1024), 1), ((2, 2 * 7 * 11 * 13), 1), ((2, 34), 1), ((3, 19), 1), ((3, 4096), 1), ((2, 8192), 1),
