@@ -29,15 +29,17 @@ using dft::kPipeCompute;
 using dft::kPipeProducers;
 using dft::kPipeThreads;
 
+// (const object with const methods: the programs take their context by reference, and a mutable one whose address has been
+// taken is re-read from local memory after every barrier's memory clobber -- a long-scoreboard stall per barrier)
 struct GroupCtx {
-    int tid, nthr, bar_id;
-    __host__ __device__ __forceinline__ void sync()
+    const int tid, nthr, bar_id;
+    __host__ __device__ __forceinline__ void sync() const
     {
 #if defined(__CUDA_ARCH__)
         asm volatile("bar.sync %0, %1;" ::"r"(bar_id), "r"(nthr) : "memory");
 #endif
     }
-    __host__ __device__ __forceinline__ bool bulk_load(void*, const void*, long long) { return false; }
+    __host__ __device__ __forceinline__ bool bulk_load(void*, const void*, long long) const { return false; }
 };
 
 __device__ __forceinline__ void cp_async8(void* dst, const void* src)
@@ -354,29 +356,26 @@ __global__ void __launch_bounds__(kPipeThreads, 1)
         asm volatile("cp.async.wait_all;" ::: "memory");
         return;
     }
-    GroupCtx ctx;
     const int g = tid / gt;
-    ctx.tid = tid - g * gt;
-    ctx.nthr = gt;
-    ctx.bar_id = 1 + g;
+    const GroupCtx ctx{tid - g * gt, gt, 1 + g};
     long long it = g;
     for (long long tile = blockIdx.x + (long long)g * gridDim.x; tile < p.ntiles; tile += (long long)ng * gridDim.x, it += ng) {
         const int s = (int)(it % ns);
         float2* buf = reinterpret_cast<float2*>(smem_raw + (size_t)s * stage_bytes);
         gp_wait(full0 + 8 * s, (unsigned)((it / ns) & 1));
-        if constexpr (MODE == dft::MODE_F2D) dft::program_f2d<GroupCtx, false>(p, tile, buf, in, out, ctx);
-        if constexpr (MODE == dft::MODE_I2D) dft::program_i2d<GroupCtx, false>(p, tile, buf, in, out, ctx);
+        if constexpr (MODE == dft::MODE_F2D) dft::program_f2d<const GroupCtx, false>(p, tile, buf, in, out, ctx);
+        if constexpr (MODE == dft::MODE_I2D) dft::program_i2d<const GroupCtx, false>(p, tile, buf, in, out, ctx);
         if constexpr (MODE == dft::MODE_F1D) {
             if constexpr (geo_two_rows<Geo>::value) Geo::run_f1d(p, tile, buf, out, ctx);
-            else dft::program_f1d<GroupCtx, false>(p, tile, buf, in, out, ctx);
+            else dft::program_f1d<const GroupCtx, false>(p, tile, buf, in, out, ctx);
         }
         if constexpr (MODE == dft::MODE_I1D) {
             if constexpr (geo_two_rows<Geo>::value) Geo::run_i1d(p, tile, buf, out, ctx);
-            else dft::program_i1d<GroupCtx, false>(p, tile, buf, in, out, ctx);
+            else dft::program_i1d<const GroupCtx, false>(p, tile, buf, in, out, ctx);
         }
         if constexpr (MODE == dft::MODE_C2C_COLS) {
             if constexpr (geo_two_step<Geo>::value) Geo::run_cols(p, tile, buf, out, ctx);
-            else dft::program_cols<GroupCtx, false>(p, tile, buf, in, out, ctx);
+            else dft::program_cols<const GroupCtx, false>(p, tile, buf, in, out, ctx);
         }
         asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
         __syncwarp();
@@ -400,6 +399,7 @@ namespace dft {
 #define DFT_GEO_ROWS_TWO(X) X(720, 16, 9, 5, 3, 8, 5, 6)
 #define DFT_GEO_COLS_TWO(X)              \
     X(720, 10, 9, 8, 3, 8, 5, 6, 16, false)     \
+    X(720, 10, 9, 8, 3, 8, 5, 6, 8, false)      \
     X(128, 16, 8, 1, 8, 1, 16, 1, 32, true)     \
     X(64, 8, 8, 1, 8, 1, 8, 1, 64, true)
 
