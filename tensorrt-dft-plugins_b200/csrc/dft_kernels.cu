@@ -7,6 +7,7 @@
 // another tile's butterflies and a third one's stores.
 //
 // There is no CPU route in this file: if a kernel cannot be launched the call returns an error.
+#include <cuda.h>
 #include <cuda_runtime.h>
 #include <stdint.h>
 #include <stdio.h>
@@ -65,6 +66,39 @@ std::vector<float2> spec_tables(const SpecEntry& e, bool inverse, double scale)
         t.push_back(float2{(float)(f * cos(a)), (float)(-f * sin(a))});
     }
     return t;
+}
+
+// cuTensorMapEncodeTiled through the runtime's driver entry point (no link against libcuda)
+typedef CUresult (*encode_tiled_fn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                                    const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                    CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+encode_tiled_fn tensor_map_encoder()
+{
+    static encode_tiled_fn fn = []() -> encode_tiled_fn {
+        void* p = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) != cudaSuccess || q != cudaDriverEntryPointSuccess) {
+            cudaGetLastError();
+            return nullptr;
+        }
+        return (encode_tiled_fn)p;
+    }();
+    return fn;
+}
+
+// Tensor map over a padded four-step workspace as the second pass sees it: [outer * N1 rows][N2 * pitch complex] fp32 pairs,
+// box = one tile ([G columns][N1 rows]).  false: fall back to element copies.
+bool encode_cols_tensor_map(CUtensorMap* tm, const KParams& k, const void* ws)
+{
+    encode_tiled_fn enc = tensor_map_encoder();
+    if (!enc || ((uintptr_t)ws & 15)) return false;
+    const cuuint64_t gdim[2] = {(cuuint64_t)k.inner * 2, (cuuint64_t)k.outer * (cuuint64_t)k.H};
+    const cuuint64_t gstride[1] = {(cuuint64_t)k.inner * 8};
+    const cuuint32_t box[2] = {(cuuint32_t)k.G * 2, (cuuint32_t)k.H};
+    const cuuint32_t estr[2] = {1, 1};
+    if ((gstride[0] & 15) || box[0] > 256 || box[1] > 256 || gdim[0] >= (1ull << 32) || gdim[1] >= (1ull << 32)) return false;
+    return enc(tm, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, const_cast<void*>(ws), gdim, gstride, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+               CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
 }
 
 struct ResolvedLaunch {
@@ -500,8 +534,9 @@ int trt_dft_plan_set_peer_row_split(trt_dft_plan_t plan, int nparts, const int64
     const bool four = plan->launches.size() == 2 && plan->launches[0].kp.n1split > 1;
     const long long n2 = four ? plan->launches[0].kp.H : 1;
     const long long n_axis = (long long)k.H * n2, inner = k.inner / n2;
+    const long long width = k.unflat_w ? k.unflat_w : inner;     // (a padded workspace's extra column is never stored)
     if (!row_starts || !peer_bands || row_starts[0] != 0 || row_starts[nparts] != n_axis || dest_pitch < 1 || dest_col_offset < 0 ||
-        dest_col_offset + inner > dest_pitch || dest_pitch > (1LL << 30))
+        dest_col_offset + width > dest_pitch || dest_pitch > (1LL << 30))
         return TRT_DFT_ERR_INVALID_ARG;
     k.split_n2 = (int)n2;
     k.split_inner = (int)inner;
@@ -640,10 +675,15 @@ int trt_dft_exec(trt_dft_plan_t plan, const void* in, void* out, void* workspace
             return TRT_DFT_ERR_INVALID_ARG;
         if (r.spec && !(r.spec_needs_align16 && ((((uintptr_t)src) | ((uintptr_t)dst)) & 15)))
             r.spec<<<r.spec_grid, r.spec_nt, r.spec_smem, st>>>(src, dst, r.kp.nunits, r.spec_tab, r.kp.scale);
-        else if (r.gpipe && (r.kp.pack_n == 0 || r.gpipe_pack))
-            (r.kp.pack_n ? r.gpipe_pack : r.gpipe)<<<r.gp_grid, kPipeThreads, r.gp_smem, st>>>(r.kp, src, dst, r.gp_ns, r.gp_ng, r.gp_stage,
-                                                                                            r.gp_tables);
-        else
+        else if (r.gpipe && (r.kp.pack_n == 0 || r.gpipe_pack)) {
+            CUtensorMap tmap;
+            memset(&tmap, 0, sizeof tmap);
+            KParams kp = r.kp;
+            // the second four-step pass fetches its tiles from the padded workspace with one 2-D TMA tensor copy each
+            if (kp.tma_cols && !(kp.mode == dft::MODE_C2C_COLS && encode_cols_tensor_map(&tmap, kp, src))) kp.tma_cols = 0;
+            (kp.pack_n ? r.gpipe_pack : r.gpipe)<<<r.gp_grid, kPipeThreads, r.gp_smem, st>>>(kp, src, dst, r.gp_ns, r.gp_ng, r.gp_stage,
+                                                                                          r.gp_tables, tmap);
+        } else
             r.fn<<<r.grid, r.kp.threads, r.kp.smem_bytes, st>>>(r.kp, src, dst);
         if (cudaPeekAtLastError() != cudaSuccess) {
             cudaGetLastError();

@@ -2,12 +2,14 @@
 // units that instantiate the kernels (dft_tile_kernels.cu, dft_pipe_kernels.cu); split so that nvcc compiles
 // them in parallel.
 #pragma once
+#include <cuda.h>            // CUtensorMap (type only; the encoder is fetched through cudaGetDriverEntryPoint)
+
 #include "dft_types.h"
 
 namespace dft {
 
 typedef void (*kernel_fn)(const KParams, const float*, float*);
-typedef void (*pipe_fn)(const KParams, const float*, float*, int, int, int, int);
+typedef void (*pipe_fn)(const KParams, const float*, float*, int, int, int, int, const CUtensorMap);
 
 constexpr int kPipeCompute = 512, kPipeProducers = 64, kPipeThreads = kPipeCompute + kPipeProducers;
 

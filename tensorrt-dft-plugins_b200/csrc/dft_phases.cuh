@@ -71,6 +71,7 @@ DFT_HD float2* split_elem_ptr(const KParams& p, long long o_, int qp, long long 
         const int k2 = (int)(jj / p.split_inner);
         c = jj - (long long)k2 * p.split_inner;
         q = qp * p.split_n2 + k2;
+        if (p.unflat_w && c >= p.unflat_w) return nullptr;       // padding column of the workspace: nothing to store
     }
     return split_row_ptr(p, o_, q) + c;
 }

@@ -1,4 +1,5 @@
 // dft_pipe_kernels.cu -- the persistent pipelined shell of the generic engine.
+#include <cuda.h>
 #include <cuda_runtime.h>
 #include <stdint.h>
 #include <stdlib.h>
@@ -69,12 +70,26 @@ __device__ __forceinline__ void gp_wait(unsigned bar, unsigned parity)
 // thread 0 (0 = element copies only)
 template <int MODE>
 __device__ __forceinline__ unsigned produce_tile(const KParams& p, long long tile, float2* buf, const float* in, int pt,
-                                                 unsigned full_bar)
+                                                 unsigned full_bar, const CUtensorMap* tmap)
 {
     constexpr int NP = kPipeProducers;
     if (MODE == dft::MODE_C2C_COLS) {
         const int N = p.H, P = p.P;
         const long long o_ = tile / p.chunks, c_ = tile - o_ * p.chunks, col0 = c_ * p.G;
+        if (p.tma_cols) {
+            // The whole tile -- N rows of G complex columns out of the padded workspace -- with one tensor copy: the TMA unit
+            // walks the strided rows, columns past the end of the workspace row are zero-filled (and dropped later).
+            const unsigned bytes = (unsigned)N * (unsigned)p.G * 8u;
+            if (pt == 0) {
+                asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(full_bar), "r"(bytes) : "memory");
+                asm volatile(
+                    "cp.async.bulk.tensor.2d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];" ::"r"(
+                        smem_u32(buf)),
+                    "l"(tmap), "r"((int)(col0 * 2)), "r"((int)(o_ * N)), "r"(full_bar)
+                    : "memory");
+            }
+            return bytes;
+        }
         const int ncol = (int)((p.inner - col0) < p.G ? (p.inner - col0) : p.G);
         const int n1s = p.n1split > 1 ? p.n1split : 1;   // four-step first pass: rows n1 + n1split*n2 of image o_hi
         const long long o_hi = o_ / n1s;
@@ -224,10 +239,17 @@ struct GeoTwo : GeoLine<N_, S0, S1, S2, 1> {
     {
         const long long o_ = tile / p.chunks, c_ = tile - o_ * p.chunks, col0 = c_ * p.G;
         const int ncol = (int)((p.inner - col0) < p.G ? (p.inner - col0) : p.G);
-        float2* dst = (float2*)out + o_ * N_ * p.inner + col0;
+        // output rows: pitch out_rowlen (first pass into a padded workspace), or -- second pass out of one -- the image
+        // pitch times the rows folded into one workspace row, with the column unfolded per work item (KParams::unflat_in)
+        long long orow = p.out_rowlen ? p.out_rowlen : p.inner;
+        float2* dst = (float2*)out + o_ * N_ * orow + col0;
+        if (p.unflat_in) {
+            orow = (p.inner / p.unflat_in) * p.unflat_w;
+            dst = (float2*)out + o_ * N_ * orow;
+        }
         const int n1s = p.n1split > 1 ? p.n1split : 1;
         const int n1 = (int)(o_ % n1s);
-        dft::cols_two_step<R1A, R1B, R2A, R2B, TM_, FOUR_>(buf, p.P, p.tw_col, dst, p.inner, ncol, p.scale, p.inverse != 0,
+        dft::cols_two_step<R1A, R1B, R2A, R2B, TM_, FOUR_>(buf, p.P, p.tw_col, dst, orow, ncol, p.scale, p.inverse != 0,
                                                     p.n1split > 1 ? p.tw_four : nullptr, n1, ctx,
                                                     p, p.split_n != 0 && p.n1split <= 1, o_, col0);
     }
@@ -273,7 +295,7 @@ struct geo_two_step<G, std::void_t<typename G::two_step_cols_tag>> : std::true_t
 template <int MODE, class Geo = GeoNone>
 __global__ void __launch_bounds__(kPipeThreads, 1)
     pipe_tile_kernel(const __grid_constant__ KParams p_in, const float* __restrict__ in, float* __restrict__ out, int ns, int ng,
-                     int stage_bytes, int tables_in_smem)
+                     int stage_bytes, int tables_in_smem, const __grid_constant__ CUtensorMap tmap)
 {
     extern __shared__ __align__(128) unsigned char smem_raw[];
     const unsigned full0 = smem_u32(smem_raw + (size_t)ns * stage_bytes);
@@ -346,7 +368,7 @@ __global__ void __launch_bounds__(kPipeThreads, 1)
             asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
             float2* buf = reinterpret_cast<float2*>(smem_raw + (size_t)s * stage_bytes);
             const unsigned bar = full0 + 8 * s;
-            const unsigned bulk = produce_tile<MODE>(p, tile, buf, in, pt, bar);
+            const unsigned bulk = produce_tile<MODE>(p, tile, buf, in, pt, bar, &tmap);
             if (bulk) {
                 if (pt != 0) asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
             } else {

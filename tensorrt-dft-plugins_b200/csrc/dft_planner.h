@@ -297,7 +297,13 @@ struct Planner {
         }
         if (!best1) return false;
         const int N1 = best1, N2 = N / best1;
-        const size_t bytes = (size_t)outer * N * inner * 8;
+        // The workspace rows are padded to an even number of complex elements: a 16-byte multiple, which makes the
+        // workspace a legal 2-D TMA tensor for pass 2 (the native one-sided pitch, (W/2+1)*8 bytes, never is).
+        // (not when the second pass runs in place on the workspace -- the un-fused inverse -- where it would read the padded
+        // layout and write the plain one over it)
+        const bool pad_ok = dst != BUF_WS && inner <= (1 << 28) && !getenv("TRT_DFT_NO_WS_PAD");
+        const long long inner_p = pad_ok ? inner + (inner & 1) : inner;
+        const size_t bytes = (size_t)outer * N * inner_p * 8;
         pd->ws_bytes = std::max(pd->ws_bytes, bytes);
         const size_t before = pd->launches.size();
         add_cols(false, outer * N1, N2, inner, src, BUF_WS, 1.0f, /*allow_four_step=*/false);
@@ -305,11 +311,21 @@ struct Planner {
             Launch& l = pd->launches[before];
             l.kp.n1split = N1;
             l.kp.rev_in = inverse ? 1 : 0;
+            l.kp.out_rowlen = pad_ok ? (int)inner_p : 0;
             l.tw_four_id = add_tw(make_twiddles(N, N));
             l.name += " [four-step pass 1 of " + std::to_string(N) + "]";
         }
-        add_cols(false, outer, N1, (long long)N2 * inner, BUF_WS, dst, scale, false);
-        pd->launches.back().name += " [four-step pass 2]";
+        add_cols(false, outer, N1, (long long)N2 * inner_p, BUF_WS, dst, scale, false);
+        {
+            Launch& l = pd->launches.back();
+            if (pad_ok) {
+                l.kp.unflat_in = (int)inner_p;
+                l.kp.unflat_w = (int)inner;
+                // one tensor copy per tile: box = [G columns][N1 rows], both at most 256
+                l.kp.tma_cols = (N1 <= 256 && l.kp.G <= 128 && l.kp.G == l.kp.P && !getenv("TRT_DFT_NO_TMA_COLS")) ? 1 : 0;
+            }
+            l.name += pad_ok ? " [four-step pass 2, padded workspace]" : " [four-step pass 2]";
+        }
         return true;
     }
 

@@ -315,20 +315,35 @@ DFT_HD void program_cols(const KParams& p, long long tile, float2* buf, const fl
     }
     if (LOAD) ctx.sync();
     run_line_fft(p.col, true, buf, ncol, P, p.tw_col, ncol, 0, ctx);
-    float2* dst = (float2*)out + o_ * N * p.inner + col0;
+    const long long orow = p.out_rowlen ? p.out_rowlen : p.inner;          // pitch of the rows this pass writes
+    float2* dst = (float2*)out + o_ * N * orow + col0;
     const float sc = p.scale;
     const bool four = p.n1split > 1;
-    if (p.split_n) {
+    if (p.unflat_in && !p.split_n) {
+        // second pass over a padded workspace: tile column j' = (workspace row k2, column c); see KParams::unflat_in
+        const long long n2 = p.inner / p.unflat_in;
+        float2* img = (float2*)out + o_ * N * n2 * p.unflat_w;
+        for (int idx = ctx.tid; idx < total; idx += ctx.nthr) {
+            const int q = idx / ncol;
+            const int j = idx - q * ncol;
+            const long long jj = col0 + j;
+            const long long k2 = jj / p.unflat_in, c = jj - k2 * p.unflat_in;
+            if (c >= p.unflat_w) continue;
+            const float2 z = buf[DFT_LDT(p.perm_col + q) * P + j];
+            img[((long long)q * n2 + k2) * p.unflat_w + c] = float2{z.x * sc, z.y * sc};
+        }
+    } else if (p.split_n) {
         // rows go to the rank that owns them (never combined with the four-step first pass, which writes the workspace)
         for (int idx = ctx.tid; idx < total; idx += ctx.nthr) {
             const int q = idx / ncol;
             const int j = idx - q * ncol;
             const float2 z = buf[DFT_LDT(p.perm_col + q) * P + j];
-            *split_elem_ptr(p, o_, q, col0 + j) = float2{z.x * sc, z.y * sc};
+            float2* d = split_elem_ptr(p, o_, q, col0 + j);
+            if (d) *d = float2{z.x * sc, z.y * sc};
         }
     } else if (fixed_col) {
-        float2* d0 = dst + (long long)n0 * p.inner + j0;
-        const long long dstep2 = (long long)rstep * p.inner;
+        float2* d0 = dst + (long long)n0 * orow + j0;
+        const long long dstep2 = (long long)rstep * orow;
         if (!four) {
 #if defined(__CUDA_ARCH__)
 #pragma unroll 4
@@ -349,7 +364,7 @@ DFT_HD void program_cols(const KParams& p, long long tile, float2* buf, const fl
             const int j = idx - q * ncol;
             float2 z = buf[DFT_LDT(p.perm_col + q) * P + j];
             if (four) z = cmul(z, DFT_LDT(p.tw_four + (long long)n1 * q));
-            dst[(long long)q * p.inner + j] = float2{z.x * sc, z.y * sc};
+            dst[(long long)q * orow + j] = float2{z.x * sc, z.y * sc};
         }
     }
     ctx.sync();

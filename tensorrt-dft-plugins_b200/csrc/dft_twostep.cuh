@@ -82,20 +82,31 @@ DFT_HD void cols_two_step(float2* buf, int P, const float2* tw /* w_N^j */, floa
                 v[k2] = cmul(v[k2], DFT_LDT(t4 + k2 * t4s));
             });
         }
+        // column of this work item in the output: j, or (second pass over a padded workspace, KParams::unflat_in) workspace
+        // row k2 / column c unfolded again; padding columns are dropped
+        long long jo = j;
+        bool ok = j < ncol;
+        if (kp.unflat_in && !split) {
+            const long long jj = split_col0 + j;
+            const long long kk = jj / kp.unflat_in, c = jj - kk * kp.unflat_in;
+            ok = ok && c < kp.unflat_w;
+            jo = kk * kp.unflat_w + c;
+        }
         if (j < ncol && split) {
             static_for<0, R2>([&](auto kc) {
                 constexpr int k2 = decltype(kc)::value;
                 const int q = k1 + R1 * k2;
                 const int qq = inverse ? (q == 0 ? 0 : N - q) : q;
-                *split_elem_ptr(kp, split_img, qq, split_col0 + j) = float2{v[k2].x * scale, v[k2].y * scale};
+                float2* d = split_elem_ptr(kp, split_img, qq, split_col0 + j);
+                if (d) *d = float2{v[k2].x * scale, v[k2].y * scale};
             });
-        } else if (j < ncol) {
+        } else if (ok) {
             // output row q = k1 + R1*k2, or (N - q) mod N for the inverse
             // one pointer walks down (or, for the inverse, up) the output rows
             const long long step = inverse ? -(long long)R1 * inner : (long long)R1 * inner;
-            float2* d = dst + j + (inverse ? (long long)(N - k1) * inner : (long long)k1 * inner);
+            float2* d = dst + jo + (inverse ? (long long)(N - k1) * inner : (long long)k1 * inner);
             if (inverse && k1 == 0) {                    // (N - 0) mod N = 0: row 0 stays, the rest walks up from N - R1
-                dst[j] = float2{v[0].x * scale, v[0].y * scale};
+                dst[jo] = float2{v[0].x * scale, v[0].y * scale};
             } else {
                 *d = float2{v[0].x * scale, v[0].y * scale};
             }

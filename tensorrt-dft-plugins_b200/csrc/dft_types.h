@@ -181,6 +181,18 @@ struct KParams {
     int n1split;
     const float2* tw_four;
     int rev_in;
+    // Four-step passes through a PADDED workspace (row pitch a multiple of 16 bytes, so that pass 2 can fetch its tiles
+    // with 2-D TMA tensor copies):
+    //   out_rowlen : pass 1 -- pitch of the rows it writes, in complex elements (0: = inner)
+    //   unflat_in  : pass 2 -- it sees the workspace as [outer][N1][N2 * unflat_in]; column j' of its tile is column
+    //                j' % unflat_in (dropped when >= unflat_w) of workspace row k2 = j' / unflat_in, and the result goes to
+    //                row q' * N2 + k2 of the image, pitch unflat_w.  0: input and output are flattened alike.
+    //   tma_cols   : pass 2 -- the executor provides a tensor map over the workspace; tiles arrive by one
+    //                cp.async.bulk.tensor.2d each instead of per-element copies
+    int out_rowlen;
+    int unflat_in;
+    int unflat_w;
+    int tma_cols;
     int inverse;             // cols mode: 1 = inverse transform (output index reversed)
     int in_place_ok;         // informational
     int io_align;            // 16 if in/out base pointers and unit strides allow 16-byte bulk copies
