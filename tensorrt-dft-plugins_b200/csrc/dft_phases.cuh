@@ -189,6 +189,78 @@ DFT_NOINLINE_HD void fft_step_big(float2* buf, int nlines, int pitch, int N, int
     fft_step<R, COLS>(buf, nlines, pitch, N, L, tw, ncols, img_stride, mmag, bmag, lmag, pad, ord, tid, nthr, tw_t);
 }
 
+// ---- one radix-R step for ANY prime R (used for prime factors above 31) ----------------------------------------------
+// No register butterfly exists for these, so every output element is one work item: Y[c] = w_L^(b c) * sum_a x[a] w_R^(a c),
+// R shared-memory reads and complex multiply-adds per output (O(N R) per line instead of the naive kernels' O(N^2) from
+// global memory).  The step cannot run in place that way, so it writes into `scr`, a second copy of the tile's
+// footprint; the caller copies it back after a barrier.  tw = w_N^j, j in [0, N).
+template <bool COLS>
+DFT_HD void fft_step_generic(int R, const float2* buf, float2* scr, int nlines, int pitch, int N, int L, const float2* tw, int ncols,
+                             int img_stride, int tid, int nthr)
+{
+    const int m = L / R;
+    const int tws = N / L, twr = N / R;
+    const long long total = (long long)nlines * N;
+    for (long long t = tid; t < total; t += nthr) {
+        int line, e;
+        if (COLS) {
+            e = (int)(t / nlines);
+            line = (int)(t - (long long)e * nlines);
+        } else {
+            line = (int)(t / N);
+            e = (int)(t - (long long)line * N);
+        }
+        const int blk = e / L, r = e - blk * L;
+        const int c = r / m, b = r - c * m;
+        const int e0 = blk * L + b;
+        int base, es;
+        if (COLS) {
+            base = line;
+            if (ncols != nlines) {
+                const int img = line / ncols;
+                base = img * img_stride + (line - img * ncols);
+            }
+            base += e0 * pitch;
+            es = m * pitch;
+        } else {
+            base = line * pitch + e0;
+            es = m;
+        }
+        const float2* x = buf + base;
+        // blocked summation (partial sums of 32 terms, then the sum of those): the rounding error grows like
+        // sqrt(32) + sqrt(R / 32) ulps instead of sqrt(R), which keeps the round trip of a 4099-point prime inside 1e-6
+        float ax = 0.f, ay = 0.f;
+        int idx = 0;
+        const int step = c * twr;                       // (a c mod R) * N/R, advanced incrementally
+        for (int a0 = 0; a0 < R; a0 += 32) {
+            float bx = 0.f, by = 0.f;
+            const int a1 = a0 + 32 < R ? a0 + 32 : R;
+            for (int a = a0; a < a1; ++a) {
+                const float2 w = DFT_LDT(tw + idx), v = x[a * es];
+                bx = fmaf(v.x, w.x, fmaf(-v.y, w.y, bx));
+                by = fmaf(v.x, w.y, fmaf(v.y, w.x, by));
+                idx += step;
+                if (idx >= N) idx -= N;
+            }
+            ax += bx;
+            ay += by;
+        }
+        if (m > 1) {
+            const float2 w = DFT_LDT(tw + b * c * tws);   // b c < L, so b c tws < N
+            const float tx = ax * w.x - ay * w.y;
+            ay = ax * w.y + ay * w.x;
+            ax = tx;
+        }
+        scr[base + c * es] = float2{ax, ay};
+    }
+}
+
+DFT_HD bool radix_has_butterfly(int r)
+{
+    return r == 2 || r == 3 || r == 4 || r == 5 || r == 6 || r == 7 || r == 8 || r == 9 || r == 10 || r == 11 || r == 13 || r == 16 ||
+           r == 17 || r == 19 || r == 23 || r == 29 || r == 31;
+}
+
 template <bool COLS>
 DFT_HD void fft_step_dispatch(int radix, float2* buf, int nlines, int pitch, int N, int L,
                               const float2* tw, int ncols, int img_stride, unsigned mmag, unsigned bmag,

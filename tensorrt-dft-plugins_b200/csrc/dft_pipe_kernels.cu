@@ -304,6 +304,7 @@ __global__ void __launch_bounds__(kPipeThreads, 1)
     const int gt = kPipeCompute / ng;
     KParams p = p_in;
     if constexpr (Geo::kStatic) {
+        p.scratch_off = 0;              // registered schedules have no generic prime step: fold that path away
         if (MODE == dft::MODE_C2C_COLS) {
             Geo::apply(p.col);
             p.H = Geo::N;

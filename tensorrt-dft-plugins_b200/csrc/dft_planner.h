@@ -75,7 +75,17 @@ inline void factor_search(int n, int start, std::vector<int>& cur, std::vector<i
 inline bool is_pow2(int n) { return n > 0 && (n & (n - 1)) == 0; }
 inline int phys_index(int p, bool pad) { return pad ? p + (p >> 4) + (p >> 8) : p; }
 
-// false when n has a prime factor above 31 or needs too many steps.
+constexpr int kMaxGenericPrime = 8191;      // prime factors above 31 run as generic O(R) -per-output steps (fft_step_generic)
+
+inline bool radix_is_generic(int r) { return r > 31; }
+inline bool line_has_generic(const LineFFT& f)
+{
+    for (int i = 0; i < f.nsteps; ++i)
+        if (radix_is_generic(f.radix[i])) return true;
+    return false;
+}
+
+// false when n has a prime factor above kMaxGenericPrime or needs too many steps.
 inline bool make_line_fft(int n, bool rows, LineFFT* f)
 {
     memset(f, 0, sizeof(*f));
@@ -85,11 +95,36 @@ inline bool make_line_fft(int n, bool rows, LineFFT* f)
     int m = n;
     for (int p : {2, 3, 5, 7, 11, 13, 17, 19, 23, 29, 31})
         while (m % p == 0) m /= p;
-    if (m != 1) return false;
+    // what is left are prime factors above 31: each becomes a radix of its own (a generic step)
+    std::vector<int> big;
+    for (int p = 37; (long long)p * p <= m; p += 2)
+        while (m % p == 0) {
+            big.push_back(p);
+            m /= p;
+        }
+    if (m > 1) big.push_back(m);
+    for (int p : big)
+        if (p > kMaxGenericPrime) return false;
+    const int small = n / [&] { long long q = 1; for (int p : big) q *= p; return (int)q; }();
     std::vector<int> cur, best;
-    factor_search(n, 0, cur, best);
-    if (best.empty() || (int)best.size() > kMaxSteps) return false;
+    if (small > 1) factor_search(small, 0, cur, best);
+    if ((small > 1 && best.empty()) || (int)(best.size() + big.size()) > kMaxSteps) return false;
     std::sort(best.begin(), best.end(), [](int a, int b) { return a > b; });
+    if (!big.empty()) {
+        // generic steps first (largest block length: their one-output-per-item form does not care), butterflies after
+        std::sort(big.begin(), big.end(), [](int a, int b) { return a > b; });
+        best.insert(best.begin(), big.begin(), big.end());
+        f->nsteps = (int)best.size();
+        int L = n;
+        for (int i = 0; i < f->nsteps; ++i) {
+            f->radix[i] = best[i];
+            const unsigned mm = (unsigned)(L / best[i]), bpl = (unsigned)(n / best[i]);
+            f->mmag[i] = mm <= 1 ? 0u : (unsigned)(((1ull << 32) + mm - 1) / mm);
+            f->bmag[i] = bpl <= 1 ? 0u : (unsigned)(((1ull << 32) + bpl - 1) / bpl);
+            L /= best[i];
+        }
+        return true;
+    }
     if (rows && is_pow2(n) && n >= 32) {
         // power-of-two rows are stored skewed (phys(p) = p + p/16 + p/256); the skew is linear inside a
         // butterfly when the schedule is r_top, 16, 16, ... (n = r_top * 16^k)
@@ -256,11 +291,13 @@ struct Planner {
         make_line_fft(M, true, &k.row);
         k.pad = (even && is_pow2(M) && M >= 32) ? 1 : 0;
         k.P = k.pad ? phys_index(M, true) + 1 : ((inverse && even) ? M + 1 : M);
-        if (even && !k.pad && !getenv("TRT_DFT_NO_ROW_ORDER")) set_row_orders(k.row, k.P);   // bank-conflict-free work-item order
+        if (even && !k.pad && !line_has_generic(k.row) && !getenv("TRT_DFT_NO_ROW_ORDER")) set_row_orders(k.row, k.P);   // bank-conflict-free work-item order
         k.nunits = nrows;
-        k.G = pick_group(nrows, (long long)k.P * 8, 48 * 1024);
+        const bool gen = line_has_generic(k.row);      // generic prime steps need a second copy of the tile
+        k.G = pick_group(nrows, (long long)k.P * 8 * (gen ? 2 : 1), 48 * 1024);
         k.ntiles = (nrows + k.G - 1) / k.G;
-        k.smem_bytes = k.G * k.P * 8 + kBarrierBytes;
+        k.smem_bytes = k.G * k.P * 8 * (gen ? 2 : 1) + kBarrierBytes;
+        k.scratch_off = gen ? k.G * k.P : 0;
         k.scale = scale;
         Launch l;
         l.kp = k;
@@ -337,12 +374,13 @@ struct Planner {
         KParams k = base(MODE_C2C_COLS);
         k.H = N;
         make_line_fft(N, false, &k.col);
-        const long long maxfit = std::max<long long>(1, (long long)(kSmemMax - kBarrierBytes) / ((long long)N * 8));
+        const bool gen = line_has_generic(k.col);
+        const long long maxfit = std::max<long long>(1, (long long)(kSmemMax - kBarrierBytes) / ((long long)N * 8 * (gen ? 2 : 1)));
         long long tm = std::max(std::min<long long>(16, maxfit), std::min<long long>(32, (64 * 1024) / ((long long)N * 8)));
         // prefer a tile that leaves room for two pipeline stages, as long as rows stay >= 32 bytes wide
         {
             long long t2 = 16;
-            while (t2 > 1 && t2 * N * 8 > (kSmemMax - 1024) / 2) t2 /= 2;
+            while (t2 > 1 && t2 * N * 8 * (gen ? 2 : 1) > (kSmemMax - 1024) / 2) t2 /= 2;
             // short axes: widen the tile to ~32 KB so that per-tile overheads (barriers, pipeline handshakes) amortise
             while (t2 < 64 && t2 * 2 * N * 8 <= 32 * 1024) t2 *= 2;
             if (t2 >= 4) tm = t2;
@@ -356,7 +394,8 @@ struct Planner {
         k.chunks = (inner + tm - 1) / tm;
         k.nunits = outer * k.chunks;
         k.ntiles = k.nunits;
-        k.smem_bytes = N * k.P * 8 + kBarrierBytes;
+        k.smem_bytes = N * k.P * 8 * (gen ? 2 : 1) + kBarrierBytes;
+        k.scratch_off = gen ? N * k.P : 0;
         k.scale = scale;
         k.inverse = inverse ? 1 : 0;
         k.threads = ((long long)N * tm >= 8192) ? 512 : 256;   // big tiles: more warps to hide the strided loads
@@ -383,11 +422,13 @@ struct Planner {
         k.P = inverse ? M + 1 : M;
         make_line_fft(M, true, &k.row);
         make_line_fft(H, false, &k.col);
-        const long long unit = (long long)H * k.P * 8;
+        const bool gen = line_has_generic(k.row) || line_has_generic(k.col);
+        const long long unit = (long long)H * k.P * 8 * (gen ? 2 : 1);
         k.nunits = nimg;
         k.G = pick_group(nimg, unit, 48 * 1024);
         k.ntiles = (nimg + k.G - 1) / k.G;
         k.smem_bytes = (int)(k.G * unit) + kBarrierBytes;
+        k.scratch_off = gen ? k.G * H * k.P : 0;
         k.scale = scale;
         Launch l;
         l.kp = k;
@@ -436,7 +477,12 @@ inline bool line_supported(int n, bool rows_pitch_plus1)
     LineFFT f;
     if (!make_line_fft(n, true, &f)) return false;
     const long long pitch = (rows_pitch_plus1 && is_pow2(n) && n >= 32) ? phys_index(n, true) + 1 : n + (rows_pitch_plus1 ? 1 : 0);
-    return pitch * 8 + kBarrierBytes <= kSmemMax;
+    return pitch * 8 * (line_has_generic(f) ? 2 : 1) + kBarrierBytes <= kSmemMax;
+}
+inline bool length_has_generic(int n)
+{
+    LineFFT f;
+    return make_line_fft(n, false, &f) && line_has_generic(f);
 }
 
 // Returns 0 on success, nonzero TRT_DFT_ERR_* style code (1 = invalid argument).
@@ -504,8 +550,9 @@ inline int build_plan(PlanDesc* pd, int direction, int rank, const int64_t* dims
             }
         }
     } else {
-        const bool fuse_fwd = rank >= 2 && even && ((long long)H * M * 8 + kBarrierBytes <= kSmemMax);
-        const bool fuse_inv = rank >= 2 && even && ((long long)H * (M + 1) * 8 + kBarrierBytes <= kSmemMax);
+        const int gen2 = (rank >= 2 && (length_has_generic(M) || length_has_generic(H))) ? 2 : 1;   // generic prime steps: tile + scratch
+        const bool fuse_fwd = rank >= 2 && even && ((long long)H * M * 8 * gen2 + kBarrierBytes <= kSmemMax);
+        const bool fuse_inv = rank >= 2 && even && ((long long)H * (M + 1) * 8 * gen2 + kBarrierBytes <= kSmemMax);
         if (!inv) {
             if (rank == 1) {
                 P.add_rows(false, batch, W, BUF_IN, BUF_OUT, 1.f);
@@ -568,7 +615,7 @@ inline int build_c2c_plan(PlanDesc* pd, int direction, int64_t n, int64_t outer,
     }
     Planner P{pd};
     LineFFT f;
-    const bool engine = make_line_fft((int)n, false, &f) && (long long)n * 8 + kBarrierBytes <= kSmemMax;
+    const bool engine = make_line_fft((int)n, false, &f) && (long long)n * 8 * (line_has_generic(f) ? 2 : 1) + kBarrierBytes <= kSmemMax;
     if (engine) {
         const size_t before = pd->launches.size();
         P.add_cols(direction == 1, outer, (int)n, inner, BUF_IN, BUF_OUT, scale);

@@ -11,9 +11,12 @@
 
 namespace dft {
 
+// scratch_off != 0: the plan contains prime radices above 31; those steps go out of place into buf + scratch_off and are
+// copied back (see fft_step_generic).  Compiled out of the kernels whose schedule is a compile-time constant.
 template <class Ctx>
 DFT_HD void run_line_fft(const LineFFT& f, bool cols, float2* buf, int nlines, int pitch,
-                         const float2* tw, int ncols, int img_stride, Ctx& ctx, int pad = 0, const float2* tw_t = nullptr)
+                         const float2* tw, int ncols, int img_stride, Ctx& ctx, int pad = 0, const float2* tw_t = nullptr,
+                         int scratch_off = 0)
 {
     int L = f.n;
     int toff = 0;                                       // start of this step's block of tw_t
@@ -24,6 +27,17 @@ DFT_HD void run_line_fft(const LineFFT& f, bool cols, float2* buf, int nlines, i
     for (int s = 0; s < kMaxSteps; ++s) {
         if (s >= f.nsteps) break;
         const int r = f.radix[s];
+        if (scratch_off != 0 && !radix_has_butterfly(r)) {
+            float2* scr = buf + scratch_off;
+            if (cols) fft_step_generic<true>(r, buf, scr, nlines, pitch, f.n, L, tw, ncols, img_stride, ctx.tid, ctx.nthr);
+            else fft_step_generic<false>(r, buf, scr, nlines, pitch, f.n, L, tw, ncols, img_stride, ctx.tid, ctx.nthr);
+            ctx.sync();
+            for (int i = ctx.tid; i < scratch_off; i += ctx.nthr) buf[i] = scr[i];
+            ctx.sync();
+            toff += (r - 1) * (L / r);
+            L /= r;
+            continue;
+        }
         if (cols)
             fft_step_dispatch<true>(r, buf, nlines, pitch, f.n, L, tw, ncols, img_stride, f.mmag[s], f.bmag[s], lmag, 0, 0,
                                     ctx.tid, ctx.nthr);
@@ -64,8 +78,8 @@ DFT_HD void program_f2d(const KParams& p, long long tile, float2* buf, const flo
     const long long first = tile * p.G;
     const int nimg = (int)((p.nunits - first) < p.G ? (p.nunits - first) : p.G);
     if (LOAD) load_contig(ctx, (float*)buf, in + first * H * p.W, (long long)nimg * H * p.W);
-    run_line_fft(p.row, false, buf, nimg * H, M, p.tw_row, 0, 0, ctx, 0, p.tw_row_t);
-    run_line_fft(p.col, true, buf, nimg * M, M, p.tw_col, M, H * M, ctx);
+    run_line_fft(p.row, false, buf, nimg * H, M, p.tw_row, 0, 0, ctx, 0, p.tw_row_t, p.scratch_off);
+    run_line_fft(p.col, true, buf, nimg * M, M, p.tw_col, M, H * M, ctx, 0, nullptr, p.scratch_off);
     // 2-D real-FFT split, two outputs per item: X[q][k] and X[(H-q)%H][M-k] share the pair
     // Y[q][k], Y[(H-q)%H][(M-k)%M].  k = M/2 (M even) is produced twice with identical values.
     float2* o = (float2*)out + first * H * Mo;
@@ -102,10 +116,10 @@ DFT_HD void program_i2d(const KParams& p, long long tile, float2* buf, const flo
     const long long first = tile * p.G;
     const int nimg = (int)((p.nunits - first) < p.G ? (p.nunits - first) : p.G);
     if (LOAD) load_contig(ctx, (float*)buf, in + first * H * P * 2, (long long)nimg * H * P * 2);
-    run_line_fft(p.col, true, buf, nimg * P, P, p.tw_col, P, H * P, ctx);
+    run_line_fft(p.col, true, buf, nimg * P, P, p.tw_col, P, H * P, ctx, 0, nullptr, p.scratch_off);
     merge_rows(buf, nimg * H, P, M, p.tw_unt, 0, ctx.tid, ctx.nthr);
     ctx.sync();
-    run_line_fft(p.row, false, buf, nimg * H, P, p.tw_row, 0, 0, ctx, 0, p.tw_row_t);
+    run_line_fft(p.row, false, buf, nimg * H, P, p.tw_row, 0, 0, ctx, 0, p.tw_row_t, p.scratch_off);
     float2* o = (float2*)out + first * H * M;
     const int per_img = H * M;
     const int total = nimg * per_img;
@@ -151,7 +165,7 @@ DFT_HD void program_f1d(const KParams& p, long long tile, float2* buf, const flo
     } else {
         load_contig(ctx, (float*)buf, in + first * p.W, (long long)nrows * p.W);
     }
-    run_line_fft(p.row, false, buf, nrows, P, p.tw_row, 0, 0, ctx, p.pad, p.tw_row_t);
+    run_line_fft(p.row, false, buf, nrows, P, p.tw_row, 0, 0, ctx, p.pad, p.tw_row_t, p.scratch_off);
     // real-FFT split, two outputs per item: X[k] and X[M-k] come from the same pair Z[k], Z[M-k]
     float2* o = (float2*)out + first * Mo;
     const int per_row = M / 2 + 1;
@@ -205,7 +219,7 @@ DFT_HD void program_i1d(const KParams& p, long long tile, float2* buf, const flo
     }
     merge_rows(buf, nrows, P, M, p.tw_unt, p.pad, ctx.tid, ctx.nthr);
     ctx.sync();
-    run_line_fft(p.row, false, buf, nrows, P, p.tw_row, 0, 0, ctx, p.pad, p.tw_row_t);
+    run_line_fft(p.row, false, buf, nrows, P, p.tw_row, 0, 0, ctx, p.pad, p.tw_row_t, p.scratch_off);
     float2* o = (float2*)out + first * M;
     const int total = nrows * M;
     const float sc = p.scale;
@@ -229,7 +243,7 @@ DFT_HD void program_f1d_odd(const KParams& p, long long tile, float2* buf, const
     const float* src = in + first * W;
     for (int idx = ctx.tid; idx < nrows * W; idx += ctx.nthr) buf[idx] = float2{DFT_LDG(src + idx), 0.f};
     ctx.sync();
-    run_line_fft(p.row, false, buf, nrows, W, p.tw_row, 0, 0, ctx);
+    run_line_fft(p.row, false, buf, nrows, W, p.tw_row, 0, 0, ctx, 0, nullptr, p.scratch_off);
     float2* o = (float2*)out + first * Mo;
     for (int idx = ctx.tid; idx < nrows * Mo; idx += ctx.nthr) {
         const int r = idx / Mo;
@@ -260,7 +274,7 @@ DFT_HD void program_i1d_odd(const KParams& p, long long tile, float2* buf, const
         buf[idx] = v;
     }
     ctx.sync();
-    run_line_fft(p.row, false, buf, nrows, W, p.tw_row, 0, 0, ctx);
+    run_line_fft(p.row, false, buf, nrows, W, p.tw_row, 0, 0, ctx, 0, nullptr, p.scratch_off);
     float* o = out + first * W;
     const float sc = p.scale;
     for (int idx = ctx.tid; idx < nrows * W; idx += ctx.nthr) {
@@ -314,7 +328,7 @@ DFT_HD void program_cols(const KParams& p, long long tile, float2* buf, const fl
         }
     }
     if (LOAD) ctx.sync();
-    run_line_fft(p.col, true, buf, ncol, P, p.tw_col, ncol, 0, ctx);
+    run_line_fft(p.col, true, buf, ncol, P, p.tw_col, ncol, 0, ctx, 0, nullptr, p.scratch_off);
     const long long orow = p.out_rowlen ? p.out_rowlen : p.inner;          // pitch of the rows this pass writes
     float2* dst = (float2*)out + o_ * N * orow + col0;
     const float sc = p.scale;

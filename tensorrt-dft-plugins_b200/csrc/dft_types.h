@@ -194,6 +194,8 @@ struct KParams {
     int unflat_w;
     int tma_cols;
     int inverse;             // cols mode: 1 = inverse transform (output index reversed)
+    int scratch_off;         // != 0: the tile is followed (scratch_off complex elements on) by a second copy of its
+                             // footprint, the out-of-place target of the generic prime-radix steps (radices above 31)
     int in_place_ok;         // informational
     int io_align;            // 16 if in/out base pointers and unit strides allow 16-byte bulk copies
 };

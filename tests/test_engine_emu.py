@@ -60,8 +60,8 @@ SHAPES = [
     # 2-D: fused, multi-image tiles, odd widths, unsupported primes (naive), H == 1
     ((7, 8, 8), 2), ((3, 6, 10), 2), ((2, 5, 7), 2), ((2, 12, 18), 2), ((2, 17, 6), 2), ((2, 6, 38), 2),
     ((700, 4, 4), 2), ((1, 4096, 64), 2), ((2, 5120, 40), 2), ((1, 1, 16), 2), ((2, 16, 1), 2), ((2, 3, 3), 2),
-    # prime factors 17..31 run as register butterflies; 37 and up still take the naive kernels
-    ((2, 2 * 17 * 19), 1), ((3, 46), 1), ((2, 29), 1), ((2, 62), 1), ((2, 34, 58), 2), ((2, 31, 38), 2), ((1, 74), 1), ((2, 37, 6), 2),
+    # prime factors 17..31 run as register butterflies, 37 and up as generic prime-radix steps (one output per work item)
+    ((2, 2 * 17 * 19), 1), ((3, 46), 1), ((2, 29), 1), ((2, 62), 1), ((2, 34, 58), 2), ((2, 31, 38), 2), ((1, 74), 1), ((2, 37, 6), 2), ((2, 2 * 37 * 41), 1), ((3, 1009), 1), ((2, 202), 1), ((2, 43, 86), 2), ((1, 3, 74, 6), 3), ((2, 8 * 53), 1),
     # 3-D
     ((2, 4, 6, 8), 3), ((2, 3, 5, 6), 3), ((1, 2, 3, 5, 7), 3), ((2, 1, 4, 4), 3), ((1, 17, 4, 6), 3),
 ]

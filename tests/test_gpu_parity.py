@@ -78,6 +78,9 @@ SHAPES = [
     ((3, 2), 1), ((3, 6), 1), ((5, 30), 1), ((2, 9), 1), ((2, 15), 1), ((3, 1), 1), ((2, 360), 1),
     ((1000, 1024), 1), ((2, 2 * 7 * 11 * 13), 1), ((2, 34), 1), ((3, 19), 1), ((3, 4096), 1), ((2, 8192), 1),
     ((2, 50000), 1), ((2, 65536), 1), ((1203, 1440), 1),   # persistent two-step row kernels, last tile partial
+    # prime factors above 31: generic prime-radix steps in shared memory (1009 and 4099 are prime)
+    ((40, 74), 1), ((3, 2 * 37 * 41), 1), ((300, 1009), 1), ((5, 4099), 1), ((2, 8 * 53), 1), ((6, 43, 86), 2), ((2, 202, 74), 2),
+    ((1, 3, 74, 6), 3), ((2, 2018, 40), 2),
     # 2-D
     ((7, 8, 8), 2), ((3, 6, 10), 2), ((2, 5, 7), 2), ((2, 12, 18), 2), ((2, 17, 6), 2), ((2, 6, 38), 2),
     ((700, 4, 4), 2), ((1, 1, 16), 2), ((2, 16, 1), 2), ((2, 3, 3), 2), ((300, 32, 32), 2), ((5, 64, 64), 2),
@@ -418,10 +421,10 @@ def test_reference_irfft2_cases_at_the_reference_defaults(capi):
 
 
 def test_in_place_c2c_on_a_length_outside_the_radix_set(capi):
-    """Lengths with a prime factor above 31 run the naive column kernel, which must not run in place: the plan goes
+    """Lengths with a prime factor above 8191 run the naive column kernel, which must not run in place: the plan goes
     through its workspace instead (many blocks, so a race would show)."""
     torch.manual_seed(7)
-    outer, n, inner = 4, 74, 4000                                    # 74 = 2 * 37
+    outer, n, inner = 1, 8209, 64                                    # 8209 is prime
     z = torch.randn(outer, n, inner, 2)
     want = torch.view_as_real(torch.fft.fft(torch.view_as_complex(z.double()), dim=1))
     plan = capi.C2CPlan(capi.FORWARD, n, outer, inner)
