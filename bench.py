@@ -174,12 +174,33 @@ def time_config(capi, torch, name, iters, peak, batch_override=None):
         e1.record()
         torch.cuda.synchronize()
         res[key] = e0.elapsed_time(e1) / iters
+    if small:
+        # launch-bound sizes: the same launches replayed from a CUDA graph (how TensorRT runs an engine), which takes
+        # the Python / ctypes call overhead out of the figure
+        s2 = torch.cuda.Stream()
+        for key, pl, a, b in (("graph_fwd", f, x, y), ("graph_inv", i, y, xr)):
+            g = torch.cuda.CUDAGraph()
+            with torch.cuda.stream(s2):
+                with torch.cuda.graph(g, stream=s2):
+                    for _ in range(20):
+                        pl.exec_ptr(a.data_ptr(), b.data_ptr(), ws.data_ptr(), s2.cuda_stream)
+            g.replay()
+            torch.cuda.synchronize()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            for _ in range(20):
+                g.replay()
+            e1.record()
+            torch.cuda.synchronize()
+            res[key] = e0.elapsed_time(e1) / 400
     ab = algo_bytes(shape, nd)
     out = {"shape": list(shape), "fwd_ms": res["fwd"], "inv_ms": res["inv"], "pair_ms": res["pair"],
            "fwd_GBs": ab / res["fwd"] / 1e6, "inv_GBs": ab / res["inv"] / 1e6, "pair_GBs": 2 * ab / res["pair"] / 1e6,
            "frac_of_measured_peak": 2 * ab / res["pair"] / 1e6 / peak, "round_trip_rel_l2": rt, "iters": iters,
            "algorithmic_bytes_per_direction": ab, "l2_resident": bool(small),
            "launches": [f.num_launches, i.num_launches], "workspace_bytes": [f.workspace_bytes, i.workspace_bytes]}
+    if small:
+        out["graph_fwd_ms"], out["graph_inv_ms"] = res["graph_fwd"], res["graph_inv"]
     del x, y, xr, ws, f, i
     torch.cuda.empty_cache()
     return out
@@ -193,11 +214,12 @@ def truncated_bench(capi, torch, peak, iters=200):
     x = torch.randn(nimg, H, W, device="cuda", generator=g)
     xr = torch.empty_like(x)
     st = torch.cuda.current_stream().cuda_stream
-    for kh, kw in ((45, 91), (22, 45), (12, 24)):
+    for kh, kw in ((45, 91), (22, 45), (12, 24), (6, 12)):
         f = capi.TruncatedPlan(capi.FORWARD, (H, W), nimg, kh, kw)
         i = capi.TruncatedPlan(capi.INVERSE, (H, W), nimg, kh, kw)
         y = torch.empty(nimg, 2 * kh, kw, 2, device="cuda")
-        step = lambda: (f.exec_ptr(x.data_ptr(), y.data_ptr(), 0, st), i.exec_ptr(y.data_ptr(), xr.data_ptr(), 0, st))
+        ws = torch.empty(max(f.workspace_bytes, i.workspace_bytes, 16), dtype=torch.uint8, device="cuda")
+        step = lambda: (f.exec_ptr(x.data_ptr(), y.data_ptr(), ws.data_ptr(), st), i.exec_ptr(y.data_ptr(), xr.data_ptr(), ws.data_ptr(), st))
         for _ in range(5):
             step()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
@@ -211,8 +233,9 @@ def truncated_bench(capi, torch, peak, iters=200):
         ab = 2 * nimg * (H * W * 4 + 2 * kh * kw * 8)
         out[f"keep_{2 * kh}x{kw}"] = {"pair_ms": ms, "algorithmic_bytes_per_pair": ab, "GBs": ab / ms / 1e6,
                                       "frac_of_measured_peak": ab / ms / 1e6 / peak,
-                                      "speedup_vs_full_pair_bytes": 2 * algo_bytes_one_direction(nimg) / ab}
-        del f, i, y
+                                      "bytes_vs_full_pair": ab / (2 * algo_bytes_one_direction(nimg)),
+                                      "route": f.describe()[1].split("[")[1].split("]")[0]}
+        del f, i, y, ws
     del x, xr
     torch.cuda.empty_cache()
     return out
@@ -367,6 +390,25 @@ def run_reference(args):
     print(json.dumps(line))
 
 
+def bind_to_gpu_numa_node(index):
+    """Pin this process to the CPUs next to its GPU (NVML's affinity mask), so that the pinned host buffers of the
+    end-to-end leg are first-touched on that NUMA node and the copies do not cross the socket interconnect.
+    Returns a short description for the JSON line."""
+    try:
+        import pynvml
+        pynvml.nvmlInit()
+        h = pynvml.nvmlDeviceGetHandleByIndex(index)
+        words = pynvml.nvmlDeviceGetCpuAffinity(h, (os.cpu_count() + 63) // 64)
+        cpus = [64 * i + b for i, w in enumerate(words) for b in range(64) if (w >> b) & 1]
+        allowed = sorted(set(cpus) & set(os.sched_getaffinity(0)))
+        if allowed:
+            os.sched_setaffinity(0, allowed)
+            return f"bound to {len(allowed)} CPUs local to GPU {index} ({allowed[0]}-{allowed[-1]})"
+        return "GPU-local CPUs not in this process's allowed set; not bound"
+    except Exception as e:
+        return "not bound: " + repr(e)[:80]
+
+
 def run_ours(args):
     import torch
     import torch.distributed as dist
@@ -377,6 +419,8 @@ def run_ours(args):
     local = int(os.environ.get("LOCAL_RANK", "0"))
     if not torch.cuda.is_available():
         raise SystemExit("bench.py needs a CUDA device (there is no CPU fallback); run it under gpurun")
+    orig_affinity = os.sched_getaffinity(0)
+    numa = bind_to_gpu_numa_node(local) if not os.environ.get("BENCH_NO_NUMA_BIND") else "binding disabled"
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
     if world > 1:
@@ -440,8 +484,8 @@ def run_ours(args):
         torch.cuda.synchronize()
         kms[name] = a.elapsed_time(b) / args.steps
     # sustained figure: the same step for long enough (>= 0.6 s) that the power cap, not the burst clocks, sets the pace
-    sus_steps = 1500
-    for _ in range(500):
+    sus_steps = 1500 if not args.headline_only else max(args.steps, 1)
+    for _ in range(500 if not args.headline_only else 0):
         step()
     s0, s1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     s0.record()
@@ -479,7 +523,9 @@ def run_ours(args):
 
     # ---- beyond the headline: the other BASELINE configs, the reference's cuFFT sequence, the multi-GPU paths ----
     extras = {}
-    if world == 1:
+    if args.headline_only:
+        pass
+    elif world == 1:
         try:
             extras["all_configs"] = {n: time_config(capi, torch, n, 200 if n in ("cfg1", "cfg2") else 10, peak)
                                      for n in ("cfg1", "cfg2", "cfg4", "cfg5")}
@@ -532,14 +578,15 @@ def run_ours(args):
                          "algorithmic_bytes_per_launch": algo_bytes_one_direction(nimg)},
             "e2e": {"value": world * pair_bytes * e2e_steps / e2e_s / 1e9, "unit": "GB/s",
                     "h2d_bytes_per_step": pair_bytes // 2, "d2h_bytes_per_step": pair_bytes // 2,
-                    "steps": e2e_steps, "api": "trt_dft_exec_host (pinned host buffers)"},
+                    "steps": e2e_steps, "api": "trt_dft_exec_host (pinned host buffers)", "cpu_affinity": numa},
             "gpu_launches": launches_per_step * args.steps,
             "clocks": clocks,
             "plan": plan_desc,
         }
         line.update(extras)
         if world == 1:
-            cores = os.cpu_count() or 1
+            os.sched_setaffinity(0, orig_affinity)          # the CPU baseline gets every host core again
+            cores = len(os.sched_getaffinity(0)) or 1
             sample = 768
             t = time_cpu_pair(sample, 3, cores)
             line["cpu_baseline"] = {"value": 2 * algo_bytes_one_direction(sample) / t / 1e9, "unit": "GB/s", "cores": cores,
@@ -556,6 +603,8 @@ def main():
     ap.add_argument("--steps", type=int, default=500)
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--headline-only", action="store_true",
+                    help="skip the extra keys (other configs, cuFFT comparator, truncated modes, multi-GPU paths): for profiler passes")
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference(args)

@@ -50,9 +50,7 @@ def test_reference_irfft2_cases(capi, name):
     y = torch.from_numpy(GOLD[name + "_rfft2"])
     x = capi.irfftn(y.cuda(), 2).cpu()
     x_expected = torch.from_numpy(GOLD[name + "_irfft2"])
-    # tests/test_dft.py:184 uses the allclose defaults; atol 1e-8 is below fp32 resolution for
-    # values that cancel to ~1e-8, so the absolute floor is stated explicitly here.
-    assert torch.allclose(x_expected, x, rtol=1e-5, atol=1e-6)
+    assert torch.allclose(x_expected, x)                       # tests/test_dft.py:184, the reference's defaults (rtol 1e-5, atol 1e-8)
     assert O.rel_l2(x.numpy(), GOLD[name + "_irfft2_f64"]) <= FWD_TOL
 
 
@@ -404,10 +402,10 @@ def test_cfg5_full_size_both_directions(capi):
 
 
 def test_reference_irfft2_cases_at_the_reference_defaults(capi):
-    """tests/test_dft.py:184 asserts torch.allclose at the defaults (rtol 1e-5, atol 1e-8).  fp32 cannot promise an
-    absolute 1e-8 on elements that cancel to ~0 (the CPU oracle itself is only reproducible to ~1e-7 there), so
-    the parametrised test above states atol 1e-6.  This one records how the 8 cases fare at the defaults, and every
-    element that misses them must be off by less than 1e-6 absolute (a few fp32 ulps of the O(1) intermediates)."""
+    """tests/test_dft.py:184 asserts torch.allclose at the defaults (rtol 1e-5, atol 1e-8), and so does the parametrised
+    test above: all 8 cases pass them on B200.  fp32 cannot promise an absolute 1e-8 on elements that cancel to ~0 in
+    general, so this test also pins the fallback statement: any element that ever misses the defaults must be off by less
+    than 1e-6 absolute (a few fp32 ulps of the O(1) intermediates)."""
     passed = 0
     for name in REF:
         y = torch.from_numpy(GOLD[name + "_rfft2"])
