@@ -424,6 +424,7 @@ namespace dft {
     X(720, 10, 9, 8, 3, 8, 5, 6, 16, false)     \
     X(720, 10, 9, 8, 3, 8, 5, 6, 8, false)      \
     X(128, 16, 8, 1, 8, 1, 16, 1, 32, true)     \
+    X(128, 16, 8, 1, 8, 1, 16, 1, 64, true)     \
     X(64, 8, 8, 1, 8, 1, 8, 1, 64, true)
 
 pipe_fn pipe_kernel_for_geo(const KParams& k, bool tables_in_smem)
