@@ -167,8 +167,9 @@ int trt_dft_plan_describe(trt_dft_plan_t plan, char* buf, size_t len);
  * buffer because they cannot allocate one where they run -- inside an enqueue, in a serving
  * loop that must not hit cudaMalloc's device-wide synchronisation, or behind an op interface
  * that has inputs and outputs only.  The workspace is a fixed region of
- * TRT_DFT_STATIC_WS_BYTES that the library reserves on every GPU it is loaded on (held until
- * the process exits); the call itself allocates and frees nothing.
+ * TRT_DFT_STATIC_WS_BYTES: a __device__ array, which a GPU holds from the first time this entry
+ * point runs on it (that call's address lookup makes the runtime load the array's module there)
+ * until the process exits; the call itself allocates and frees nothing.
  *   - plans needing more than TRT_DFT_STATIC_WS_BYTES are refused with
  *     TRT_DFT_ERR_UNSUPPORTED (and a message on stderr); plans needing none run as usual;
  *   - all calls on one GPU share the region: calls whose GPU work may overlap (different

@@ -8,10 +8,12 @@
 //     a thread that is not allowed to touch the allocator at all;
 //   * hosts that wire our kernels in behind an interface with no workspace argument (an inference
 //     runtime that gave the op zero scratch bytes, a custom-op ABI with only inputs and outputs).
-// For them the library keeps one fixed scratch region per GPU, reserved when the module is loaded
-// on that GPU (a __device__ array, so it costs TRT_DFT_STATIC_WS_BYTES of device memory on every
-// GPU that loads the library, until the process exits), and this entry point hands that region to
-// the ordinary executor.  Nothing is allocated or freed here, by us or by any library we call.
+// For them the library keeps one fixed scratch region per GPU: a __device__ array, so it costs
+// TRT_DFT_STATIC_WS_BYTES of device memory on every GPU on which this entry point has run -- from
+// its first call there (with CUDA's lazy module loading the array's module is loaded by that call's
+// address lookup, not when the library is opened) until the process exits -- and this entry point
+// hands that region to the ordinary executor.  Nothing is allocated or freed here, by us or by any
+// library we call.
 //
 // Rules that follow from sharing one region:
 //   * plans whose workspace exceeds TRT_DFT_STATIC_WS_BYTES are refused (status

@@ -4,8 +4,8 @@ A plan for a large inverse transform needs scratch memory between its column pas
 pass.  Normally the caller allocates that buffer and passes it to trt_dft_exec.  Code that runs
 where allocation is off limits (a plugin's enqueue, a serving loop that cannot afford cudaMalloc's
 device synchronisation, an op interface with no workspace argument) calls
-trt_dft_exec_static_ws instead, which lends the plan a fixed region the library reserved on the
-GPU at load time.  This file checks, through the C ABI, that the result is the same as with a
+trt_dft_exec_static_ws instead, which lends the plan a fixed region the library holds on the
+GPU (from this entry point's first call there).  This file checks, through the C ABI, that the result is the same as with a
 caller-owned workspace -- twice in a row, with different inputs, because the region is shared and
 keeps the previous call's contents -- and that a plan too large for the region is refused.
 
