@@ -38,6 +38,15 @@ def sources():
     return cu, deps
 
 
+# A/B switch, off by default: TRT_DFT_BUILD_F32X2=1 compiles the butterflies with packed fp32 arithmetic (add / sub / fma.f32x2 ->
+# FADD2 / FFMA2).  Measured on B200: 18 % fewer instructions in the headline forward kernel but 0.138 -> 0.191 ms -- the
+# packed forms have the scalar forms' lane throughput (tools/dev/ffma2_bench.cu) and evidently a longer dependent-issue
+# latency, which these latency-bound kernels cannot hide.
+import os as _os
+if _os.environ.get("TRT_DFT_BUILD_F32X2"):
+    NVCC_FLAGS.append("-DDFT_F32X2")
+
+
 def build(force=False, verbose=False):
     cu, deps = sources()
     if not force and OUT.exists() and all(OUT.stat().st_mtime >= d.stat().st_mtime for d in deps + [Path(__file__)]):

@@ -82,8 +82,42 @@ DFT_CX double cx_sin2pi(long long j, long long n)  // sin(2*pi*j/n) = cos(2*pi*(
 }
 
 // ---- complex helpers ------------------------------------------------------------------------
+// DFT_F32X2 (sm_100a): complex add / subtract as ONE packed instruction (add.f32x2 -> FADD2).  The packed form has the
+// same lane throughput as two scalar adds (measured, tools/dev/ffma2_bench.cu) but takes one issue slot instead of two.
+#if defined(__CUDA_ARCH__) && defined(DFT_F32X2)
+__device__ __forceinline__ unsigned long long f2_bits(float2 a) { return (unsigned long long)__float_as_uint(a.x) | ((unsigned long long)__float_as_uint(a.y) << 32); }
+__device__ __forceinline__ float2 bits_f2(unsigned long long r) { return float2{__uint_as_float((unsigned)r), __uint_as_float((unsigned)(r >> 32))}; }
+__device__ __forceinline__ float2 cadd(float2 a, float2 b)
+{
+    unsigned long long r;
+    asm("add.f32x2 %0, %1, %2;" : "=l"(r) : "l"(f2_bits(a)), "l"(f2_bits(b)));
+    return bits_f2(r);
+}
+__device__ __forceinline__ float2 csub(float2 a, float2 b)
+{
+    unsigned long long r;
+    asm("sub.f32x2 %0, %1, %2;" : "=l"(r) : "l"(f2_bits(a)), "l"(f2_bits(b)));
+    return bits_f2(r);
+}
+// p + c * a with a real scalar c (both halves): one FFMA2 with a broadcast operand
+__device__ __forceinline__ float2 cfma_s(float c, float2 a, float2 p)
+{
+    unsigned long long r;
+    asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(r) : "l"(f2_bits(a)), "l"(f2_bits(float2{c, c})), "l"(f2_bits(p)));
+    return bits_f2(r);
+}
+__device__ __forceinline__ float2 cmul_s(float c, float2 a)
+{
+    unsigned long long r;
+    asm("mul.f32x2 %0, %1, %2;" : "=l"(r) : "l"(f2_bits(a)), "l"(f2_bits(float2{c, c})));
+    return bits_f2(r);
+}
+#else
 DFT_HD float2 cadd(float2 a, float2 b) { return float2{a.x + b.x, a.y + b.y}; }
 DFT_HD float2 csub(float2 a, float2 b) { return float2{a.x - b.x, a.y - b.y}; }
+DFT_HD float2 cfma_s(float c, float2 a, float2 p) { return float2{fmaf(c, a.x, p.x), fmaf(c, a.y, p.y)}; }
+DFT_HD float2 cmul_s(float c, float2 a) { return float2{c * a.x, c * a.y}; }
+#endif
 DFT_HD float2 cmul(float2 a, float2 w) { return float2{a.x * w.x - a.y * w.y, a.x * w.y + a.y * w.x}; }
 DFT_HD float2 cconj(float2 a) { return float2{a.x, -a.y}; }
 
@@ -125,11 +159,13 @@ DFT_HD void dft_prime(float2 (&v)[P])
 {
     static_assert(P % 2 == 1 && P >= 3, "odd prime expected");
     constexpr int Hh = (P - 1) / 2;
-    float2 a[Hh], b[Hh];
+    // a_j = v_j + v_{P-j};  br_j = -i (v_j - v_{P-j}) = (d.y, -d.x): kept rotated, so that X_k = p_k + qr_k and
+    // X_{P-k} = p_k - qr_k are plain complex additions (packed on sm_100a, see cadd)
+    float2 a[Hh], br[Hh];
     static_for<0, Hh>([&](auto jc) {
         constexpr int j = decltype(jc)::value;
         a[j] = cadd(v[j + 1], v[P - 1 - j]);
-        b[j] = csub(v[j + 1], v[P - 1 - j]);
+        br[j] = float2{v[j + 1].y - v[P - 1 - j].y, v[P - 1 - j].x - v[j + 1].x};
     });
     const float2 v0 = v[0];
     float2 s0 = v0;
@@ -143,19 +179,12 @@ DFT_HD void dft_prime(float2 (&v)[P])
             constexpr int j = decltype(jc)::value;
             constexpr float c = float(cx_cos2pi((long long)j * k, P));
             constexpr float s = float(cx_sin2pi((long long)j * k, P));
-            p.x = fmaf(c, a[j - 1].x, p.x);
-            p.y = fmaf(c, a[j - 1].y, p.y);
-            if constexpr (j == 1) {
-                q.x = s * b[0].x;
-                q.y = s * b[0].y;
-            } else {
-                q.x = fmaf(s, b[j - 1].x, q.x);
-                q.y = fmaf(s, b[j - 1].y, q.y);
-            }
+            p = cfma_s(c, a[j - 1], p);
+            if constexpr (j == 1) q = cmul_s(s, br[0]);
+            else q = cfma_s(s, br[j - 1], q);
         });
-        // -i*q = (q.y, -q.x)
-        v[k] = float2{p.x + q.y, p.y - q.x};
-        v[P - k] = float2{p.x - q.y, p.y + q.x};
+        v[k] = cadd(p, q);
+        v[P - k] = csub(p, q);
     });
 }
 

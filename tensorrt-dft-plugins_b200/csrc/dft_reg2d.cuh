@@ -96,7 +96,7 @@ __device__ __forceinline__ void load_fold(float2 (&y)[L2], const float4* __restr
         constexpr int i = decltype(ic)::value;
         constexpr int n2 = (i * S) % L2;
         const float4 cur = line[n2];
-        y[n2] = float2{fmaf(sg, prev.z, cur.x), fmaf(sg, prev.w, cur.y)};
+        y[n2] = cfma_s(sg, float2{prev.z, prev.w}, float2{cur.x, cur.y});
         prev = cur;
     });
 }
@@ -184,7 +184,7 @@ __device__ __forceinline__ void load_fold_rev(float2 (&y)[L2], const float2* __r
         constexpr int n2 = decltype(nc)::value;
         constexpr int ia = (L - 2 * n2) % L, ib = (2 * L - L2 - 2 * n2) % L;
         const float2 a = src[ia * STRIDE], b = src[ib * STRIDE];
-        y[n2] = float2{fmaf(sg, b.x, a.x), fmaf(sg, b.y, a.y)};
+        y[n2] = cfma_s(sg, b, a);
     });
 }
 
