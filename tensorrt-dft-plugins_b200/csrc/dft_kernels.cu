@@ -114,6 +114,7 @@ struct ResolvedLaunch {
     pipe_fn gpipe_pack = nullptr;    // what runs in its place once trt_dft_plan_set_column_split has been called
                                      // (the two-step row programs write plain rows only)
     int gp_ns = 0, gp_ng = 0, gp_stage = 0, gp_smem = 0, gp_grid = 0, gp_tables = 0;
+    int gp_threads = dft::kPipeThreads, gp_threads_pack = dft::kPipeThreads;   // CTA size of gpipe / gpipe_pack
 };
 
 }  // namespace
@@ -413,9 +414,11 @@ static int realize_plan(trt_dft_plan_s* pl, trt_dft_plan_t* plan_out)
                     tables = 1;
                 }
             }
+            int ct = dft::kPipeCompute, ptn = dft::kPipeProducers;
             if (pf && !getenv("TRT_DFT_NO_GEO")) {
-                pipe_fn pg = dft::pipe_kernel_for_geo(r.kp, tables != 0);
+                pipe_fn pg = dft::pipe_kernel_for_geo(r.kp, tables != 0, &ct, &ptn);
                 if (pg) pf = pg;
+                else ct = dft::kPipeCompute, ptn = dft::kPipeProducers;
             }
             if (pf && !getenv("TRT_DFT_NO_GPIPE") && stage >= 8 * 1024 && ns >= 2 && r.kp.ntiles >= num_sms) {
                 const int smem = ns * stage + 2 * ns * 8 + 64 + (tables ? tab_bytes : 0);
@@ -423,12 +426,17 @@ static int realize_plan(trt_dft_plan_s* pl, trt_dft_plan_t* plan_out)
                 if (cudaFuncSetAttribute((const void*)pf, cudaFuncAttributeMaxDynamicSharedMemorySize, dft::kSmemMax) == cudaSuccess) {
                     r.gpipe = pf;
                     r.gpipe_pack = pf;
+                    r.gp_threads = r.gp_threads_pack = ct + ptn;
                     if (r.kp.mode == dft::MODE_F1D) {
                         KParams kpack = r.kp;
                         kpack.pack_n = 1;
                         pipe_fn pp = dft::pipe_kernel_for(r.kp.mode);
-                        if (!getenv("TRT_DFT_NO_GEO"))
-                            if (pipe_fn pg2 = dft::pipe_kernel_for_geo(kpack, tables != 0)) pp = pg2;
+                        int ct2 = dft::kPipeCompute, pt2 = dft::kPipeProducers;
+                        if (!getenv("TRT_DFT_NO_GEO")) {
+                            if (pipe_fn pg2 = dft::pipe_kernel_for_geo(kpack, tables != 0, &ct2, &pt2)) pp = pg2;
+                            else ct2 = dft::kPipeCompute, pt2 = dft::kPipeProducers;
+                        }
+                        r.gp_threads_pack = ct2 + pt2;
                         if (pp != pf && cudaFuncSetAttribute((const void*)pp, cudaFuncAttributeMaxDynamicSharedMemorySize, dft::kSmemMax) != cudaSuccess) {
                             cudaGetLastError();
                             pp = nullptr;            // fall back to the non-persistent kernel for split output
@@ -579,7 +587,7 @@ int trt_dft_plan_describe(trt_dft_plan_t plan, char* buf, size_t len)
             const auto& rl = plan->launches[i];
             if (rl.gpipe && !rl.spec)
                 snprintf(t, sizeof t, "%s[%d]pipelined grid=%dx%d stages=%d groups=%d", i ? "," : " ", (int)i, rl.gp_grid,
-                         kPipeThreads, rl.gp_ns, rl.gp_ng);
+                         rl.gp_threads, rl.gp_ns, rl.gp_ng);
             else
                 snprintf(t, sizeof t, rl.spec ? "%s[%d]grid=%dx%d smem=%d" : "%s[%d]grid=%dx%d", i ? "," : " ", (int)i,
                          rl.spec ? rl.spec_grid : rl.grid, rl.spec ? rl.spec_nt : rl.kp.threads, rl.spec_smem);
@@ -681,7 +689,7 @@ int trt_dft_exec(trt_dft_plan_t plan, const void* in, void* out, void* workspace
             KParams kp = r.kp;
             // the second four-step pass fetches its tiles from the padded workspace with one 2-D TMA tensor copy each
             if (kp.tma_cols && !(kp.mode == dft::MODE_C2C_COLS && encode_cols_tensor_map(&tmap, kp, src))) kp.tma_cols = 0;
-            (kp.pack_n ? r.gpipe_pack : r.gpipe)<<<r.gp_grid, kPipeThreads, r.gp_smem, st>>>(kp, src, dst, r.gp_ns, r.gp_ng, r.gp_stage,
+            (kp.pack_n ? r.gpipe_pack : r.gpipe)<<<r.gp_grid, kp.pack_n ? r.gp_threads_pack : r.gp_threads, r.gp_smem, st>>>(kp, src, dst, r.gp_ns, r.gp_ng, r.gp_stage,
                                                                                           r.gp_tables, tmap);
         } else
             r.fn<<<r.grid, r.kp.threads, r.kp.smem_bytes, st>>>(r.kp, src, dst);

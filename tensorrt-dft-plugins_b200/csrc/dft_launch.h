@@ -16,7 +16,7 @@ constexpr int kPipeCompute = 512, kPipeProducers = 64, kPipeThreads = kPipeCompu
 kernel_fn tile_kernel_for(int mode, int threads);           // nullptr: unknown mode
 kernel_fn small_rows_kernel_for(int mode, int M);           // MODE_SMALL_ROWS_*: one thread per row; nullptr: M not instantiated
 pipe_fn pipe_kernel_for(int mode);                          // nullptr: mode has no pipelined variant
-pipe_fn pipe_kernel_for_geo(const KParams& k, bool tables_in_smem);   // nullptr: schedule not registered
+pipe_fn pipe_kernel_for_geo(const KParams& k, bool tables_in_smem, int* compute_threads, int* producer_threads);   // nullptr: schedule not registered
 
 // dft_trunc.cu: kept modes <-> full one-sided spectrum (fallback of the truncated-mode plans)
 void launch_crop_modes(const void* full, void* kept, long long nimg, int H, int MO, int kh, int kw, void* stream);

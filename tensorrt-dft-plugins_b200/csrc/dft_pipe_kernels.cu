@@ -68,11 +68,10 @@ __device__ __forceinline__ void gp_wait(unsigned bar, unsigned parity)
 
 // producer side: start the copies of one tile; returns the byte count of a bulk copy issued by
 // thread 0 (0 = element copies only)
-template <int MODE>
+template <int MODE, int NP>
 __device__ __forceinline__ unsigned produce_tile(const KParams& p, long long tile, float2* buf, const float* in, int pt,
                                                  unsigned full_bar, const CUtensorMap* tmap)
 {
-    constexpr int NP = kPipeProducers;
     if (MODE == dft::MODE_C2C_COLS) {
         const int N = p.H, P = p.P;
         const long long o_ = tile / p.chunks, c_ = tile - o_ * p.chunks, col0 = c_ * p.G;
@@ -292,8 +291,12 @@ struct geo_two_step : std::false_type {};
 template <class G>
 struct geo_two_step<G, std::void_t<typename G::two_step_cols_tag>> : std::true_type {};
 
-template <int MODE, class Geo = GeoNone>
-__global__ void __launch_bounds__(kPipeThreads, 1)
+// CT compute threads + PT producer threads.  The default 512 + 64 = 18 warps puts 5 warps on one of the SM's four
+// sub-partitions, which caps a thread at 96 registers (5 x 32 x 96 <= 16 K); 480 + 32 = 16 warps leave 128 and remove the
+// 720-point column program's 16 bytes of spills (loop invariants reloaded on the path to every barrier) -- but one producer
+// warp cannot keep the tile ring full: cfg4 columns 2.67 -> 2.89 ms.  Kept as an A/B (TRT_DFT_480=1).
+template <int MODE, class Geo = GeoNone, int CT = kPipeCompute, int PT = kPipeProducers>
+__global__ void __launch_bounds__(CT + PT, 1)
     pipe_tile_kernel(const __grid_constant__ KParams p_in, const float* __restrict__ in, float* __restrict__ out, int ns, int ng,
                      int stage_bytes, int tables_in_smem, const __grid_constant__ CUtensorMap tmap)
 {
@@ -301,7 +304,7 @@ __global__ void __launch_bounds__(kPipeThreads, 1)
     const unsigned full0 = smem_u32(smem_raw + (size_t)ns * stage_bytes);
     const unsigned empty0 = full0 + 8 * ns;
     const int tid = threadIdx.x;
-    const int gt = kPipeCompute / ng;
+    const int gt = CT / ng;
     KParams p = p_in;
     if constexpr (Geo::kStatic) {
         p.scratch_off = 0;              // registered schedules have no generic prime step: fold that path away
@@ -328,7 +331,7 @@ __global__ void __launch_bounds__(kPipeThreads, 1)
         unsigned char* tb = smem_raw + (size_t)ns * stage_bytes + 2 * ns * 8 + 64;
         auto stash = [&](const void* src, int bytes) -> void* {
             void* dst = tb;
-            for (int i = tid * 4; i < bytes; i += kPipeThreads * 4) *(int*)(tb + i) = __ldg((const int*)((const unsigned char*)src + i));
+            for (int i = tid * 4; i < bytes; i += (CT + PT) * 4) *(int*)(tb + i) = __ldg((const int*)((const unsigned char*)src + i));
             tb += (bytes + 15) / 16 * 16;
             return dst;
         };
@@ -338,7 +341,7 @@ __global__ void __launch_bounds__(kPipeThreads, 1)
         }
         if (MODE != dft::MODE_C2C_COLS) {
             if constexpr (geo_two_rows<Geo>::value) {
-                Geo::fill_table((float2*)tb, p_in.tw_row, tid, kPipeThreads);   // p.tw_row now means T (dft_twostep.cuh)
+                Geo::fill_table((float2*)tb, p_in.tw_row, tid, CT + PT);   // p.tw_row now means T (dft_twostep.cuh)
                 p.tw_row = (const float2*)tb;
                 tb += (p_in.row.n * 8 + 15) / 16 * 16;
             } else if (Geo::kStatic || p_in.tw_row_t) {           // (the planner always provides it for the row modes)
@@ -352,7 +355,7 @@ __global__ void __launch_bounds__(kPipeThreads, 1)
     }
     if (tid == 0) {
         for (int s = 0; s < ns; ++s) {
-            asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(full0 + 8 * s), "r"(kPipeProducers) : "memory");
+            asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(full0 + 8 * s), "r"(PT) : "memory");
             asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(empty0 + 8 * s), "r"(gt / 32) : "memory");
         }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
@@ -360,8 +363,8 @@ __global__ void __launch_bounds__(kPipeThreads, 1)
     }
     __syncthreads();
 
-    if (tid >= kPipeCompute) {
-        const int pt = tid - kPipeCompute;
+    if (tid >= CT) {
+        const int pt = tid - CT;
         long long it = 0;
         for (long long tile = blockIdx.x; tile < p.ntiles; tile += gridDim.x, ++it) {
             const int s = (int)(it % ns);
@@ -369,7 +372,7 @@ __global__ void __launch_bounds__(kPipeThreads, 1)
             asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
             float2* buf = reinterpret_cast<float2*>(smem_raw + (size_t)s * stage_bytes);
             const unsigned bar = full0 + 8 * s;
-            const unsigned bulk = produce_tile<MODE>(p, tile, buf, in, pt, bar, &tmap);
+            const unsigned bulk = produce_tile<MODE, PT>(p, tile, buf, in, pt, bar, &tmap);
             if (bulk) {
                 if (pt != 0) asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
             } else {
@@ -427,8 +430,10 @@ namespace dft {
     X(128, 16, 8, 1, 8, 1, 16, 1, 64, true)     \
     X(64, 8, 8, 1, 8, 1, 8, 1, 64, true)
 
-pipe_fn pipe_kernel_for_geo(const KParams& k, bool tables_in_smem)
+pipe_fn pipe_kernel_for_geo(const KParams& k, bool tables_in_smem, int* compute_threads, int* producer_threads)
 {
+    *compute_threads = kPipeCompute;
+    *producer_threads = kPipeProducers;
     if (!tables_in_smem) return nullptr;                 // the static kernels keep their tables in shared memory
     const int mode = k.mode;
     const dft::LineFFT& f = mode == dft::MODE_C2C_COLS ? k.col : k.row;
@@ -445,8 +450,17 @@ pipe_fn pipe_kernel_for_geo(const KParams& k, bool tables_in_smem)
         return pipe_tile_kernel<dft::MODE_C2C_COLS, GeoLine<N_, A, B, C, D>>;
 #define DFT_GEO_TRY_COLS_TWO(N_, A, B, C, R1A, R1B, R2A, R2B, TM_, FOUR_)                                            \
     if (DFT_GEO_MATCH(N_, A, B, C, 1) && mode == dft::MODE_C2C_COLS && k.G == TM_ && !(k.inverse && k.n1split > 1) && (FOUR_ || k.n1split <= 1) && tables_in_smem && \
-        !getenv("TRT_DFT_NO_TWOSTEP"))                                                                         \
-        return pipe_tile_kernel<dft::MODE_C2C_COLS, GeoTwo<N_, A, B, C, R1A, R1B, R2A, R2B, TM_, FOUR_>>;
+        !getenv("TRT_DFT_NO_TWOSTEP")) {                                                                       \
+        /* both steps' work items (R2*TM and R1*TM) fit 480 threads: 16 warps, 128 registers (see pipe_tile_kernel) */ \
+        if constexpr ((R2A * R2B) * TM_ <= 480 && (R1A * R1B) * TM_ <= 480 && (R2A * R2B) * TM_ > 256) {       \
+            if (getenv("TRT_DFT_480")) { /* A/B only: measured slower, one producer warp cannot feed the tile ring */ \
+                *compute_threads = 480;                                                                        \
+                *producer_threads = 32;                                                                        \
+                return pipe_tile_kernel<dft::MODE_C2C_COLS, GeoTwo<N_, A, B, C, R1A, R1B, R2A, R2B, TM_, FOUR_>, 480, 32>; \
+            }                                                                                                  \
+        }                                                                                                      \
+        return pipe_tile_kernel<dft::MODE_C2C_COLS, GeoTwo<N_, A, B, C, R1A, R1B, R2A, R2B, TM_, FOUR_>>;    \
+    }
     DFT_GEO_COLS_TWO(DFT_GEO_TRY_COLS_TWO)
 #undef DFT_GEO_TRY_COLS_TWO
 #define DFT_GEO_TRY_ROWS_TWO(N_, A, B, C, R1A, R1B, R2A, R2B)                                                     \
