@@ -459,6 +459,13 @@ pipe_fn pipe_kernel_for_geo(const KParams& k, bool tables_in_smem, int* compute_
                 return pipe_tile_kernel<dft::MODE_C2C_COLS, GeoTwo<N_, A, B, C, R1A, R1B, R2A, R2B, TM_, FOUR_>, 480, 32>; \
             }                                                                                                  \
         }                                                                                                      \
+        /* four producer warps instead of two (20 warps still leave 96 registers) where the producers compute every row */ \
+        /* address (index-reversed first pass of an inverse four-step FFT: cfg5 inverse 1.65 -> 1.57 ms; elsewhere +-1 %) */ \
+        if (k.rev_in && !getenv("TRT_DFT_NO_P128")) {                                                          \
+            *compute_threads = 512;                                                                            \
+            *producer_threads = 128;                                                                           \
+            return pipe_tile_kernel<dft::MODE_C2C_COLS, GeoTwo<N_, A, B, C, R1A, R1B, R2A, R2B, TM_, FOUR_>, 512, 128>; \
+        }                                                                                                      \
         return pipe_tile_kernel<dft::MODE_C2C_COLS, GeoTwo<N_, A, B, C, R1A, R1B, R2A, R2B, TM_, FOUR_>>;    \
     }
     DFT_GEO_COLS_TWO(DFT_GEO_TRY_COLS_TWO)
