@@ -240,10 +240,9 @@ int trt_dft_plan_create_truncated(trt_dft_plan_t* plan_out, int direction, const
     }
     char desc[192];
     const SpecEntry* e = (batch > 0 && !getenv("TRT_DFT_NO_SPEC")) ? find_spec((int)H, (int)W) : nullptr;
-    // The fused kernels pay for compacting / expanding the kept block in shared memory; measured on B200 they win while
-    // the block is at most ~60 % of the spectrum, beyond that the full kernels plus a crop / zero-pad pass are faster.
-    const bool small_keep = 2 * keep_h * keep_w * 10 <= H * MO * 6 || getenv("TRT_DFT_TRUNC_FUSED");
-    if (e && e->trunc_fwd && e->trunc_inv && small_keep) {
+    // (The fused kernels pay for compacting / expanding the kept block in shared memory, but measured on B200 they beat the
+    // full kernels plus a crop / zero-pad pass at every kept fraction: 0.44 vs 0.65 ms per pair even when everything is kept.)
+    if (e && e->trunc_fwd && e->trunc_inv && !getenv("TRT_DFT_TRUNC_UNFUSED")) {
         pl->t_fwd = e->trunc_fwd;
         pl->t_inv = e->trunc_inv;
         pl->t_threads = e->NT;

@@ -77,7 +77,7 @@ def test_full_keep_equals_the_ordinary_transform():
     t = torch.empty(200, 90, 91, 2, device="cuda")
     capi.TruncatedPlan(capi.FORWARD, (90, 180), 200, 45, 91).exec(x, t)
     torch.cuda.synchronize()
-    assert torch.equal(t, full)                 # same arithmetic, only the store differs
+    assert torch.equal(t, full)                 # same arithmetic, only the way out of shared memory differs
     back = torch.empty_like(x)
     capi.TruncatedPlan(capi.INVERSE, (90, 180), 200, 45, 91).exec(full, back)
     torch.cuda.synchronize()
