@@ -37,6 +37,7 @@ SHAPE = (8, 768, 90, 180)
 H, W = 90, 180
 MO = W // 2 + 1
 METRIC = "rfft2+irfft2 algorithmic HBM GB/s at AFNO [8,768,90,180] fp32"
+EXTRAS_TIMEOUT_S = 420
 
 
 def algo_bytes_one_direction(nimg):
@@ -521,32 +522,7 @@ def run_ours(args):
     torch.cuda.empty_cache()
     peak, peak_src = measured_peak()
 
-    # ---- beyond the headline: the other BASELINE configs, the reference's cuFFT sequence, the multi-GPU paths ----
-    extras = {}
-    if args.headline_only:
-        pass
-    elif world == 1:
-        try:
-            extras["all_configs"] = {n: time_config(capi, torch, n, 200 if n in ("cfg1", "cfg2") else 10, peak)
-                                     for n in ("cfg1", "cfg2", "cfg4", "cfg5")}
-        except Exception as e:
-            extras["all_configs"] = {"error": repr(e)[:300]}
-        torch.cuda.empty_cache()
-        try:
-            extras["truncated_modes"] = truncated_bench(capi, torch, peak)
-        except Exception as e:
-            extras["truncated_modes"] = {"error": repr(e)[:300]}
-        extras["cufft_sequence"] = cufft_sequence(torch, capi, ["cfg1", "cfg2", "cfg3", "cfg4", "cfg5"])
-    else:
-        try:
-            extras["cfg4_shard"] = cfg4_shard(capi, torch, dist, world, rank, dev, peak)
-        except Exception as e:
-            extras["cfg4_shard"] = {"error": repr(e)[:300]}
-        try:
-            extras["pencil"] = pencil_bench(torch, dist, world, rank, dev)
-        except Exception as e:
-            extras["pencil"] = {"error": repr(e)[:300]}
-
+    line = None
     if rank == 0:
         pair_bytes = 2 * algo_bytes_one_direction(nimg)
         gbs = world * pair_bytes * args.steps / (ms * 1e-3) / 1e9
@@ -583,7 +559,6 @@ def run_ours(args):
             "clocks": clocks,
             "plan": plan_desc,
         }
-        line.update(extras)
         if world == 1:
             os.sched_setaffinity(0, orig_affinity)          # the CPU baseline gets every host core again
             cores = len(os.sched_getaffinity(0)) or 1
@@ -592,7 +567,52 @@ def run_ours(args):
             line["cpu_baseline"] = {"value": 2 * algo_bytes_one_direction(sample) / t / 1e9, "unit": "GB/s", "cores": cores,
                                     "kind": "port",
                                     "sample": f"torch.fft rfft2+irfft2 (reference tests' oracle) on [{sample},90,180] fp32, best of 3"}
-        print(json.dumps(line))
+    # The headline line must come out even if one of the extra measurements below hangs (a multi-rank collective with a
+    # rank missing, a comparator subprocess): after EXTRAS_TIMEOUT_S rank 0 prints what it has and every rank leaves.
+    emitted = threading.Event()
+
+    def emit(extra):
+        if rank == 0 and not emitted.is_set():
+            emitted.set()
+            line.update(extra)
+            print(json.dumps(line), flush=True)
+
+    def give_up():
+        emit({"extras": f"timed out after {EXTRAS_TIMEOUT_S} s; the headline above was measured normally"})
+        os._exit(0)
+
+    watchdog = threading.Timer(EXTRAS_TIMEOUT_S, give_up)
+    watchdog.daemon = True
+    watchdog.start()
+
+    # ---- beyond the headline: the other BASELINE configs, the reference's cuFFT sequence, the multi-GPU paths ----
+    extras = {}
+    if args.headline_only:
+        pass
+    elif world == 1:
+        try:
+            extras["all_configs"] = {n: time_config(capi, torch, n, 200 if n in ("cfg1", "cfg2") else 10, peak)
+                                     for n in ("cfg1", "cfg2", "cfg4", "cfg5")}
+        except Exception as e:
+            extras["all_configs"] = {"error": repr(e)[:300]}
+        torch.cuda.empty_cache()
+        try:
+            extras["truncated_modes"] = truncated_bench(capi, torch, peak)
+        except Exception as e:
+            extras["truncated_modes"] = {"error": repr(e)[:300]}
+        extras["cufft_sequence"] = cufft_sequence(torch, capi, ["cfg1", "cfg2", "cfg3", "cfg4", "cfg5"])
+    else:
+        try:
+            extras["cfg4_shard"] = cfg4_shard(capi, torch, dist, world, rank, dev, peak)
+        except Exception as e:
+            extras["cfg4_shard"] = {"error": repr(e)[:300]}
+        try:
+            extras["pencil"] = pencil_bench(torch, dist, world, rank, dev)
+        except Exception as e:
+            extras["pencil"] = {"error": repr(e)[:300]}
+
+    watchdog.cancel()
+    emit(extras)
     if world > 1:
         dist.destroy_process_group()
 
