@@ -82,3 +82,20 @@ def test_full_keep_equals_the_ordinary_transform():
     capi.TruncatedPlan(capi.INVERSE, (90, 180), 200, 45, 91).exec(full, back)
     torch.cuda.synchronize()
     assert torch.equal(back, capi.irfftn(full, 2))
+
+
+@pytest.mark.parametrize("H,W,kh,kw", [(90, 180, 10, 16), (64, 64, 8, 12)])
+def test_truncated_plans_through_the_host_buffer_call(H, W, kh, kw):
+    """trt_dft_exec_host with a truncated plan (fused route and crop / pad route): host buffers in and out."""
+    from trt_dft_plugins import capi
+    torch.manual_seed(5)
+    batch = 9
+    x = torch.randn(batch, H, W).pin_memory()
+    out = torch.empty(batch, 2 * kh, kw, 2).pin_memory()
+    capi.TruncatedPlan(capi.FORWARD, (H, W), batch, kh, kw).exec_host(x, out)
+    want = oracle_truncated(x, kh, kw)
+    assert O.rel_l2(out.numpy(), want.numpy()) <= 1e-5
+    back = torch.empty(batch, H, W).pin_memory()
+    capi.TruncatedPlan(capi.INVERSE, (H, W), batch, kh, kw).exec_host(out, back)
+    want_x = oracle_padded_inverse(out, H, W, kh, kw)
+    assert O.rel_l2(back.numpy(), want_x.numpy()) <= 1e-5
