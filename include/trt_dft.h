@@ -67,7 +67,7 @@ int trt_dft_plan_create(trt_dft_plan_t* plan, int direction, int rank, const int
  * exp(-i..), TRT_DFT_INVERSE exp(+i..).  `in` may equal `out` in trt_dft_exec (each tile is read
  * completely before it is written; lengths outside the radix set go through the workspace for that).  Query
  * trt_dft_workspace_bytes: it is non-zero for long axes (>= 4096 points, run as a four-step FFT through a
- * workspace copy of the tensor) and for lengths with a prime factor above 31.
+ * workspace copy of the tensor) and for lengths with a prime factor above 8191 (naive kernel, never in place).
  */
 int trt_dft_plan_create_c2c(trt_dft_plan_t* plan, int direction, int64_t n, int64_t outer, int64_t inner, float scale);
 
