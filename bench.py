@@ -349,6 +349,11 @@ def pencil_bench(torch, dist, world, rank, dev, iters=10):
     en = ((yn - ref).double().norm() / ref.double().norm()).reshape(1)
     dist.all_reduce(en, op=dist.ReduceOp.MAX)
     out["nccl_rel_l2"] = en.item()
+    xn = pn.inverse(yn)
+    torch.cuda.synchronize()
+    ern = ((xn - x_loc).double().norm() / x_loc.double().norm()).reshape(1)
+    dist.all_reduce(ern, op=dist.ReduceOp.MAX)
+    out["nccl_round_trip_rel_l2"] = ern.item()
     out["nccl_ms"] = timed(lambda: pn.forward(x_loc), iters)
     yr = pn.row_pass(x_loc)
     z = pn.transpose(yr)

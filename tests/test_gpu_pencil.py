@@ -97,3 +97,54 @@ def test_peer_split_addresses_with_several_destinations_on_one_gpu():
             got = bands[j][:, :, c0:c0 + cn]
             assert O.rel_l2(got.cpu().numpy(), want[:, rstarts[j]:rstarts[j + 1]].cpu().numpy()) <= 1e-5
             assert torch.isnan(bands[j][:, :, :c0]).all() and torch.isnan(bands[j][:, :, c0 + cn:]).all()
+
+
+def _two_gpu_worker(rank, world, port, out_dir):
+    import os
+    import sys
+    from pathlib import Path
+    root = Path(__file__).resolve().parent.parent
+    sys.path.insert(0, str(root / "tensorrt-dft-plugins_b200"))
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    import torch.distributed as dist
+    torch.cuda.set_device(rank)
+    dev = torch.device("cuda", rank)
+    dist.init_process_group("nccl", rank=rank, world_size=world, device_id=dev)
+    from trt_dft_plugins import capi
+    from trt_dft_plugins.pencil import PencilRfft2
+    res = {}
+    for (B, H, W) in ((2, 720, 1440), (1, 8192, 2048), (3, 96, 200)):
+        g = torch.Generator(device=dev).manual_seed(21)
+        full = torch.randn(B, H, W, device=dev, generator=g)          # same on both ranks
+        ref = capi.rfftn(full, 2)
+        for mode in ("peer", "nccl"):
+            p = PencilRfft2(B, H, W, device=dev, exchange="auto" if mode == "peer" else "nccl")
+            x_loc = full[:, p.h0:p.h0 + p.hn].contiguous()
+            y = p.forward(x_loc)
+            torch.cuda.synchronize()
+            want = ref[:, :, p.c0:p.c0 + p.cn]
+            e_f = ((y - want).double().norm() / want.double().norm()).item()
+            xb = p.inverse(y.clone())
+            torch.cuda.synchronize()
+            e_i = ((xb - x_loc).double().norm() / x_loc.double().norm()).item()
+            res[(B, H, W, mode)] = (e_f, e_i, p.exchange_used)
+    torch.save(res, os.path.join(out_dir, f"r{rank}.pt"))
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+def test_pencil_on_two_gpus_over_peer_memory_and_nccl(tmp_path):
+    """The real exchange, both ways of running it and both directions, at world size 2 (skipped on a one-GPU box; the same
+    check runs inside `bench.py --gpus N` and is printed as `pencil.rel_l2`)."""
+    import os
+    import torch.multiprocessing as mp
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs two GPUs")
+    port = 32500 + (os.getpid() % 2000)
+    mp.spawn(_two_gpu_worker, args=(2, port, str(tmp_path)), nprocs=2, join=True)
+    for r in range(2):
+        res = torch.load(tmp_path / f"r{r}.pt")
+        for key, (e_f, e_i, used) in res.items():
+            assert e_f <= 1e-6 and e_i <= 1e-6, (key, e_f, e_i, used)
+            assert used.startswith("peer") or key[3] == "nccl", (key, used)
