@@ -331,6 +331,8 @@ def pencil_bench(torch, dist, world, rank, dev, iters=10):
     y = p.forward(x_loc)
     torch.cuda.synchronize()
     out["exchange"] = p.exchange_used
+    if isinstance(getattr(p, "_peer", None), dict):
+        out["row_kernel"] = p._peer["rows"].describe()[1].split(" [0]")[-1]
     if getattr(p, "_peer_error", None):
         out["peer_unavailable"] = p._peer_error
     err = ((y - ref).double().norm() / ref.double().norm())

@@ -104,13 +104,18 @@ int trt_dft_plan_create_truncated(trt_dft_plan_t* plan, int direction, const int
  * dft_plugins.cpp:341).  Same column split as trt_dft_plan_set_column_split, but block j of every image is not
  * packed into `out`: the row kernel stores it straight into rank j's column slab
  *     peer_slabs[j][image][image_rows][col_starts[j+1] - col_starts[j]]   (interleaved complex fp32)
- * at rows row_offset .. row_offset + rows_per_image - 1 -- ordinary global stores through a peer mapping of that
- * GPU's memory (CUDA IPC / symmetric memory; peer_slabs[own rank] is simply local memory).  `out` of trt_dft_exec
- * is then unused (pass any valid pointer).  The caller synchronises the ranks (all rows written before any rank
- * starts its column pass, and nobody overwrites a slab that is still being read).  nparts <= 8.
+ * at rows row_offset .. row_offset + rows_per_image - 1 -- stores through a peer mapping of that GPU's memory (CUDA
+ * IPC / symmetric memory; peer_slabs[own rank] is simply local memory).  `out` of trt_dft_exec is then unused (pass
+ * any valid pointer).  The caller synchronises the ranks (all rows written before any rank starts its column pass,
+ * and nobody overwrites a slab that is still being read).  nparts <= 8.
+ *   slab_pitches : row pitch of each slab in complex elements (NULL: dense, pitch = its column count).
+ * When every col_starts[j] is even, every pitch is even and at least the slab's column count rounded up to even, and
+ * the slabs are 16-byte aligned, each (row, destination) run leaves shared memory as ONE bulk copy (TMA store into the
+ * peer's memory) that overlaps the next rows' transform; an odd column count then also writes the slab's padding
+ * column.  Otherwise the kernel falls back to 8-byte stores from its registers.
  */
 int trt_dft_plan_set_peer_column_split(trt_dft_plan_t plan, int nparts, const int64_t* col_starts, int64_t rows_per_image,
-                                       int64_t image_rows, int64_t row_offset, void* const* peer_slabs);
+                                       int64_t image_rows, int64_t row_offset, void* const* peer_slabs, const int64_t* slab_pitches);
 
 /*
  * The mirror image for the pencil irfft2: a trt_dft_plan_create_c2c plan over data[outer][n][inner] stores output row

@@ -115,6 +115,8 @@ struct ResolvedLaunch {
                                      // (the two-step row programs write plain rows only)
     int gp_ns = 0, gp_ng = 0, gp_stage = 0, gp_smem = 0, gp_grid = 0, gp_tables = 0;
     int gp_threads = dft::kPipeThreads, gp_threads_pack = dft::kPipeThreads;   // CTA size of gpipe / gpipe_pack
+    int gp_smem_nopack = 0;          // gp_smem without the staging rows of the bulk-store epilogue
+    int gp_ns_pack = 0, gp_ng_pack = 0;   // ring depth / groups while the bulk-store epilogue is on
 };
 
 }  // namespace
@@ -447,6 +449,7 @@ static int realize_plan(trt_dft_plan_s* pl, trt_dft_plan_t* plan_out)
                     if (getenv("TRT_DFT_GP_NG")) r.gp_ng = std::max(1, std::min(atoi(getenv("TRT_DFT_GP_NG")), ns - 1));
                     r.gp_stage = stage;
                     r.gp_smem = smem;
+                    r.gp_smem_nopack = smem;
                     r.gp_grid = (int)std::min<long long>(r.kp.ntiles, num_sms);
                 } else {
                     cudaGetLastError();
@@ -504,11 +507,14 @@ int trt_dft_plan_set_column_split(trt_dft_plan_t plan, int nparts, const int64_t
     for (int j = 0; nparts > 0 && j <= nparts; ++j) k.pack_c0[j] = (int)col_starts[j];   // (nparts == 0: back to plain rows, col_starts may be null)
     k.pack_hn = (int)rows_per_image;
     k.pack_peer_on = 0;
+    k.pack_bulk = 0;
+    for (int j = 0; j < 8; ++j) k.pack_pitch[j] = j < nparts ? (int)(col_starts[j + 1] - col_starts[j]) : 0;
+    plan->launches[0].gp_smem = plan->launches[0].gp_smem_nopack;
     return TRT_DFT_OK;
 }
 
 int trt_dft_plan_set_peer_column_split(trt_dft_plan_t plan, int nparts, const int64_t* col_starts, int64_t rows_per_image,
-                                       int64_t image_rows, int64_t row_offset, void* const* peer_slabs)
+                                       int64_t image_rows, int64_t row_offset, void* const* peer_slabs, const int64_t* slab_pitches)
 {
     if (nparts < 1 || !peer_slabs || image_rows < 1 || row_offset < 0 || row_offset + rows_per_image > image_rows ||
         image_rows > (1LL << 30))
@@ -517,11 +523,49 @@ int trt_dft_plan_set_peer_column_split(trt_dft_plan_t plan, int nparts, const in
         if (!peer_slabs[j] || ((uintptr_t)peer_slabs[j] & 7)) return TRT_DFT_ERR_INVALID_ARG;
     const int rc = trt_dft_plan_set_column_split(plan, nparts, col_starts, rows_per_image);
     if (rc != TRT_DFT_OK) return rc;
-    KParams& k = plan->launches[0].kp;
+    ResolvedLaunch& rl = plan->launches[0];
+    KParams& k = rl.kp;
+    for (int j = 0; j < nparts; ++j) {
+        const int64_t cn = col_starts[j + 1] - col_starts[j];
+        const int64_t pitch = slab_pitches ? slab_pitches[j] : cn;
+        if (pitch < cn || pitch > (1LL << 30)) return TRT_DFT_ERR_INVALID_ARG;
+        k.pack_pitch[j] = (int)pitch;
+    }
     k.pack_peer_on = 1;
     k.pack_H = (int)image_rows;
     k.pack_h0 = (int)row_offset;
     for (int j = 0; j < 8; ++j) k.pack_peer[j] = j < nparts ? (float2*)peer_slabs[j] : nullptr;
+    // Bulk stores (KParams::pack_bulk): every run [c0, c0 + cn) of a staged row must start and end on 16 bytes on both
+    // sides -- even column starts, even pitches that cover an odd cn rounded up, 16-byte aligned slabs -- and the staging rows
+    // of the compute groups must fit beside the tile ring.
+    k.pack_bulk = 0;
+    bool ok = rl.gpipe_pack != nullptr && !getenv("TRT_DFT_NO_PEER_BULK");
+    for (int j = 0; ok && j < nparts; ++j) {
+        const int64_t cn = col_starts[j + 1] - col_starts[j];
+        ok = (col_starts[j] % 2 == 0) && (k.pack_pitch[j] % 2 == 0) && (k.pack_pitch[j] >= (cn + 1) / 2 * 2) && (((uintptr_t)peer_slabs[j] & 15) == 0);
+    }
+    rl.gp_ns_pack = rl.gp_ns;
+    rl.gp_ng_pack = rl.gp_ng;
+    if (ok) {
+        // Room for the staging rows: the split twiddles leave shared memory (the kernel reads them from global memory in
+        // this mode) and the tile ring gives up stages until everything fits.
+        const int mo_pad = (k.M + 1 + 1) / 2 * 2;                       // staging row: M + 1 results + padding to an even count
+        const int stage_bytes = (k.G * mo_pad * 8 + 127) / 128 * 128;
+        const int tabs = rl.gp_tables ? k.row.n * 12 + 128 : 0;         // per-step twiddles ((n - 1) * 8) + permutation (n * 4), 16-byte rounding
+        for (int ns = rl.gp_ns; ns >= 2 && !k.pack_bulk; --ns) {
+            const int ng = std::min(rl.gp_ng, ns >= 3 ? 2 : 1);
+            const int base = (ns * rl.gp_stage + 2 * ns * 8 + 64 + tabs + 127) / 128 * 128;
+            if (base + ng * stage_bytes > dft::kSmemMax) continue;
+            k.pack_bulk = 1;
+            k.pack_mo_pad = mo_pad;
+            k.pack_stage_off = base;
+            k.pack_stage_bytes = stage_bytes;
+            rl.gp_ns_pack = ns;
+            rl.gp_ng_pack = ng;
+            rl.gp_smem = base + ng * stage_bytes;
+        }
+    }
+    if (!k.pack_bulk) rl.gp_smem = rl.gp_smem_nopack;
     return TRT_DFT_OK;
 }
 
@@ -585,8 +629,9 @@ int trt_dft_plan_describe(trt_dft_plan_t plan, char* buf, size_t len)
             char t[128];
             const auto& rl = plan->launches[i];
             if (rl.gpipe && !rl.spec)
-                snprintf(t, sizeof t, "%s[%d]pipelined grid=%dx%d stages=%d groups=%d", i ? "," : " ", (int)i, rl.gp_grid,
-                         rl.gp_threads, rl.gp_ns, rl.gp_ng);
+                snprintf(t, sizeof t, "%s[%d]pipelined grid=%dx%d stages=%d groups=%d%s", i ? "," : " ", (int)i, rl.gp_grid,
+                         rl.gp_threads, rl.kp.pack_bulk ? rl.gp_ns_pack : rl.gp_ns, rl.kp.pack_bulk ? rl.gp_ng_pack : rl.gp_ng,
+                         rl.kp.pack_bulk ? " bulk-stores-to-peers" : (rl.kp.pack_peer_on ? " stores-to-peers" : ""));
             else
                 snprintf(t, sizeof t, rl.spec ? "%s[%d]grid=%dx%d smem=%d" : "%s[%d]grid=%dx%d", i ? "," : " ", (int)i,
                          rl.spec ? rl.spec_grid : rl.grid, rl.spec ? rl.spec_nt : rl.kp.threads, rl.spec_smem);
@@ -688,7 +733,8 @@ int trt_dft_exec(trt_dft_plan_t plan, const void* in, void* out, void* workspace
             KParams kp = r.kp;
             // the second four-step pass fetches its tiles from the padded workspace with one 2-D TMA tensor copy each
             if (kp.tma_cols && !(kp.mode == dft::MODE_C2C_COLS && encode_cols_tensor_map(&tmap, kp, src))) kp.tma_cols = 0;
-            (kp.pack_n ? r.gpipe_pack : r.gpipe)<<<r.gp_grid, kp.pack_n ? r.gp_threads_pack : r.gp_threads, r.gp_smem, st>>>(kp, src, dst, r.gp_ns, r.gp_ng, r.gp_stage,
+            (kp.pack_n ? r.gpipe_pack : r.gpipe)<<<r.gp_grid, kp.pack_n ? r.gp_threads_pack : r.gp_threads, r.gp_smem, st>>>(kp, src, dst, kp.pack_bulk ? r.gp_ns_pack : r.gp_ns,
+                                                                                          kp.pack_bulk ? r.gp_ng_pack : r.gp_ng, r.gp_stage,
                                                                                           r.gp_tables, tmap);
         } else
             r.fn<<<r.grid, r.kp.threads, r.kp.smem_bytes, st>>>(r.kp, src, dst);

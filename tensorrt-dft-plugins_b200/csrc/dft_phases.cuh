@@ -44,7 +44,7 @@ DFT_HD float2* packed_ptr(const KParams& p, float2* out, int R, int k, int Mo)
     const int b = R / p.pack_hn, rl = R - b * p.pack_hn;
     // fully unrolled with constant indices: a run-time index into p.pack_c0 would push the kernel's
     // private KParams copy into local memory
-    int c0 = p.pack_c0[0], cn = p.pack_c0[1] - p.pack_c0[0];
+    int c0 = p.pack_c0[0], cn = p.pack_c0[1] - p.pack_c0[0], pitch = p.pack_pitch[0];
     float2* peer = p.pack_peer[0];
 #if defined(__CUDA_ARCH__)
 #pragma unroll
@@ -54,10 +54,11 @@ DFT_HD float2* packed_ptr(const KParams& p, float2* out, int R, int k, int Mo)
             c0 = p.pack_c0[t];
             cn = p.pack_c0[t + 1] - p.pack_c0[t];
             peer = p.pack_peer[t];
+            pitch = p.pack_pitch[t];
         }
     }
-    if (p.pack_peer_on)   // straight into the owning rank's slab [image][pack_H][cn]
-        return peer + ((long long)b * p.pack_H + p.pack_h0 + rl) * cn + (k - c0);
+    if (p.pack_peer_on)   // straight into the owning rank's slab [image][pack_H][pitch >= cn]
+        return peer + ((long long)b * p.pack_H + p.pack_h0 + rl) * pitch + (k - c0);
     return out + (long long)b * p.pack_hn * Mo + (long long)p.pack_hn * c0 + (long long)rl * cn + (k - c0);
 }
 

@@ -34,6 +34,7 @@ using dft::kPipeThreads;
 // taken is re-read from local memory after every barrier's memory clobber -- a long-scoreboard stall per barrier)
 struct GroupCtx {
     const int tid, nthr, bar_id;
+    float2* const stg;                  // this group's staging rows for bulk stores (KParams::pack_bulk), else null
     __host__ __device__ __forceinline__ void sync() const
     {
 #if defined(__CUDA_ARCH__)
@@ -41,6 +42,32 @@ struct GroupCtx {
 #endif
     }
     __host__ __device__ __forceinline__ bool bulk_load(void*, const void*, long long) const { return false; }
+    // bulk stores shared -> global (possibly a peer GPU's memory): issued and awaited by one thread of the group
+    __host__ __device__ __forceinline__ float2* stage_out() const { return stg; }
+    __host__ __device__ __forceinline__ void fence_async_shared() const
+    {
+#if defined(__CUDA_ARCH__)
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+#endif
+    }
+    __host__ __device__ __forceinline__ void bulk_store(void* dst, const void* src, unsigned bytes) const
+    {
+#if defined(__CUDA_ARCH__)
+        asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(dst), "r"(smem_u32(src)), "r"(bytes) : "memory");
+#endif
+    }
+    __host__ __device__ __forceinline__ void commit_bulk_stores() const
+    {
+#if defined(__CUDA_ARCH__)
+        asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+#endif
+    }
+    __host__ __device__ __forceinline__ void wait_bulk_stores_read() const
+    {
+#if defined(__CUDA_ARCH__)
+        if (tid == 0) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
+#endif
+    }
 };
 
 __device__ __forceinline__ void cp_async8(void* dst, const void* src)
@@ -350,7 +377,8 @@ __global__ void __launch_bounds__(CT + PT, 1)
                 p.tw_row = (const float2*)stash(p_in.tw_row, p_in.row.n * 8);
             }
             p.perm_row = (const int*)stash(p_in.perm_row, p_in.row.n * 4);
-            p.tw_unt = (const float2*)stash(p_in.tw_unt, (p_in.M + 1) * 8);
+            // (bulk-store epilogue: the split twiddles stay in global memory, their 8 (M + 1) bytes go to the staging rows)
+            if (!p_in.pack_bulk) p.tw_unt = (const float2*)stash(p_in.tw_unt, (p_in.M + 1) * 8);
         }
     }
     if (tid == 0) {
@@ -383,7 +411,8 @@ __global__ void __launch_bounds__(CT + PT, 1)
         return;
     }
     const int g = tid / gt;
-    const GroupCtx ctx{tid - g * gt, gt, 1 + g};
+    const GroupCtx ctx{tid - g * gt, gt, 1 + g,
+                       p_in.pack_bulk ? reinterpret_cast<float2*>(smem_raw + p_in.pack_stage_off + (size_t)g * p_in.pack_stage_bytes) : nullptr};
     long long it = g;
     for (long long tile = blockIdx.x + (long long)g * gridDim.x; tile < p.ntiles; tile += (long long)ng * gridDim.x, it += ng) {
         const int s = (int)(it % ns);
@@ -407,6 +436,8 @@ __global__ void __launch_bounds__(CT + PT, 1)
         __syncwarp();
         if ((tid & 31) == 0) asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(empty0 + 8 * s) : "memory");
     }
+    // bulk stores out of the staging rows must have completed before the CTA's shared memory goes away
+    if (p.pack_bulk && ctx.tid == 0) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
 }
 
 }  // namespace

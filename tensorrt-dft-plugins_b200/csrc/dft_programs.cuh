@@ -169,6 +169,13 @@ DFT_HD void program_f1d(const KParams& p, long long tile, float2* buf, const flo
     // real-FFT split, two outputs per item: X[k] and X[M-k] come from the same pair Z[k], Z[M-k]
     float2* o = (float2*)out + first * Mo;
     const int per_row = M / 2 + 1;
+    // KParams::pack_bulk: results go to the group's staging rows (natural order) and leave as bulk copies below
+    float2* stg = nullptr;
+    if (p.pack_bulk) {
+        stg = ctx.stage_out();
+        ctx.wait_bulk_stores_read();                      // the previous tile's copies have read the staging rows
+        ctx.sync();
+    }
     const int total = nrows * per_row;
     const unsigned omg = magic_of((unsigned)per_row);
     for (int idx = ctx.tid; idx < total; idx += ctx.nthr) {
@@ -184,7 +191,11 @@ DFT_HD void program_f1d(const KParams& p, long long tile, float2* buf, const flo
         const float tx = 0.5f * (w.x * dx - w.y * dy), ty = 0.5f * (w.x * dy + w.y * dx);
         const float2 x1 = float2{0.5f * sx + ty, 0.5f * sy - tx};
         const float2 x2 = float2{0.5f * sx - ty, -0.5f * sy - tx};
-        if (p.pack_n == 0) {
+        if (stg) {
+            float2* srow = stg + r * p.pack_mo_pad;
+            srow[k] = x1;
+            if (kk != k) srow[kk] = x2;
+        } else if (p.pack_n == 0) {
             float2* orow = o + (long long)r * Mo;
             orow[k] = x1;
             if (kk != k) orow[kk] = x2;
@@ -194,6 +205,30 @@ DFT_HD void program_f1d(const KParams& p, long long tile, float2* buf, const flo
             *packed_ptr(p, ob, R, k, Mo) = x1;
             if (kk != k) *packed_ptr(p, ob, R, kk, Mo) = x2;
         }
+    }
+    if (stg) {
+        // one bulk copy per (row, destination): columns [c0, c0 + cn) of the row into the owner's slab.  An odd cn is
+        // rounded up: the extra element lands in the slab's padding column (pitch even, > cn) and comes from the staging
+        // row's padding.
+        ctx.fence_async_shared();
+        ctx.sync();
+        if (ctx.tid == 0) {
+            for (int r = 0; r < nrows; ++r) {
+                const int R = (int)first + r, b = R / p.pack_hn, rl = R - b * p.pack_hn;
+#if defined(__CUDA_ARCH__)
+#pragma unroll
+#endif
+                for (int t = 0; t < 8; ++t) {
+                    if (t >= p.pack_n) break;
+                    const int c0 = p.pack_c0[t], cn = p.pack_c0[t + 1] - c0;
+                    if (cn <= 0) continue;
+                    float2* dst = p.pack_peer[t] + ((long long)b * p.pack_H + p.pack_h0 + rl) * p.pack_pitch[t];
+                    ctx.bulk_store(dst, stg + r * p.pack_mo_pad + c0, (unsigned)((cn + 1) / 2 * 16));
+                }
+            }
+            ctx.commit_bulk_stores();
+        }
+        return;                                           // (the next tile's first barrier follows its own loads)
     }
     ctx.sync();
 }

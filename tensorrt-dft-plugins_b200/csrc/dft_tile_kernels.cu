@@ -29,6 +29,13 @@ struct CtaCtx {
 #endif
     }
 
+    // bulk stores out of staging rows exist in the pipelined shell only (KParams::pack_bulk is never set here)
+    __host__ __device__ __forceinline__ float2* stage_out() const { return nullptr; }
+    __host__ __device__ __forceinline__ void fence_async_shared() const {}
+    __host__ __device__ __forceinline__ void bulk_store(void*, const void*, unsigned) const {}
+    __host__ __device__ __forceinline__ void commit_bulk_stores() const {}
+    __host__ __device__ __forceinline__ void wait_bulk_stores_read() const {}
+
     // Whole-tile global->shared copy by the TMA unit (1-D bulk copy).  All threads call it with
     // identical arguments; returns false (nothing done) when the copy is not 16-byte clean.
     __host__ __device__ __forceinline__ bool bulk_load(void* dst, const void* src, long long bytes)

@@ -159,6 +159,15 @@ struct KParams {
     int pack_H;
     int pack_h0;
     float2* pack_peer[8];
+    int pack_pitch[8];       // row pitch of rank j's slab in complex elements (>= its column count)
+    // pack_bulk != 0 (pipelined kernel only): the split result of a tile is staged in shared memory in natural order
+    // (pack_stage_off bytes into the CTA's shared memory, pack_stage_bytes per compute group, row pitch pack_mo_pad
+    // elements) and every (row, destination) run leaves as ONE bulk copy (cp.async.bulk shared -> peer global), which
+    // keeps the NVLink stores going while the group transforms its next tile.  Needs even column starts and even pitches.
+    int pack_bulk;
+    int pack_stage_off;
+    int pack_stage_bytes;
+    int pack_mo_pad;
     // MODE_C2C_COLS, mirror image of the above (pencil irfft2, exchange fused into the column pass): output row q of
     // every image belongs to the rank j with split_r0[j] <= q < split_r0[j+1] and is stored into that rank's row band
     // [image][rows of rank j][split_pitch columns] at split_peer[j], starting at column split_c0 (this rank's first

@@ -35,6 +35,21 @@ import torch.distributed as dist
 from .multi_gpu import shard_batch
 
 
+def even_column_split(ncols: int, world: int):
+    """(start, count) of every rank's column band of the one-sided spectrum.  Every band but the last has an even number of
+    columns, so every band STARTS on an even column: a band of a staged row is then 16-byte aligned in shared memory and
+    in the owner's slab, which lets the row kernel send it as one bulk copy (trt_dft_plan_set_peer_column_split).  The
+    last band takes what is left (W/2 + 1 is odd for even W, so one band has to be odd)."""
+    if world == 1:
+        return [(0, ncols)]
+    base = (ncols // world) // 2 * 2
+    if base == 0:
+        return [shard_batch(ncols, r, world) for r in range(world)]
+    spans = [(r * base, base) for r in range(world - 1)]
+    spans.append(((world - 1) * base, ncols - (world - 1) * base))
+    return spans
+
+
 class PeerBuffer:
     """`nfloats` fp32 of device memory on every rank of the group, each rank's copy mapped into every other rank's
     address space.  ptrs[r] is rank r's buffer as seen from this process; barrier() is a GPU-side barrier on the
@@ -86,7 +101,7 @@ class PencilRfft2:
         self.rank = dist.get_rank(group) if dist.is_initialized() else 0
         self.device = device
         self.row_spans = [shard_batch(self.H, r, self.world) for r in range(self.world)]    # (h0, hn) per rank
-        self.col_spans = [shard_batch(self.Mo, r, self.world) for r in range(self.world)]   # (c0, cn) per rank
+        self.col_spans = even_column_split(self.Mo, self.world)                             # (c0, cn) per rank
         self.h0, self.hn = self.row_spans[self.rank]
         self.c0, self.cn = self.col_spans[self.rank]
         self._row_fft, self._col_fft = row_fft, col_fft
@@ -161,7 +176,8 @@ class PencilRfft2:
 
     def forward(self, x_local):
         """x_local: this rank's row band [B, H_r, W] (fp32).  Returns its column band [B, H, C_r, 2].  With the peer
-        exchange the result is a view of the rank's peer-mapped slab: it stays valid until the next forward()."""
+        exchange the result is a view of the rank's peer-mapped slab: it stays valid until the next forward(), and its
+        rows may be one padding column apart (call .contiguous() for a dense copy)."""
         assert tuple(x_local.shape) == (self.B, self.hn, self.W)
         if self._injected(x_local):
             return self.col_pass(self.transpose(self.row_pass(x_local)))
@@ -199,11 +215,16 @@ class PencilRfft2:
         L = capi.lib()
         L.trt_dft_plan_set_peer_column_split.restype = ctypes.c_int
         L.trt_dft_plan_set_peer_column_split.argtypes = [ctypes.c_void_p, ctypes.c_int, ctypes.POINTER(ctypes.c_int64), ctypes.c_int64,
-                                                         ctypes.c_int64, ctypes.c_int64, ctypes.POINTER(ctypes.c_void_p)]
+                                                         ctypes.c_int64, ctypes.c_int64, ctypes.POINTER(ctypes.c_void_p),
+                                                         ctypes.POINTER(ctypes.c_int64)]
         L.trt_dft_plan_set_peer_row_split.restype = ctypes.c_int
         L.trt_dft_plan_set_peer_row_split.argtypes = [ctypes.c_void_p, ctypes.c_int, ctypes.POINTER(ctypes.c_int64), ctypes.c_int64,
                                                       ctypes.c_int64, ctypes.POINTER(ctypes.c_void_p)]
-        cn_max = max(cn for _, cn in self.col_spans)
+        # slab row pitch: the band's column count rounded up to even (one padding column for the odd band), so that every
+        # row of every slab starts on 16 bytes; the column pass transforms the padding column along with the rest
+        self.pitches = [(cn + 1) // 2 * 2 for (_, cn) in self.col_spans]
+        self.pitch = self.pitches[self.rank]
+        cn_max = max(self.pitches)
         hn_max = max(hn for _, hn in self.row_spans)
         if self.world > 1:
             slab = PeerBuffer(self.B * self.H * cn_max * 2, device, self.group)       # forward target / inverse source
@@ -217,10 +238,11 @@ class PencilRfft2:
         rows = capi.Plan(capi.FORWARD, (self.W,), self.B * self.hn)
         starts = (ctypes.c_int64 * (self.world + 1))(*([c0 for (c0, _) in self.col_spans] + [self.Mo]))
         parr = (ctypes.c_void_p * self.world)(*slab_ptrs)
-        rc = L.trt_dft_plan_set_peer_column_split(rows.handle, self.world, starts, self.hn, self.H, self.h0, parr)
+        pitches = (ctypes.c_int64 * self.world)(*self.pitches)
+        rc = L.trt_dft_plan_set_peer_column_split(rows.handle, self.world, starts, self.hn, self.H, self.h0, parr, pitches)
         if rc != 0:
             raise capi.DftError(f"trt_dft_plan_set_peer_column_split failed with status {rc}")
-        cols = capi.C2CPlan(capi.FORWARD, self.H, self.B, self.cn)
+        cols = capi.C2CPlan(capi.FORWARD, self.H, self.B, self.pitch)        # (padding column included)
         # inverse: columns (C2C, +i sign, scaled by 1/H) store their rows into the owners' row bands; the C2R row pass
         # scales by 1/W, together the Irfft plugin's 1/(H*W)
         icols = capi.C2CPlan(capi.INVERSE, self.H, self.B, self.cn, scale=1.0 / self.H)
@@ -235,13 +257,13 @@ class PencilRfft2:
     def _forward_peer(self, x_local):
         P = self._peer
         slab, rows, cols = P["slab"], P["rows"], P["cols"]
-        z = slab.local[: self.B * self.H * self.cn * 2].view(self.B, self.H, self.cn, 2)
+        zp = slab.local[: self.B * self.H * self.pitch * 2].view(self.B, self.H, self.pitch, 2)
         slab.barrier()                    # nobody is still reading (or returning) last call's slabs
-        rows.exec_ptr(x_local.data_ptr(), z.data_ptr(), 0, torch.cuda.current_stream(x_local.device).cuda_stream)
+        rows.exec_ptr(x_local.data_ptr(), zp.data_ptr(), 0, torch.cuda.current_stream(x_local.device).cuda_stream)
         slab.barrier()                    # every rank's row blocks have landed everywhere
-        cols.exec(z, z)
+        cols.exec(zp, zp)
         self.exchange_used = "peer:" + P["kind"]
-        return z
+        return zp[:, :, : self.cn]        # (a view: row pitch `pitch` columns, the last one padding when cn is odd)
 
     def _inverse_peer(self, z_cols):
         P = self._peer

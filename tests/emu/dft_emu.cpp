@@ -20,6 +20,11 @@ struct HostCtx {
     int tid = 0, nthr = 1;
     void sync() {}
     bool bulk_load(void*, const void*, long long) { return false; }
+    float2* stage_out() const { return nullptr; }
+    void fence_async_shared() const {}
+    void bulk_store(void*, const void*, unsigned) const {}
+    void commit_bulk_stores() const {}
+    void wait_bulk_stores_read() const {}
 };
 }  // namespace
 

@@ -53,7 +53,8 @@ def test_peer_split_addresses_with_several_destinations_on_one_gpu():
     L = capi.lib()
     L.trt_dft_plan_set_peer_column_split.restype = ctypes.c_int
     L.trt_dft_plan_set_peer_column_split.argtypes = [ctypes.c_void_p, ctypes.c_int, ctypes.POINTER(ctypes.c_int64), ctypes.c_int64,
-                                                     ctypes.c_int64, ctypes.c_int64, ctypes.POINTER(ctypes.c_void_p)]
+                                                     ctypes.c_int64, ctypes.c_int64, ctypes.POINTER(ctypes.c_void_p),
+                                                     ctypes.POINTER(ctypes.c_int64)]
     L.trt_dft_plan_set_peer_row_split.restype = ctypes.c_int
     L.trt_dft_plan_set_peer_row_split.argtypes = [ctypes.c_void_p, ctypes.c_int, ctypes.POINTER(ctypes.c_int64), ctypes.c_int64,
                                                   ctypes.c_int64, ctypes.POINTER(ctypes.c_void_p)]
@@ -65,7 +66,7 @@ def test_peer_split_addresses_with_several_destinations_on_one_gpu():
         slabs = [torch.full((B, H, max(starts[j + 1] - starts[j], 1), 2), float("nan"), device="cuda") for j in range(4)]
         rows = capi.Plan(capi.FORWARD, (W,), B * hn)
         rc = L.trt_dft_plan_set_peer_column_split(rows.handle, 4, (ctypes.c_int64 * 5)(*starts), hn, H, h0,
-                                                  (ctypes.c_void_p * 4)(*[s.data_ptr() for s in slabs]))
+                                                  (ctypes.c_void_p * 4)(*[s.data_ptr() for s in slabs]), None)
         assert rc == 0
         dummy = torch.empty(B * hn * Mo * 2, device="cuda")
         rows.exec_ptr(x.data_ptr(), dummy.data_ptr(), 0, torch.cuda.current_stream().cuda_stream)
@@ -78,6 +79,25 @@ def test_peer_split_addresses_with_several_destinations_on_one_gpu():
             got = slabs[j][:, h0:h0 + hn]
             assert O.rel_l2(got.cpu().numpy(), plain[:, :, starts[j]:starts[j + 1]].cpu().numpy()) <= 1e-6
             assert torch.isnan(slabs[j][:, :h0]).all() and torch.isnan(slabs[j][:, h0 + hn:]).all()   # nothing else touched
+        # the same with even column starts and even slab pitches: runs leave as bulk copies out of staged rows (persistent
+        # row kernel; shapes too small for it keep the 8-byte stores) -- the padding column may be written, nothing else
+        bstarts = [0, (Mo // 3) // 2 * 2, (Mo // 3) // 2 * 2, (Mo - 7) // 2 * 2, Mo]
+        pitches = [max((bstarts[j + 1] - bstarts[j] + 1) // 2 * 2, 2) for j in range(4)]
+        bslabs = [torch.full((B, H, pitches[j], 2), float("nan"), device="cuda") for j in range(4)]
+        rows2 = capi.Plan(capi.FORWARD, (W,), B * hn)
+        rc = L.trt_dft_plan_set_peer_column_split(rows2.handle, 4, (ctypes.c_int64 * 5)(*bstarts), hn, H, h0,
+                                                  (ctypes.c_void_p * 4)(*[s.data_ptr() for s in bslabs]), (ctypes.c_int64 * 4)(*pitches))
+        assert rc == 0
+        rows2.exec_ptr(x.data_ptr(), dummy.data_ptr(), 0, torch.cuda.current_stream().cuda_stream)
+        rows2.exec_ptr(x.data_ptr(), dummy.data_ptr(), 0, torch.cuda.current_stream().cuda_stream)      # staging rows are reused
+        torch.cuda.synchronize()
+        for j in range(4):
+            cn = bstarts[j + 1] - bstarts[j]
+            if cn == 0:
+                continue
+            got = bslabs[j][:, h0:h0 + hn, :cn]
+            assert O.rel_l2(got.cpu().numpy(), plain[:, :, bstarts[j]:bstarts[j + 1]].cpu().numpy()) <= 1e-6
+            assert torch.isnan(bslabs[j][:, :h0]).all() and torch.isnan(bslabs[j][:, h0 + hn:]).all()
         # mirror: a column band [B, H, cn] -> rows scattered into 4 row bands at column offset c0
         cn, c0 = 37, 5
         z = torch.randn(B, H, cn, 2, device="cuda")

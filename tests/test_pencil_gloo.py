@@ -20,7 +20,7 @@ def _worker(rank, world, port, out_dir):
     dist.init_process_group("gloo", rank=rank, world_size=world)
     from trt_dft_plugins.pencil import PencilRfft2
     torch.manual_seed(1)
-    B, H, W = 3, 10, 12                                # Mo = 7 columns: split 4 + 3; rows 5 + 5
+    B, H, W = 3, 10, 12                                # Mo = 7 columns: split 2 + 5 (even band starts); rows 5 + 5
     full = torch.randn(B, H, W)
     row_fft = lambda x: torch.view_as_real(torch.fft.rfft(x, dim=-1))
     col_fft = lambda z: torch.view_as_real(torch.fft.fft(torch.view_as_complex(z.contiguous()), dim=1))
@@ -42,6 +42,6 @@ def test_pencil_transpose_two_ranks(tmp_path):
     port = 31500 + (os.getpid() % 2000)
     mp.spawn(_worker, args=(2, port, str(tmp_path)), nprocs=2, join=True)
     r0, r1 = torch.load(tmp_path / "r0.pt"), torch.load(tmp_path / "r1.pt")
-    assert r0["cn"] + r1["cn"] == 7 and r0["shape"] == (3, 10, 4, 2) and r1["shape"] == (3, 10, 3, 2)
+    assert r0["cn"] + r1["cn"] == 7 and r0["shape"] == (3, 10, 2, 2) and r1["shape"] == (3, 10, 5, 2)
     assert r0["err"] < 1e-6 and r1["err"] < 1e-6
     assert r0["err_inv"] < 1e-6 and r1["err_inv"] < 1e-6
