@@ -118,6 +118,18 @@ int trt_dft_plan_set_peer_column_split(trt_dft_plan_t plan, int nparts, const in
                                        int64_t image_rows, int64_t row_offset, void* const* peer_slabs, const int64_t* slab_pitches);
 
 /*
+ * The pencil irfft2 with the exchange fused into the row pass's LOADS: a rank-1 INVERSE plan over this rank's row band
+ * takes row R of image b not from `in` (then unused) but from the ranks' column slabs -- columns
+ * [col_starts[j], col_starts[j+1]) of that row from peer_slabs[j][b][row_offset + R][.] (pitch slab_pitches[j]; NULL:
+ * dense) -- with the persistent row kernel's producer warps copying straight out of the owners' memory (plain loads over
+ * NVLink into shared memory, no multicast).  Same arguments as trt_dft_plan_set_peer_column_split; nparts = 0 switches
+ * it off.  TRT_DFT_ERR_UNSUPPORTED when the plan does not run the persistent row kernel (small batches): use
+ * trt_dft_plan_set_peer_row_split on the column pass instead.
+ */
+int trt_dft_plan_set_peer_column_gather(trt_dft_plan_t plan, int nparts, const int64_t* col_starts, int64_t rows_per_image,
+                                        int64_t image_rows, int64_t row_offset, void* const* peer_slabs, const int64_t* slab_pitches);
+
+/*
  * The mirror image for the pencil irfft2: a trt_dft_plan_create_c2c plan over data[outer][n][inner] stores output row
  * q of every image into the row band of the rank that owns it,
  *     peer_bands[j][image][row_starts[j+1] - row_starts[j]][dest_pitch]   for row_starts[j] <= q < row_starts[j+1],

@@ -569,6 +569,40 @@ int trt_dft_plan_set_peer_column_split(trt_dft_plan_t plan, int nparts, const in
     return TRT_DFT_OK;
 }
 
+int trt_dft_plan_set_peer_column_gather(trt_dft_plan_t plan, int nparts, const int64_t* col_starts, int64_t rows_per_image,
+                                        int64_t image_rows, int64_t row_offset, void* const* peer_slabs, const int64_t* slab_pitches)
+{
+    if (!plan || nparts < 0 || nparts > 8) return TRT_DFT_ERR_INVALID_ARG;
+    if (plan->launches.size() != 1 || plan->launches[0].kp.mode != dft::MODE_I1D) return TRT_DFT_ERR_UNSUPPORTED;
+    ResolvedLaunch& rl = plan->launches[0];
+    KParams& k = rl.kp;
+    if (nparts == 0) {
+        k.pack_n = 0;
+        k.pack_peer_on = 0;
+        return TRT_DFT_OK;
+    }
+    if (!rl.gpipe) return TRT_DFT_ERR_UNSUPPORTED;              // only the persistent row kernel's producers can gather
+    const int Mo = k.M + 1;
+    if (!col_starts || !peer_slabs || rows_per_image < 1 || image_rows < 1 || row_offset < 0 || row_offset + rows_per_image > image_rows ||
+        image_rows > (1LL << 30) || col_starts[0] != 0 || col_starts[nparts] != Mo || k.nunits % rows_per_image != 0 || k.nunits > (1LL << 30))
+        return TRT_DFT_ERR_INVALID_ARG;
+    for (int j = 0; j < nparts; ++j) {
+        const int64_t cn = col_starts[j + 1] - col_starts[j];
+        const int64_t pitch = slab_pitches ? slab_pitches[j] : cn;
+        if (cn < 0 || pitch < cn || pitch > (1LL << 30) || !peer_slabs[j] || ((uintptr_t)peer_slabs[j] & 7)) return TRT_DFT_ERR_INVALID_ARG;
+        k.pack_pitch[j] = (int)pitch;
+    }
+    k.pack_n = nparts;
+    for (int j = 0; j <= nparts; ++j) k.pack_c0[j] = (int)col_starts[j];
+    k.pack_hn = (int)rows_per_image;
+    k.pack_H = (int)image_rows;
+    k.pack_h0 = (int)row_offset;
+    k.pack_peer_on = 1;
+    k.pack_bulk = 0;
+    for (int j = 0; j < 8; ++j) k.pack_peer[j] = j < nparts ? (float2*)peer_slabs[j] : nullptr;
+    return TRT_DFT_OK;
+}
+
 int trt_dft_plan_set_peer_row_split(trt_dft_plan_t plan, int nparts, const int64_t* row_starts, int64_t dest_pitch,
                                     int64_t dest_col_offset, void* const* peer_bands)
 {

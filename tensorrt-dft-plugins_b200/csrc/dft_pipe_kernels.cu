@@ -160,6 +160,23 @@ __device__ __forceinline__ unsigned produce_tile(const KParams& p, long long til
         const long long first = tile * p.G * (two_d ? p.H : 1);
         const long long units_left = (p.nunits - tile * p.G) < p.G ? (p.nunits - tile * p.G) : p.G;
         const int nrows = (int)(units_left * (two_d ? p.H : 1));
+        if (MODE == dft::MODE_I1D && p.pack_peer_on) {
+            // Pencil irfft2, exchange fused into the LOAD: row R of this rank's band is spread over the ranks' column slabs
+            // (KParams::pack_*: slab j holds columns [c0_j, c0_{j+1}) of every row at pitch pack_pitch[j]); the producers
+            // fetch each run straight from its owner's memory with element copies (plain loads over NVLink, no multicast).
+            for (int r = 0; r < nrows; ++r) {
+                const int R = (int)first + r, b = R / p.pack_hn, rl = R - b * p.pack_hn;
+                float2* drow = buf + r * P;
+#pragma unroll
+                for (int t = 0; t < 8; ++t) {
+                    if (t >= p.pack_n) break;
+                    const int c0 = p.pack_c0[t], c1 = p.pack_c0[t + 1];
+                    const float2* srow = p.pack_peer[t] + ((long long)b * p.pack_H + p.pack_h0 + rl) * p.pack_pitch[t] - c0;
+                    for (int k = c0 + pt; k < c1; k += NP) cp_async8(drow + dft::phys(k, p.pad), srow + k);
+                }
+            }
+            return 0;
+        }
         const float* src = in + first * per_row * 2;
         const long long nbytes = (long long)nrows * per_row * 8;
         if (!p.pad && P == per_row && (((uintptr_t)src) & 15) == 0 && (nbytes & 15) == 0 && nbytes < (1 << 20)) {

@@ -15,7 +15,7 @@ SYMBOLS = [
     "trt_dft_exec", "trt_dft_plan_destroy", "trt_dft_exec_host", "trt_dft_plan_describe",
     "trt_dft_plan_input_floats", "trt_dft_plan_output_floats", "trt_dft_plan_create_c2c", "trt_dft_plan_set_column_split",
     "trt_dft_query_workspace_bytes", "trt_dft_exec_static_ws", "trt_dft_plan_create_truncated",
-    "trt_dft_plan_set_peer_column_split", "trt_dft_plan_set_peer_row_split",
+    "trt_dft_plan_set_peer_column_split", "trt_dft_plan_set_peer_row_split", "trt_dft_plan_set_peer_column_gather",
 ]
 
 _bound = None

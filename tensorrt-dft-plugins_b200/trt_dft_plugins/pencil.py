@@ -110,6 +110,7 @@ class PencilRfft2:
         self.exchange = exchange
         self._peer = None
         self.exchange_used = None
+        self.inverse_exchange = "auto"      # "stores": keep the inverse on the column kernel's peer stores (A/B)
 
     # ---- default GPU transforms ---------------------------------------------------------------
     def _gpu_plans(self):
@@ -252,7 +253,17 @@ class PencilRfft2:
         if rc != 0:
             raise capi.DftError(f"trt_dft_plan_set_peer_row_split failed with status {rc}")
         irows = capi.Plan(capi.INVERSE, (self.W,), self.B * self.hn)
-        self._peer = {"slab": slab, "band": band, "rows": rows, "cols": cols, "icols": icols, "irows": irows, "kind": kind}
+        # inverse, preferred: the column pass runs in place on the local slab and the ROW pass fetches each row's column
+        # bands straight out of the owners' slabs while it loads its tiles (trt_dft_plan_set_peer_column_gather)
+        L.trt_dft_plan_set_peer_column_gather.restype = ctypes.c_int
+        L.trt_dft_plan_set_peer_column_gather.argtypes = L.trt_dft_plan_set_peer_column_split.argtypes
+        icols_local = capi.C2CPlan(capi.INVERSE, self.H, self.B, self.pitch, scale=1.0 / self.H)
+        irows_gather = capi.Plan(capi.INVERSE, (self.W,), self.B * self.hn)
+        rc = L.trt_dft_plan_set_peer_column_gather(irows_gather.handle, self.world, starts, self.hn, self.H, self.h0, parr, pitches)
+        if rc != 0:                        # (small batches run a kernel that cannot gather: keep the store-based inverse)
+            irows_gather = None
+        self._peer = {"slab": slab, "band": band, "rows": rows, "cols": cols, "icols": icols, "irows": irows, "kind": kind,
+                      "icols_local": icols_local, "irows_gather": irows_gather}
 
     def _forward_peer(self, x_local):
         P = self._peer
@@ -267,6 +278,20 @@ class PencilRfft2:
 
     def _inverse_peer(self, z_cols):
         P = self._peer
+        if P["irows_gather"] is not None and self.inverse_exchange != "stores":
+            # exchange fused into the row pass's loads.  The spectrum band has to sit in the peer-visible slab (forward()'s
+            # result already does) and is transformed there in place.
+            slab = P["slab"]
+            zp = slab.local[: self.B * self.H * self.pitch * 2].view(self.B, self.H, self.pitch, 2)
+            slab.barrier()                # nobody is still fetching last call's columns out of this slab
+            if z_cols.data_ptr() != zp.data_ptr() or tuple(z_cols.stride()) != tuple(zp[:, :, : self.cn].stride()):
+                zp[:, :, : self.cn].copy_(z_cols)
+            P["icols_local"].exec(zp, zp)
+            slab.barrier()                # every rank's columns are transformed
+            x = torch.empty(self.B, self.hn, self.W, dtype=torch.float32, device=z_cols.device)
+            P["irows_gather"].exec_ptr(zp.data_ptr(), x.data_ptr(), 0, torch.cuda.current_stream(z_cols.device).cuda_stream)
+            self.exchange_used = "peer-gather:" + P["kind"]
+            return x
         band, icols, irows = P["band"], P["icols"], P["irows"]
         y = band.local[: self.B * self.hn * self.Mo * 2].view(self.B, self.hn, self.Mo, 2)
         band.barrier()                    # nobody is still reading last call's row bands

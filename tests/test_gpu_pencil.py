@@ -40,9 +40,14 @@ def test_peer_store_kernels_forward_and_inverse_on_one_gpu(B, H, W):
     torch.cuda.synchronize()
     ref = capi.rfftn(x, 2)
     assert O.rel_l2(z.cpu().numpy(), ref.cpu().numpy()) <= 1e-6
-    xb = p.inverse(z)
+    zc = z.clone()
+    xb = p.inverse(z)                          # row pass gathering from the slab (persistent kernel) or the store form
     torch.cuda.synchronize()
     assert O.rel_l2(xb.cpu().numpy(), x.cpu().numpy()) <= 1e-6
+    p.inverse_exchange = "stores"              # column pass storing into the row band
+    xs = p.inverse(zc)
+    torch.cuda.synchronize()
+    assert O.rel_l2(xs.cpu().numpy(), x.cpu().numpy()) <= 1e-6
 
 
 def test_peer_split_addresses_with_several_destinations_on_one_gpu():
@@ -145,10 +150,17 @@ def _two_gpu_worker(rank, world, port, out_dir):
             torch.cuda.synchronize()
             want = ref[:, :, p.c0:p.c0 + p.cn]
             e_f = ((y - want).double().norm() / want.double().norm()).item()
-            xb = p.inverse(y.clone())
+            yc = y.clone()                          # (the gathering inverse transforms the slab -- i.e. y -- in place)
+            xb = p.inverse(yc.clone())
             torch.cuda.synchronize()
             e_i = ((xb - x_loc).double().norm() / x_loc.double().norm()).item()
-            res[(B, H, W, mode)] = (e_f, e_i, p.exchange_used)
+            used = p.exchange_used
+            if mode == "peer":                      # the inverse's other peer form: column kernel storing into row bands
+                p.inverse_exchange = "stores"
+                xs = p.inverse(yc)
+                torch.cuda.synchronize()
+                e_i = max(e_i, ((xs - x_loc).double().norm() / x_loc.double().norm()).item())
+            res[(B, H, W, mode)] = (e_f, e_i, used)
     torch.save(res, os.path.join(out_dir, f"r{rank}.pt"))
     dist.barrier()
     dist.destroy_process_group()
