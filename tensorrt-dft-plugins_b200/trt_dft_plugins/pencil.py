@@ -20,8 +20,11 @@ Three ways to run the exchange, same results:
             kernel's epilogue (trt_dft_plan_set_peer_row_split) stores each value straight into the owning rank's
             memory with ordinary global stores over NVLink -- no pack, no send buffer, no NCCL in the data path, and
             the transfer overlaps the transform tile by tile.  Only two GPU-side barriers per call remain.
-            (Plain stores only: TMA multicast loads here read only this GPU's memory, since on B200 a TMA multicast
-            load from another GPU's memory hung the GPU.  Nothing on this path loads from a peer at all.)
+            The inverse runs the column pass in place on the slab and lets the row kernel's producers fetch every
+            row's column bands out of the owners' slabs (trt_dft_plan_set_peer_column_gather), with the column kernel
+            storing into the owners' row bands (trt_dft_plan_set_peer_row_split) as the alternative.
+            (Stores and plain loads only: TMA multicast loads here read only this GPU's memory, since on B200 a TMA
+            multicast load from another GPU's memory hung the GPU.)
   * "nccl"  the row pass writes blocks split by destination (trt_dft_plan_set_column_split) and one
             all_to_all_single per image lands them in place; kept as fallback and as the parity check of "peer".
   * injected transforms (`row_fft`, `col_fft`): plain torch exchange, so that the logic can be tested on CPU with gloo.
