@@ -102,10 +102,15 @@ __device__ __forceinline__ void f2d_bulk_store_and_wait(void* gdst, const void* 
 }
 
 // ---- forward ---------------------------------------------------------------------------------
-template <class C>
-__global__ void __launch_bounds__(C::NT, C::MINB)
-    fused_rfft2_kernel(const float* __restrict__ in, float* __restrict__ out, long long nimg,
-                       const float2* __restrict__ tables, float /*scale: forward is unnormalised*/)
+// kept-row index of spectrum row q for a truncated-mode plan (rows [0, kh) u [H - kh, H)), or -1
+__device__ __forceinline__ int f2d_kept_row(int q, int H, int kh) { return q < kh ? q : (q >= H - kh ? q - (H - 2 * kh) : -1); }
+
+// TR: truncated modes (trt_dft_plan_create_truncated) -- only rows [0, kh) u [H - kh, H), columns [0, kw) of the spectrum
+// are stored, as a dense [2*kh][kw] block per image, and column pairs none of whose two columns is kept are not
+// transformed in the last step at all.
+template <class C, bool TR>
+__device__ __forceinline__ void fused_rfft2_body(const float* __restrict__ in, float* __restrict__ out, long long nimg,
+                                                 const float2* __restrict__ tables, const int kh, const int kw)
 {
     constexpr int H = C::H, W = C::W, M = C::M, RA = C::RA, RB = C::RB, CA = C::CA, CB = C::CB, NT = C::NT;
     constexpr int KH = C::KH, MO = M + 1;
@@ -199,10 +204,11 @@ __global__ void __launch_bounds__(C::NT, C::MINB)
         }
         __syncthreads();
         // columns, step CB fused with the real-FFT split and the global stores
-        float2* oimg = reinterpret_cast<float2*>(out) + img * (long long)(H * MO);
+        float2* oimg = reinterpret_cast<float2*>(out) + img * (long long)(TR ? 2 * kh * kw : H * MO);
 #pragma unroll 1
         for (int t = tid; t < CA * KH; t += NT) {
             const int q1 = t / KH, k = t - q1 * KH;
+            if (TR && k >= kw && M - k >= kw) continue;          // neither column k nor column M - k is kept
             const int kk = (k == 0) ? 0 : M - k;
             const int swA = C::SWZ ? ((k % RA) & (RB - 1)) : 0, swB = C::SWZ ? ((kk % RA) & (RB - 1)) : 0;
             const int colA = (k % RA) * RB + ((k / RA) ^ swA);
@@ -236,21 +242,46 @@ __global__ void __launch_bounds__(C::NT, C::MINB)
                 const float ex = 0.5f * (z1.x + z2.x), ey = 0.5f * (z1.y - z2.y);
                 const float dx = z1.x - z2.x, dy = z1.y + z2.y;
                 const float tx = wh.x * dx - wh.y * dy, ty = wh.x * dy + wh.y * dx;
-                oa[k2 * CA * MO] = float2{ex + ty, ey - tx};
-                float2* pbk = ob - k2 * CA * MO;
-                if (k2 == 0 && q1 == 0) pbk -= H * MO;       // (H - 0) mod H = 0
-                *pbk = float2{ex - ty, -ey - tx};
+                if constexpr (!TR) {
+                    oa[k2 * CA * MO] = float2{ex + ty, ey - tx};
+                    float2* pbk = ob - k2 * CA * MO;
+                    if (k2 == 0 && q1 == 0) pbk -= H * MO;       // (H - 0) mod H = 0
+                    *pbk = float2{ex - ty, -ey - tx};
+                } else {
+                    const int qa = q1 + CA * k2;
+                    const int qb = (k2 == 0 && q1 == 0) ? 0 : H - q1 - CA * k2;
+                    const int ia = f2d_kept_row(qa, H, kh), ib = f2d_kept_row(qb, H, kh);
+                    if (k < kw && ia >= 0) oimg[ia * kw + k] = float2{ex + ty, ey - tx};
+                    if (M - k < kw && ib >= 0) oimg[ib * kw + (M - k)] = float2{ex - ty, -ey - tx};
+                }
             });
         }
         __syncthreads();
     }
 }
 
-// ---- inverse ---------------------------------------------------------------------------------
 template <class C>
 __global__ void __launch_bounds__(C::NT, C::MINB)
-    fused_irfft2_kernel(const float* __restrict__ in, float* __restrict__ out, long long nimg,
-                        const float2* __restrict__ tables, float scale /* 1/prod(signal dims) */)
+    fused_rfft2_kernel(const float* __restrict__ in, float* __restrict__ out, long long nimg,
+                       const float2* __restrict__ tables, float /*scale: forward is unnormalised*/)
+{
+    fused_rfft2_body<C, false>(in, out, nimg, tables, 0, 0);
+}
+template <class C>
+__global__ void __launch_bounds__(C::NT, C::MINB)
+    fused_rfft2_trunc_kernel(const float* __restrict__ in, float* __restrict__ out, long long nimg, const float2* __restrict__ tables,
+                             int kh, int kw)
+{
+    fused_rfft2_body<C, true>(in, out, nimg, tables, kh, kw);
+}
+
+// ---- inverse ---------------------------------------------------------------------------------
+// TR: the input is the dense kept block [2*kh][kw]; it is expanded into the one-sided tile while it is loaded (zeros
+// everywhere else), the rest is the ordinary kernel.
+template <class C, bool TR>
+__device__ __forceinline__ void fused_irfft2_body(const float* __restrict__ in, float* __restrict__ out, long long nimg,
+                                                  const float2* __restrict__ tables, float scale /* 1/prod(signal dims) */,
+                                                  const int kh, const int kw)
 {
     constexpr int H = C::H, W = C::W, M = C::M, RA = C::RA, RB = C::RB, CA = C::CA, CB = C::CB, NT = C::NT;
     constexpr int KH = C::KH, PI = C::PI;
@@ -266,12 +297,24 @@ __global__ void __launch_bounds__(C::NT, C::MINB)
     if (tid == 0) f2d_mbar_init(bar);
     __syncthreads();
     unsigned phase = 0;
-    const bool bulk_in = C::BULK_CPLX && (((uintptr_t)in & 15) == 0);
+    const bool bulk_in = !TR && C::BULK_CPLX && (((uintptr_t)in & 15) == 0);
     const bool bulk_out = C::BULK_REAL && (((uintptr_t)out & 15) == 0);
 
     for (long long img = blockIdx.x; img < nimg; img += gridDim.x) {
-        const float2* src = reinterpret_cast<const float2*>(in) + img * (long long)(H * PI);
-        if (bulk_in) {
+        const float2* src = reinterpret_cast<const float2*>(in) + img * (long long)(TR ? 2 * kh * kw : H * PI);
+        if constexpr (TR) {
+            // zero tile (128-bit stores), then the kept block scattered into it: cost follows the kept size
+            static_assert((H * PI) % 2 == 0, "tile is cleared two elements at a time");
+            const float4 z4 = float4{0.f, 0.f, 0.f, 0.f};
+            for (int i = tid; i < H * PI / 2; i += NT) reinterpret_cast<float4*>(buf)[i] = z4;
+            __syncthreads();
+            const int total = 2 * kh * kw;
+            for (int e = tid; e < total; e += NT) {
+                const int qi = e / kw, k = e - qi * kw;
+                buf[(qi < kh ? qi : qi + (H - 2 * kh)) * PI + k] = __ldg(src + e);
+            }
+            __syncthreads();
+        } else if (bulk_in) {
             if (tid == 0) f2d_bulk_load(buf, src, H * PI * 8, bar);
             f2d_mbar_wait(bar, phase);
             phase ^= 1u;
@@ -411,6 +454,21 @@ __global__ void __launch_bounds__(C::NT, C::MINB)
             __syncthreads();
         }
     }
+}
+
+template <class C>
+__global__ void __launch_bounds__(C::NT, C::MINB)
+    fused_irfft2_kernel(const float* __restrict__ in, float* __restrict__ out, long long nimg,
+                        const float2* __restrict__ tables, float scale)
+{
+    fused_irfft2_body<C, false>(in, out, nimg, tables, scale, 0, 0);
+}
+template <class C>
+__global__ void __launch_bounds__(C::NT, C::MINB)
+    fused_irfft2_trunc_kernel(const float* __restrict__ in, float* __restrict__ out, long long nimg, const float2* __restrict__ tables,
+                              int kh, int kw, float scale)
+{
+    fused_irfft2_body<C, true>(in, out, nimg, tables, scale, kh, kw);
 }
 
 #endif  // __CUDACC__

@@ -247,15 +247,26 @@ int trt_dft_plan_create_truncated(trt_dft_plan_t* plan_out, int direction, const
     if (e && e->trunc_fwd && e->trunc_inv && !getenv("TRT_DFT_TRUNC_UNFUSED")) {
         pl->t_fwd = e->trunc_fwd;
         pl->t_inv = e->trunc_inv;
-        pl->t_threads = e->NT;
+        pl->t_threads = (direction == TRT_DFT_INVERSE && e->NT_inv) ? e->NT_inv : e->NT;
         pl->t_smem = direction == TRT_DFT_INVERSE ? e->smem_i : e->smem_f;
         const void* fn = direction == TRT_DFT_INVERSE ? (const void*)e->trunc_inv : (const void*)e->trunc_fwd;
-        if (cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, pl->t_smem) != cudaSuccess) {
+        int occ = 0;
+        if (cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, pl->t_smem) != cudaSuccess ||
+            cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, fn, pl->t_threads, pl->t_smem) != cudaSuccess || occ < 1) {
             cudaGetLastError();
             delete pl;
             return TRT_DFT_ERR_CUDA;
         }
-        pl->t_grid = (int)std::min<long long>(batch, num_sms);
+        // the pass-per-radix fused kernels (128 x 128, 64 x 64) read their twiddles from a small device table
+        std::vector<float2> tab = spec_tables(*e, direction == TRT_DFT_INVERSE, (double)pl->t_scale);
+        if (cudaMalloc(&pl->pool, tab.size() * sizeof(float2)) != cudaSuccess ||
+            cudaMemcpy(pl->pool, tab.data(), tab.size() * sizeof(float2), cudaMemcpyHostToDevice) != cudaSuccess) {
+            cudaGetLastError();
+            if (pl->pool) cudaFree(pl->pool);
+            delete pl;
+            return TRT_DFT_ERR_ALLOC;
+        }
+        pl->t_grid = (int)std::min<long long>(batch, (long long)num_sms * occ);
         snprintf(desc, sizeof desc, "truncated_%s<%d,%d> keep=%dx%d images=%lld [fused, kept modes only] grid=%dx%d", direction ? "irfft2" : "rfft2",
                  (int)H, (int)W, 2 * pl->kh, pl->kw, (long long)batch, pl->t_grid, pl->t_threads);
     } else if (batch > 0) {
@@ -692,10 +703,11 @@ static int exec_truncated(trt_dft_plan_t plan, const void* in, void* out, void* 
     const bool aligned = ((((uintptr_t)in) | ((uintptr_t)out)) & 15) == 0;
     if (plan->t_fwd && aligned) {
         if (!inv)
-            plan->t_fwd<<<plan->t_grid, plan->t_threads, plan->t_smem, st>>>((const float*)in, (float*)out, plan->pd.batch, plan->kh, plan->kw);
+            plan->t_fwd<<<plan->t_grid, plan->t_threads, plan->t_smem, st>>>((const float*)in, (float*)out, plan->pd.batch,
+                                                                            (const float2*)plan->pool, plan->kh, plan->kw);
         else
-            plan->t_inv<<<plan->t_grid, plan->t_threads, plan->t_smem, st>>>((const float*)in, (float*)out, plan->pd.batch, plan->kh, plan->kw,
-                                                                            plan->t_scale);
+            plan->t_inv<<<plan->t_grid, plan->t_threads, plan->t_smem, st>>>((const float*)in, (float*)out, plan->pd.batch,
+                                                                            (const float2*)plan->pool, plan->kh, plan->kw, plan->t_scale);
         if (cudaPeekAtLastError() != cudaSuccess) {
             cudaGetLastError();
             return TRT_DFT_ERR_CUDA;

@@ -6,9 +6,9 @@
 namespace dft {
 
 typedef void (*spec_fn)(const float*, float*, long long, const float2*, float);
-// truncated-mode variants: (in, out, images, keep_h, keep_w[, scale])
-typedef void (*trunc_fwd_fn)(const float*, float*, long long, int, int);
-typedef void (*trunc_inv_fn)(const float*, float*, long long, int, int, float);
+// truncated-mode variants: (in, out, images, tables, keep_h, keep_w[, scale])
+typedef void (*trunc_fwd_fn)(const float*, float*, long long, const float2*, int, int);
+typedef void (*trunc_inv_fn)(const float*, float*, long long, const float2*, int, int, float);
 
 struct SpecEntry {
     int H, W, RA, RB, CA, CB, NT;

@@ -11,7 +11,7 @@ pytestmark = pytest.mark.gpu
 CASES = [
     # (batch, H, W, keep_h, keep_w)
     (7, 90, 180, 12, 20), (300, 90, 180, 45, 91), (149, 90, 180, 1, 1), (5, 90, 180, 30, 33), (64, 90, 180, 20, 64),
-    (6, 128, 128, 16, 16), (3, 64, 64, 8, 12), (2, 720, 1440, 32, 48), (4, 34, 74, 5, 7), (3, 60, 120, 30, 61),
+    (6, 128, 128, 16, 16), (3, 64, 64, 8, 12), (700, 128, 128, 12, 12), (5, 128, 128, 64, 65), (9, 128, 128, 1, 40), (4, 64, 64, 32, 33), (2, 720, 1440, 32, 48), (4, 34, 74, 5, 7), (3, 60, 120, 30, 61),
 ]
 
 
@@ -60,8 +60,10 @@ def test_truncated_plan_describes_its_route_and_rejects_bad_sizes():
     p = capi.TruncatedPlan(capi.FORWARD, (90, 180), 8, 12, 20)
     assert "kept modes only" in p.describe()[1] and p.workspace_bytes == 0 and p.num_launches == 1
     assert p.input_floats == 8 * 90 * 180 and p.output_floats == 8 * 24 * 20 * 2
-    q = capi.TruncatedPlan(capi.INVERSE, (128, 128), 8, 16, 16)
-    assert "zero-pad" in q.describe()[1] and q.workspace_bytes >= 8 * 128 * 65 * 8
+    r = capi.TruncatedPlan(capi.INVERSE, (128, 128), 8, 16, 16)            # the FNO shape has fused kernels too
+    assert "kept modes only" in r.describe()[1] and r.workspace_bytes == 0
+    q = capi.TruncatedPlan(capi.INVERSE, (60, 120), 8, 16, 16)
+    assert "zero-pad" in q.describe()[1] and q.workspace_bytes >= 8 * 60 * 61 * 8
     for kh, kw in ((0, 4), (46, 4), (4, 0), (4, 92)):
         with pytest.raises(capi.DftError):
             capi.TruncatedPlan(capi.FORWARD, (90, 180), 8, kh, kw)
@@ -84,7 +86,7 @@ def test_full_keep_equals_the_ordinary_transform():
     assert torch.equal(back, capi.irfftn(full, 2))
 
 
-@pytest.mark.parametrize("H,W,kh,kw", [(90, 180, 10, 16), (64, 64, 8, 12)])
+@pytest.mark.parametrize("H,W,kh,kw", [(90, 180, 10, 16), (64, 64, 8, 12), (60, 120, 7, 9)])
 def test_truncated_plans_through_the_host_buffer_call(H, W, kh, kw):
     """trt_dft_exec_host with a truncated plan (fused route and crop / pad route): host buffers in and out."""
     from trt_dft_plugins import capi
