@@ -130,8 +130,8 @@ struct trt_dft_plan_s {
     // truncated-mode plan (trt_dft_plan_create_truncated): kept block [2*kh][kw] on the complex side
     bool trunc = false;
     int kh = 0, kw = 0, tH = 0, tW = 0;
-    dft::trunc_fwd_fn t_fwd = nullptr;    // fused kernels that move only the kept modes ...
-    dft::trunc_inv_fn t_inv = nullptr;
+    dft::trunc_fn t_fwd = nullptr;    // fused kernels that move only the kept modes ...
+    dft::trunc_fn t_inv = nullptr;
     int t_threads = 0, t_smem = 0, t_grid = 0;
     float t_scale = 1.f;
     trt_dft_plan_t t_full = nullptr;      // ... or the full transform through the workspace plus a crop / pad kernel
@@ -704,10 +704,10 @@ static int exec_truncated(trt_dft_plan_t plan, const void* in, void* out, void* 
     if (plan->t_fwd && aligned) {
         if (!inv)
             plan->t_fwd<<<plan->t_grid, plan->t_threads, plan->t_smem, st>>>((const float*)in, (float*)out, plan->pd.batch,
-                                                                            (const float2*)plan->pool, plan->kh, plan->kw);
+                                                                            (const float2*)plan->pool, 1.0f, plan->kh, plan->kw);
         else
             plan->t_inv<<<plan->t_grid, plan->t_threads, plan->t_smem, st>>>((const float*)in, (float*)out, plan->pd.batch,
-                                                                            (const float2*)plan->pool, plan->kh, plan->kw, plan->t_scale);
+                                                                            (const float2*)plan->pool, plan->t_scale, plan->kh, plan->kw);
         if (cudaPeekAtLastError() != cudaSuccess) {
             cudaGetLastError();
             return TRT_DFT_ERR_CUDA;

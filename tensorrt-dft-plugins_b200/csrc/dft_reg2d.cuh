@@ -462,7 +462,7 @@ __global__ void __launch_bounds__(C::THREADS, 1)
 template <class C>
 __global__ void __launch_bounds__(C::THREADS, 1)
     reg_rfft2_trunc_kernel(const float* __restrict__ in, float* __restrict__ out, long long nimg, const float2* __restrict__ /*tables*/,
-                           int kh, int kw)
+                           float /*scale*/, int kh, int kw)
 {
     reg_rfft2_body<C, true>(in, out, nimg, kh, kw);
 }
@@ -673,7 +673,7 @@ __global__ void __launch_bounds__(C::THREADS, 1)
 template <class C>
 __global__ void __launch_bounds__(C::THREADS, 1)
     reg_irfft2_trunc_kernel(const float* __restrict__ in, float* __restrict__ out, long long nimg, const float2* __restrict__ /*tables*/,
-                            int kh, int kw, float scale)
+                            float scale, int kh, int kw)
 {
     reg_irfft2_body<C, true>(in, out, nimg, scale, kh, kw);
 }

@@ -14,8 +14,8 @@ SpecEntry make_spec()
 {
     SpecEntry e{C::H, C::W, C::RA, C::RB, C::CA, C::CB, C::NT, C::SMEM_F, C::SMEM_I,
                 fused_rfft2_kernel<C>, fused_irfft2_kernel<C>, false};
-    e.trunc_fwd = fused_rfft2_trunc_kernel<C>;
-    e.trunc_inv = fused_irfft2_trunc_kernel<C>;
+    e.trunc_fwd = fused_rfft2_kernel<C, int, int>;
+    e.trunc_inv = fused_irfft2_kernel<C, int, int>;
     return e;
 }
 

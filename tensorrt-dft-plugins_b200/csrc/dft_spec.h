@@ -6,9 +6,8 @@
 namespace dft {
 
 typedef void (*spec_fn)(const float*, float*, long long, const float2*, float);
-// truncated-mode variants: (in, out, images, tables, keep_h, keep_w[, scale])
-typedef void (*trunc_fwd_fn)(const float*, float*, long long, const float2*, int, int);
-typedef void (*trunc_inv_fn)(const float*, float*, long long, const float2*, int, int, float);
+// truncated-mode variants: (in, out, images, tables, scale, keep_h, keep_w); the forward ignores scale
+typedef void (*trunc_fn)(const float*, float*, long long, const float2*, float, int, int);
 
 struct SpecEntry {
     int H, W, RA, RB, CA, CB, NT;
@@ -16,8 +15,8 @@ struct SpecEntry {
     spec_fn fwd, inv;
     bool pipelined;      // dft_pipe2d.cuh: one persistent CTA per SM, needs 16-byte aligned in/out
     int NT_inv = 0;      // threads of the inverse kernel when they differ from NT
-    trunc_fwd_fn trunc_fwd = nullptr;   // same CTA size and shared memory as fwd / inv
-    trunc_inv_fn trunc_inv = nullptr;
+    trunc_fn trunc_fwd = nullptr;   // same CTA size and shared memory as fwd / inv
+    trunc_fn trunc_inv = nullptr;
 };
 
 // nullptr when (H, W) has no specialised kernel
