@@ -457,7 +457,11 @@ static int realize_plan(trt_dft_plan_s* pl, trt_dft_plan_t* plan_out)
                     }
                     r.gp_ns = ns;
                     r.gp_ng = ns >= 3 ? 2 : 1;
-                    if (getenv("TRT_DFT_GP_NG")) r.gp_ng = std::max(1, std::min(atoi(getenv("TRT_DFT_GP_NG")), ns - 1));
+                    if (getenv("TRT_DFT_GP_NG")) {
+                        // A/B switch.  Groups are whole warps of equal count (named barriers count in warps).
+                        const int want = std::max(1, std::min(atoi(getenv("TRT_DFT_GP_NG")), ns - 1));
+                        if ((ct / 32) % want == 0) r.gp_ng = want;
+                    }
                     r.gp_stage = stage;
                     r.gp_smem = smem;
                     r.gp_smem_nopack = smem;
