@@ -243,6 +243,66 @@ def truncated_bench(capi, torch, peak, iters=200, nimg=SHAPE[0] * SHAPE[1], H=H,
     return out
 
 
+def half_io_bench(capi, torch, peak, iters=200, nimg=SHAPE[0] * SHAPE[1]):
+    """The headline shape with fp16 / bf16 tensors on both sides (trt_dft_plan_create_typed; fp32 arithmetic): half the
+    bytes per element cross HBM.  Its own algorithmic bytes; accuracy against fp64 torch.fft of the same 16-bit input
+    on the first 64 images."""
+    out = {}
+    st = torch.cuda.current_stream().cuda_stream
+    for name, dt in (("f16", torch.float16), ("bf16", torch.bfloat16)):
+        g = torch.Generator(device="cuda").manual_seed(1)
+        x = torch.randn(nimg, H, W, device="cuda", generator=g).to(dt)
+        y = torch.empty(nimg, H, W // 2 + 1, 2, device="cuda", dtype=dt)
+        xr = torch.empty_like(x)
+        f = capi.TypedPlan(capi.FORWARD, (H, W), nimg, dt)
+        i = capi.TypedPlan(capi.INVERSE, (H, W), nimg, dt)
+        ws = torch.empty(max(f.workspace_bytes, i.workspace_bytes, 16), dtype=torch.uint8, device="cuda")
+        fw = lambda: f.exec_ptr(x.data_ptr(), y.data_ptr(), ws.data_ptr(), st)
+        iv = lambda: i.exec_ptr(y.data_ptr(), xr.data_ptr(), ws.data_ptr(), st)
+        res = {}
+        for key, fn in (("fwd_ms", fw), ("inv_ms", iv), ("pair_ms", lambda: (fw(), iv()))):
+            for _ in range(5):
+                fn()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            torch.cuda.synchronize()
+            e0.record()
+            for _ in range(iters):
+                fn()
+            e1.record()
+            torch.cuda.synchronize()
+            res[key] = e0.elapsed_time(e1) / iters
+        ab = 2 * nimg * (H * W * 2 + H * (W // 2 + 1) * 4)
+        want = torch.view_as_real(torch.fft.rfft2(x[:64].cpu().double()))
+        res.update({"algorithmic_bytes_per_pair": ab, "pair_GBs": ab / res["pair_ms"] / 1e6,
+                    "frac_of_measured_peak": ab / res["pair_ms"] / 1e6 / peak,
+                    "rfft2_rel_l2_vs_fp64": float((y[:64].cpu().double() - want).norm() / want.norm()),
+                    "round_trip_rel_l2": float((xr.double() - x.double()).norm() / x.double().norm()),
+                    "route": f.describe()[1].split("[")[1].split("]")[0] if "[" in f.describe()[1] else f.describe()[1][:80]})
+        # what a half-precision engine pays without these kernels: conversion passes either side of the fp32 kernels
+        os.environ["TRT_DFT_IO_UNFUSED"] = "1"
+        try:
+            fu = capi.TypedPlan(capi.FORWARD, (H, W), nimg, dt)
+            iu = capi.TypedPlan(capi.INVERSE, (H, W), nimg, dt)
+        finally:
+            del os.environ["TRT_DFT_IO_UNFUSED"]
+        wsu = torch.empty(max(fu.workspace_bytes, iu.workspace_bytes, 16), dtype=torch.uint8, device="cuda")
+        stepu = lambda: (fu.exec_ptr(x.data_ptr(), y.data_ptr(), wsu.data_ptr(), st), iu.exec_ptr(y.data_ptr(), xr.data_ptr(), wsu.data_ptr(), st))
+        for _ in range(3):
+            stepu()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        torch.cuda.synchronize()
+        e0.record()
+        for _ in range(50):
+            stepu()
+        e1.record()
+        torch.cuda.synchronize()
+        res["pair_ms_with_conversion_passes"] = e0.elapsed_time(e1) / 50
+        out[name] = res
+        del f, i, fu, iu, x, y, xr, ws, wsu
+    torch.cuda.empty_cache()
+    return out
+
+
 def cufft_sequence(torch, capi, names):
     """The reference's own device path -- cufftXtMakePlanMany / cufftXtExec (+ cublasScalEx for the inverse), the calls
     of dft_plugins.cpp:161-196, :454-468 -- timed by tools/cufft_ref_bench in a SUBPROCESS (comparator only: cuFFT is
@@ -615,6 +675,10 @@ def run_ours(args):
                                                                           keeps=((64, 65), (32, 32), (16, 16), (12, 12)))
         except Exception as e:
             extras["truncated_modes"] = {"error": repr(e)[:300]}
+        try:
+            extras["half_io_cfg3"] = half_io_bench(capi, torch, peak)
+        except Exception as e:
+            extras["half_io_cfg3"] = {"error": repr(e)[:300]}
         extras["cufft_sequence"] = cufft_sequence(torch, capi, ["cfg1", "cfg2", "cfg3", "cfg4", "cfg5"])
     else:
         try:

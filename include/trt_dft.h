@@ -100,6 +100,27 @@ int trt_dft_plan_set_column_split(trt_dft_plan_t plan, int nparts, const int64_t
 int trt_dft_plan_create_truncated(trt_dft_plan_t* plan, int direction, const int64_t* dims, int64_t batch, int64_t keep_h, int64_t keep_w);
 
 /*
+ * 16-bit tensors at the plan's boundary, fp32 arithmetic inside.  No counterpart in the reference, which accepts
+ * fp32 only (supportsFormatCombination, dft_plugins.cpp:93-105), so a half-precision TensorRT engine has to convert
+ * either side of the plugin -- two more passes over HBM for a transform that is bound by HBM.
+ *   io_type = TRT_DFT_IO_F32  : exactly trt_dft_plan_create
+ *             TRT_DFT_IO_F16 / TRT_DFT_IO_BF16 : the real tensor and the complex tensor (re, im interleaved, trailing
+ *             dim of 2) both hold 16-bit elements; same shapes, same scaling as trt_dft_plan_create.  Results are the
+ *             fp32 transform of the 16-bit input, rounded to nearest even on the way out.  (fp16 overflows at 65504:
+ *             an unnormalised forward transform of n points grows like sqrt(n) times the input's magnitude.)
+ * 90 x 180 runs kernels that convert as they load and store, so only 16-bit data crosses HBM (no workspace; both
+ * tensors 16-byte aligned).  Every other shape runs the fp32 plan between two conversion passes through the workspace
+ * (query trt_dft_workspace_bytes; tensors 2-byte aligned).  trt_dft_plan_input_floats / _output_floats count elements.
+ * Executed with trt_dft_exec / trt_dft_exec_host / trt_dft_exec_static_ws.
+ */
+#define TRT_DFT_IO_F32 0
+#define TRT_DFT_IO_F16 1
+#define TRT_DFT_IO_BF16 2
+int trt_dft_plan_create_typed(trt_dft_plan_t* plan, int direction, int rank, const int64_t* dims, int64_t batch, int io_type);
+/* The io_type a plan was created with (TRT_DFT_IO_F32 for every other constructor), -1 for NULL. */
+int trt_dft_plan_io_type(trt_dft_plan_t plan);
+
+/*
  * Multi-GPU pencil rfft2 with the exchange fused into the row pass (no counterpart in the single-GPU reference,
  * dft_plugins.cpp:341).  Same column split as trt_dft_plan_set_column_split, but block j of every image is not
  * packed into `out`: the row kernel stores it straight into rank j's column slab

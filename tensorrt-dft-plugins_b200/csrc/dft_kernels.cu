@@ -136,6 +136,12 @@ struct trt_dft_plan_s {
     float t_scale = 1.f;
     trt_dft_plan_t t_full = nullptr;      // ... or the full transform through the workspace plus a crop / pad kernel
     size_t t_full_ws_off = 0;             // where the full plan's own workspace starts inside ours
+    // typed-I/O plan (trt_dft_plan_create_typed): 16-bit data on both sides, fp32 arithmetic.  Either one kernel that
+    // converts as it loads and stores (io_fn; t_threads / t_smem / t_grid / t_scale as above), or the fp32 plan t_full
+    // between two conversion passes through the workspace: [fp32 input | fp32 output | t_full's workspace].
+    int io_type = TRT_DFT_IO_F32;
+    spec_fn io_fn = nullptr;
+    size_t io_out_off = 0;
     // trt_dft_exec_host scratch (lazily allocated, reused across calls)
     std::mutex host_mu;
     void* h_in = nullptr;
@@ -287,6 +293,65 @@ int trt_dft_plan_create_truncated(trt_dft_plan_t* plan_out, int direction, const
     *plan_out = pl;
     return TRT_DFT_OK;
 }
+
+int trt_dft_plan_create_typed(trt_dft_plan_t* plan_out, int direction, int rank, const int64_t* dims, int64_t batch, int io_type)
+{
+    if (io_type == TRT_DFT_IO_F32) return trt_dft_plan_create(plan_out, direction, rank, dims, batch);
+    if (!plan_out || (io_type != TRT_DFT_IO_F16 && io_type != TRT_DFT_IO_BF16)) return TRT_DFT_ERR_INVALID_ARG;
+    *plan_out = nullptr;
+    trt_dft_plan_t full = nullptr;
+    const int rc = trt_dft_plan_create(&full, direction, rank, dims, batch);     // validates every argument
+    if (rc != TRT_DFT_OK) return rc;
+    auto* pl = new (std::nothrow) trt_dft_plan_s();
+    if (!pl) {
+        trt_dft_plan_destroy(full);
+        return TRT_DFT_ERR_ALLOC;
+    }
+    pl->io_type = io_type;
+    pl->device = full->device;
+    pl->pd.direction = direction;
+    pl->pd.rank = rank;
+    for (int i = 0; i < rank; ++i) pl->pd.dims[i] = dims[i];
+    pl->pd.batch = batch;
+    pl->pd.in_floats = full->pd.in_floats;         // element counts; the elements are 16-bit
+    pl->pd.out_floats = full->pd.out_floats;
+    const char* tname = io_type == TRT_DFT_IO_F16 ? "f16" : "bf16";
+    char desc[512];
+    const bool inv = direction == TRT_DFT_INVERSE;
+    const SpecEntry* e = (rank == 2 && batch > 0 && !getenv("TRT_DFT_NO_SPEC") && !getenv("TRT_DFT_IO_UNFUSED"))
+                             ? find_spec((int)dims[0], (int)dims[1]) : nullptr;
+    const spec_fn fused = e ? (inv ? e->inv16[io_type - 1] : e->fwd16[io_type - 1]) : nullptr;
+    int num_sms = 0, occ = 0;
+    if (fused && cudaDeviceGetAttribute(&num_sms, cudaDevAttrMultiProcessorCount, pl->device) == cudaSuccess) {
+        pl->t_threads = (inv && e->NT_inv) ? e->NT_inv : e->NT;
+        pl->t_smem = inv ? e->smem_i : e->smem_f;
+        pl->t_scale = (float)(1.0 / ((double)dims[0] * (double)dims[1]));
+        if (cudaFuncSetAttribute((const void*)fused, cudaFuncAttributeMaxDynamicSharedMemorySize, pl->t_smem) == cudaSuccess &&
+            cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, (const void*)fused, pl->t_threads, pl->t_smem) == cudaSuccess && occ >= 1) {
+            pl->io_fn = fused;
+            pl->t_grid = (int)std::min<long long>(batch, (long long)num_sms * occ);
+        } else {
+            cudaGetLastError();
+        }
+    }
+    if (pl->io_fn) {
+        trt_dft_plan_destroy(full);
+        snprintf(desc, sizeof desc, "%s<%d,%d> %s in, %s out, fp32 arithmetic images=%lld [converts as it loads and stores] grid=%dx%d smem=%d",
+                 inv ? "irfft2" : "rfft2", (int)dims[0], (int)dims[1], tname, tname, (long long)batch, pl->t_grid, pl->t_threads, pl->t_smem);
+    } else {
+        pl->t_full = full;
+        const size_t a = ((size_t)full->pd.in_floats * 4 + 255) / 256 * 256, b = ((size_t)full->pd.out_floats * 4 + 255) / 256 * 256;
+        pl->io_out_off = a;
+        pl->t_full_ws_off = a + b;
+        pl->pd.ws_bytes = batch > 0 ? a + b + full->pd.ws_bytes : 0;
+        snprintf(desc, sizeof desc, "%s -> fp32 ; %.380s ; fp32 -> %s", tname, full->pd.description.c_str(), tname);
+    }
+    pl->pd.description = desc;
+    *plan_out = pl;
+    return TRT_DFT_OK;
+}
+
+int trt_dft_plan_io_type(trt_dft_plan_t plan) { return plan ? plan->io_type : -1; }
 
 // Device side of plan creation: tables to the GPU, kernel attributes, grid sizes.
 static int realize_plan(trt_dft_plan_s* pl, trt_dft_plan_t* plan_out)
@@ -690,6 +755,7 @@ int trt_dft_plan_describe(trt_dft_plan_t plan, char* buf, size_t len)
         buf[len - 1] = 0;
     }
     if (plan->trunc) return plan->pd.batch == 0 ? 0 : (plan->t_fwd ? 1 : 1 + (int)plan->t_full->launches.size());
+    if (plan->io_type != TRT_DFT_IO_F32) return plan->pd.batch == 0 ? 0 : (plan->io_fn ? 1 : 2 + (int)plan->t_full->launches.size());
     return (int)plan->launches.size();
 }
 
@@ -740,10 +806,42 @@ static int exec_truncated(trt_dft_plan_t plan, const void* in, void* out, void* 
     return TRT_DFT_OK;
 }
 
+static int exec_typed(trt_dft_plan_t plan, const void* in, void* out, void* workspace, void* stream)
+{
+    if (plan->pd.batch == 0) return TRT_DFT_OK;
+    if (!in || !out) return TRT_DFT_ERR_INVALID_ARG;
+    int cur_dev = -1;
+    if (cudaGetDevice(&cur_dev) != cudaSuccess || cur_dev != plan->device) {
+        cudaGetLastError();
+        return TRT_DFT_ERR_INVALID_ARG;
+    }
+    if (plan->io_fn) {
+        // whole images move as bulk copies: 16-byte aligned tensors (any tensor of a framework allocator is)
+        if ((((uintptr_t)in) | ((uintptr_t)out)) & 15) return TRT_DFT_ERR_INVALID_ARG;
+        plan->io_fn<<<plan->t_grid, plan->t_threads, plan->t_smem, (cudaStream_t)stream>>>((const float*)in, (float*)out, plan->pd.batch,
+                                                                                           nullptr, plan->t_scale);
+    } else {
+        if (!workspace || ((uintptr_t)workspace & 15)) return TRT_DFT_ERR_WORKSPACE;
+        if ((((uintptr_t)in) | ((uintptr_t)out)) & 1) return TRT_DFT_ERR_INVALID_ARG;
+        float* a = (float*)workspace;
+        float* b = (float*)((unsigned char*)workspace + plan->io_out_off);
+        dft::launch_widen(in, a, plan->pd.in_floats, plan->io_type, stream);
+        const int rc = trt_dft_exec(plan->t_full, a, b, (unsigned char*)workspace + plan->t_full_ws_off, stream);
+        if (rc != TRT_DFT_OK) return rc;
+        dft::launch_narrow(b, out, plan->pd.out_floats, plan->io_type, stream);
+    }
+    if (cudaPeekAtLastError() != cudaSuccess) {
+        cudaGetLastError();
+        return TRT_DFT_ERR_CUDA;
+    }
+    return TRT_DFT_OK;
+}
+
 int trt_dft_exec(trt_dft_plan_t plan, const void* in, void* out, void* workspace, void* stream)
 {
     if (!plan) return TRT_DFT_ERR_INVALID_ARG;
     if (plan->trunc) return exec_truncated(plan, in, out, workspace, stream);
+    if (plan->io_type != TRT_DFT_IO_F32) return exec_typed(plan, in, out, workspace, stream);
     if (plan->launches.empty()) return TRT_DFT_OK;
     if (!in || !out) return TRT_DFT_ERR_INVALID_ARG;
     // the plan's tables live on the GPU it was created on: launching from another current device would
@@ -816,7 +914,8 @@ int trt_dft_plan_destroy(trt_dft_plan_t plan)
 int trt_dft_exec_host(trt_dft_plan_t plan, const void* host_in, void* host_out)
 {
     if (!plan) return TRT_DFT_ERR_INVALID_ARG;
-    if (plan->launches.empty() && !(plan->trunc && plan->pd.batch > 0)) return TRT_DFT_OK;
+    const bool wrapped = plan->trunc || plan->io_type != TRT_DFT_IO_F32;     // plans without launches of their own
+    if (plan->launches.empty() && !(wrapped && plan->pd.batch > 0)) return TRT_DFT_OK;
     if (!host_in || !host_out) return TRT_DFT_ERR_INVALID_ARG;
     int cur_dev = -1;
     if (cudaGetDevice(&cur_dev) != cudaSuccess || cur_dev != plan->device) {
@@ -824,7 +923,8 @@ int trt_dft_exec_host(trt_dft_plan_t plan, const void* host_in, void* host_out)
         return TRT_DFT_ERR_INVALID_ARG;      // device buffers below must live on the plan's GPU
     }
     std::lock_guard<std::mutex> lock(plan->host_mu);
-    const size_t in_bytes = (size_t)plan->pd.in_floats * 4, out_bytes = (size_t)plan->pd.out_floats * 4;
+    const size_t esz = plan->io_type == TRT_DFT_IO_F32 ? 4 : 2;
+    const size_t in_bytes = (size_t)plan->pd.in_floats * esz, out_bytes = (size_t)plan->pd.out_floats * esz;
     const int64_t batch = plan->pd.batch;
     if (!plan->h_in) {
         // Large transfers are cut into batch chunks and run as a 3-stream pipeline (H2D | kernels | D2H),
@@ -833,7 +933,7 @@ int trt_dft_exec_host(trt_dft_plan_t plan, const void* host_in, void* host_out)
         if (const char* e = getenv("TRT_DFT_HOST_CHUNKS")) nchunks = std::max(1, std::min(32, atoi(e)));   // tuning override
         if (nchunks > batch) nchunks = (int)batch;
         // a c2c plan's `batch` (outer * inner) is not a contiguous leading dimension of [outer][n][inner]: one chunk
-        if (plan->c2c || plan->trunc) nchunks = 1;
+        if (plan->c2c || wrapped) nchunks = 1;
         plan->h_chunk = (batch + nchunks - 1) / nchunks;
         const int64_t tail = batch % plan->h_chunk;
         bool ok = cudaMalloc(&plan->h_in, in_bytes) == cudaSuccess && cudaMalloc(&plan->h_out, out_bytes) == cudaSuccess;

@@ -22,4 +22,10 @@ pipe_fn pipe_kernel_for_geo(const KParams& k, bool tables_in_smem, int* compute_
 void launch_crop_modes(const void* full, void* kept, long long nimg, int H, int MO, int kh, int kw, void* stream);
 void launch_pad_modes(const void* kept, void* full, long long nimg, int H, int MO, int kh, int kw, void* stream);
 
+
+// dft_typed_io.cu: 16-bit <-> fp32 passes either side of the fp32 transform (fallback of the typed-I/O plans);
+// io_type is TRT_DFT_IO_F16 (1) or TRT_DFT_IO_BF16 (2)
+void launch_widen(const void* src, float* dst, long long n, int io_type, void* stream);
+void launch_narrow(const float* src, void* dst, long long n, int io_type, void* stream);
+
 }  // namespace dft

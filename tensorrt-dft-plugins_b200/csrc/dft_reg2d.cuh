@@ -27,8 +27,12 @@
 // run across lines, so the 128-bit loads of a quarter warp hit 8 different 16-byte bank groups; the
 // transposed stores have lanes along the contiguous index.
 #pragma once
+#include <cuda_bf16.h>
+#include <cuda_fp16.h>
 #include <cuda_runtime.h>
 #include <stdint.h>
+
+#include <type_traits>
 
 #include "dft_butterflies.cuh"
 #include "dft_phases.cuh"
@@ -294,15 +298,188 @@ __device__ __forceinline__ void io_loop(int g, const unsigned char* __restrict__
     asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
 }
 
+// ---- 16-bit tensors at the kernel's boundary (trt_dft_plan_create_typed) ---------------------------------------------
+// IO = float is the ordinary kernel.  IO = __half / __nv_bfloat16: both tensors hold 16-bit elements, everything between the
+// first shared-memory read and the last shared-memory write is the fp32 kernel unchanged.  The real image is H*W*2 bytes,
+// a multiple of 16, and travels as before.  The spectrum is H*MO*4 bytes = 8 mod 16 per image: image t starts 8 bytes off a
+// 16-byte boundary when t is odd.  Bulk copies need 16-byte alignment at both ends, so an odd image sits 8 bytes into its
+// stage, and every image travels as a 16-byte aligned CORE of H*MO*4 - 8 bytes (bulk copy) plus an 8-byte EDGE -- its
+// first two elements when t is odd, its last two when t is even -- which the I/O thread moves with one ordinary
+// 64-bit access.
+template <class IO>
+struct Io16;
+// fold(a, b, sg) = a + sg * b for complex values a, b held as two 16-bit numbers in one register, sg = +-1 in the same
+// 16-bit format: widen a, then one mixed-precision FMA per component (fma.f32.f16 / .bf16 -> FHFMA on sm_100a: the 16-bit
+// operand is read as it is, exactly as a conversion followed by an fp32 FMA would compute).  Four instructions per complex
+// value where convert-everything-then-FFMA takes six (fp16) or eight (bf16); the fp32 kernel takes two.
+template <>
+struct Io16<__half> {
+    typedef __half2 v2;
+    static constexpr unsigned short kOne = 0x3C00, kMinusOne = 0xBC00;
+    __device__ static __forceinline__ v2 down(float2 v) { return __floats2half2_rn(v.x, v.y); }
+    __device__ static __forceinline__ float2 fold(unsigned a, unsigned b, unsigned short sg)
+    {
+        const unsigned short alo = (unsigned short)(a & 0xffffu), ahi = (unsigned short)(a >> 16);
+        const unsigned short blo = (unsigned short)(b & 0xffffu), bhi = (unsigned short)(b >> 16);
+        float ax, ay, rx, ry;
+        asm("cvt.f32.f16 %0, %1;" : "=f"(ax) : "h"(alo));
+        asm("cvt.f32.f16 %0, %1;" : "=f"(ay) : "h"(ahi));
+        asm("fma.rn.f32.f16 %0, %1, %2, %3;" : "=f"(rx) : "h"(blo), "h"(sg), "f"(ax));
+        asm("fma.rn.f32.f16 %0, %1, %2, %3;" : "=f"(ry) : "h"(bhi), "h"(sg), "f"(ay));
+        return float2{rx, ry};
+    }
+};
+template <>
+struct Io16<__nv_bfloat16> {
+    typedef __nv_bfloat162 v2;
+    static constexpr unsigned short kOne = 0x3F80, kMinusOne = 0xBF80;
+    __device__ static __forceinline__ v2 down(float2 v) { return __floats2bfloat162_rn(v.x, v.y); }
+    __device__ static __forceinline__ float2 fold(unsigned a, unsigned b, unsigned short sg)
+    {
+        const unsigned short blo = (unsigned short)(b & 0xffffu), bhi = (unsigned short)(b >> 16);
+        const float ax = __uint_as_float(a << 16), ay = __uint_as_float(a & 0xffff0000u);      // bf16 is the top half of an fp32
+        float rx, ry;
+        asm("fma.rn.f32.bf16 %0, %1, %2, %3;" : "=f"(rx) : "h"(blo), "h"(sg), "f"(ax));
+        asm("fma.rn.f32.bf16 %0, %1, %2, %3;" : "=f"(ry) : "h"(bhi), "h"(sg), "f"(ay));
+        return float2{rx, ry};
+    }
+};
+
+// load_fold over a line of 2*L2 complex values whose 8-byte unit j holds x[2j], x[2j+1] as four 16-bit numbers
+template <class IO, int L2>
+__device__ __forceinline__ void load_fold16(float2 (&y)[L2], const uint2* __restrict__ line, unsigned short sg)
+{
+    constexpr int S = (L2 + 1) / 2;
+    uint2 prev = line[((L2 - 1) * S) % L2];
+    static_for<0, L2>([&](auto ic) {
+        constexpr int i = decltype(ic)::value;
+        constexpr int n2 = (i * S) % L2;
+        const uint2 cur = line[n2];
+        y[n2] = Io16<IO>::fold(cur.x, prev.y, sg);
+        prev = cur;
+    });
+}
+
+template <class IO, int L2, int STRIDE>
+__device__ __forceinline__ void load_fold_rev16(float2 (&y)[L2], const unsigned* __restrict__ src, unsigned short sg)
+{
+    constexpr int L = 2 * L2;
+    static_for<0, L2>([&](auto nc) {
+        constexpr int n2 = decltype(nc)::value;
+        constexpr int ia = (L - 2 * n2) % L, ib = (2 * L - L2 - 2 * n2) % L;
+        y[n2] = Io16<IO>::fold(src[ia * STRIDE], src[ib * STRIDE], sg);
+    });
+}
+
+// store_cols with 16-bit elements: dst points at element [0][column] of the (possibly shifted) tile [q][k]
+template <class IO, class C>
+__device__ __forceinline__ void store_cols16(const float2 (&y)[C::Hh], typename Io16<IO>::v2* __restrict__ dst, int p)
+{
+    typename Io16<IO>::v2* dp = dst + p * (C::Hh * C::MO);
+    typename Io16<IO>::v2* dm = dst - p * (C::Hh * C::MO);
+    static_for<0, C::Hh>([&](auto kc) {
+        constexpr int k2 = decltype(kc)::value;
+        constexpr int c0 = ((C::Hh + 1) * k2) % C::H;
+        if constexpr (c0 < C::Hh) dp[c0 * C::MO] = Io16<IO>::down(y[k2]);
+        else dm[c0 * C::MO] = Io16<IO>::down(y[k2]);
+    });
+}
+
+// io_loop for the 16-bit kernels.  FWD: loads real images (RB bytes at the start of the stage), stores spectra (core +
+// edge).  !FWD: loads spectra, stores real images.  Pieces as in io_loop; a load piece may start 16 bytes into the stage,
+// hence LP <= SP - 16.
+template <class C, int STAGE, bool FWD>
+__device__ __forceinline__ void io_loop16(int g, const unsigned char* __restrict__ in, unsigned char* __restrict__ out, long long nimg,
+                                          unsigned char* stages, unsigned full0, unsigned done0)
+{
+    constexpr int NG = C::NG, NS = C::NS, KP = 4;
+    constexpr int RB = C::TILE_F / 2, CB = C::TILE_I / 2, CORE = CB - 8;
+    static_assert(RB % 16 == 0 && CB % 16 == 8, "real images travel whole, spectra as core + edge");
+    constexpr int LOADB = FWD ? RB : CORE, STOREB = FWD ? CORE : RB;
+    constexpr int SP = (STOREB / KP + 15) / 16 * 16;
+    constexpr int LP0 = (LOADB / KP) / 16 * 16;
+    constexpr int LP = LP0 < SP - 16 ? LP0 : SP - 16;
+    static_assert(LP > 0 && (KP - 1) * SP < STOREB && (KP - 1) * LP < LOADB, "piece sizes");
+    auto load_piece = [&](long long tile, int s, int j) {
+        const unsigned odd = FWD ? 0u : (unsigned)(tile & 1);
+        const unsigned off = (unsigned)(j * LP);
+        const unsigned bytes = (j == KP - 1) ? (unsigned)(LOADB - (KP - 1) * LP) : (unsigned)LP;
+        asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+                         pipe::s32(stages + (size_t)s * STAGE) + 16u * odd + off),
+                     "l"(in + tile * (long long)(FWD ? RB : CB) + 8u * odd + off), "r"(bytes), "r"(full0 + 8 * s)
+                     : "memory");
+    };
+    auto expect = [&](int s) {
+        asm volatile("mbarrier.expect_tx.relaxed.cta.shared::cta.b64 [%0], %1;" ::"r"(full0 + 8 * s), "r"((unsigned)LOADB) : "memory");
+    };
+    // spectrum edge of image `tile`: global byte offset inside the image / shared byte offset inside the stage
+    auto edge_g = [&](long long tile) { return (tile & 1) ? 0 : CORE; };
+    auto edge_s = [&](long long tile) { return (tile & 1) ? 8 : CORE; };
+    auto load_edge = [&](long long tile) {
+        return __ldg(reinterpret_cast<const uint2*>(in + tile * (long long)CB + edge_g(tile)));
+    };
+    auto put_edge_and_arrive = [&](long long tile, int s, uint2 e) {
+        if (!FWD) *reinterpret_cast<uint2*>(stages + (size_t)s * STAGE + edge_s(tile)) = e;
+        pipe::mbar_arrive(full0 + 8 * s);          // (release: the edge is visible to whoever sees the phase complete)
+    };
+    if (g == 0)
+        for (int s = 0; s < NS; ++s) {
+            const long long tile = blockIdx.x + s * (long long)gridDim.x;
+            if (tile >= nimg) break;
+            uint2 e = uint2{0u, 0u};
+            if (!FWD) e = load_edge(tile);
+            expect(s);
+#pragma unroll
+            for (int j = 0; j < KP; ++j) load_piece(tile, s, j);
+            put_edge_and_arrive(tile, s, e);
+        }
+    long long it = g;
+    for (long long tile = blockIdx.x + (long long)g * gridDim.x; tile < nimg; tile += (long long)NG * gridDim.x, it += NG) {
+        const int s = (int)(it % NS);
+        const long long next = tile + (long long)NS * gridDim.x;   // the image that uses this stage next
+        uint2 e = uint2{0u, 0u};
+        if (!FWD && next < nimg) e = load_edge(next);              // in flight while this image is still being computed
+        pipe::mbar_wait(done0 + 8 * (g * NS + s), (unsigned)((it / C::LCM) & 1));
+        const unsigned odd = FWD ? (unsigned)(tile & 1) : 0u;
+        unsigned char* stage = stages + (size_t)s * STAGE;
+        if (FWD) *reinterpret_cast<uint2*>(out + tile * (long long)CB + edge_g(tile)) = *reinterpret_cast<const uint2*>(stage + edge_s(tile));
+#pragma unroll
+        for (int j = 0; j < KP; ++j) {
+            const int off = j * SP;
+            const int end = (j == KP - 1) ? STOREB : (j + 1) * SP;
+            asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(out + tile * (long long)(FWD ? CB : RB) + 8u * odd + off),
+                         "r"(pipe::s32(stage) + 16u * odd + (unsigned)off), "r"((unsigned)(end - off))
+                         : "memory");
+            asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+        }
+        if (next < nimg) {
+            expect(s);
+            asm volatile("cp.async.bulk.wait_group.read 3;" ::: "memory");
+            load_piece(next, s, 0);
+            asm volatile("cp.async.bulk.wait_group.read 2;" ::: "memory");
+            load_piece(next, s, 1);
+            asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory");
+            load_piece(next, s, 2);
+            asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
+            load_piece(next, s, 3);
+            put_edge_and_arrive(next, s, e);       // (every store piece has been read out: the edge may land anywhere)
+        }
+    }
+    // the last bulk stores must have completed before the CTA (and its shared memory) goes away
+    asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
+}
+
 }  // namespace reg2d
 
 // ---- forward ---------------------------------------------------------------------------------
 // TR: truncated modes (see above io_loop): only rows [0, kh) u [H - kh, H), columns [0, kw) of the spectrum leave
 // the kernel, as a dense [2*kh][kw] block; columns past kw are not transformed at all.
-template <class C, bool TR>
+template <class C, bool TR, class IO = float>
 __device__ __forceinline__ void reg_rfft2_body(const float* __restrict__ in, float* __restrict__ out, long long nimg, const int kh, const int kw)
 {
+    constexpr bool IO16 = !std::is_same<IO, float>::value;
     static_assert(!TR || C::IOW, "the truncated kernels use the I/O-warp layout");
+    static_assert(!IO16 || (C::IOW && !TR), "the 16-bit kernels use the I/O-warp layout and move the full spectrum");
     // (truncated: the two halves of an image's work are no longer equal, so the groups run free instead of taking turns)
     constexpr int PPX = TR ? 0 : C::PP;
     constexpr int H = C::H, M = C::M, MO = C::MO, GT = C::GT, NG = C::NG, NS = C::NS, WPP = C::WPP;
@@ -324,10 +501,15 @@ __device__ __forceinline__ void reg_rfft2_body(const float* __restrict__ in, flo
 
     if constexpr (C::IOW) {
         if (tid >= NG * GT) {
-            if ((tid & 31) == 0)
-                reg2d::io_loop<C, C::STAGE_F>((tid - NG * GT) >> 5, reinterpret_cast<const unsigned char*>(in),
-                                              reinterpret_cast<unsigned char*>(out), nimg, stages, full0, done0, C::TILE_F,
-                                              TR ? 16 * kh * kw : C::TILE_I);
+            if ((tid & 31) == 0) {
+                if constexpr (IO16)
+                    reg2d::io_loop16<C, C::STAGE_F, true>((tid - NG * GT) >> 5, reinterpret_cast<const unsigned char*>(in),
+                                                          reinterpret_cast<unsigned char*>(out), nimg, stages, full0, done0);
+                else
+                    reg2d::io_loop<C, C::STAGE_F>((tid - NG * GT) >> 5, reinterpret_cast<const unsigned char*>(in),
+                                                  reinterpret_cast<unsigned char*>(out), nimg, stages, full0, done0, C::TILE_F,
+                                                  TR ? 16 * kh * kw : C::TILE_I);
+            }
             return;
         }
     }
@@ -378,7 +560,10 @@ __device__ __forceinline__ void reg_rfft2_body(const float* __restrict__ in, flo
         // rows: the whole packed row -> registers; the transposed result [k][row] overwrites the stage
         {
             float2 z[C::Mh];
-            reg2d::load_fold<C::Mh>(z, reinterpret_cast<const float4*>(buf) + lrow * (M / 2), sg);
+            if constexpr (IO16)
+                reg2d::load_fold16<IO, C::Mh>(z, reinterpret_cast<const uint2*>(buf) + lrow * (M / 2),
+                                              p ? reg2d::Io16<IO>::kMinusOne : reg2d::Io16<IO>::kOne);
+            else reg2d::load_fold<C::Mh>(z, reinterpret_cast<const float4*>(buf) + lrow * (M / 2), sg);
             refill();                                   // the previous image's store has long since drained
             DFT_TR(it, 2);
             pipe::group_sync(bar_id, GT);               // every row has been read
@@ -398,7 +583,12 @@ __device__ __forceinline__ void reg_rfft2_body(const float* __restrict__ in, flo
             DFT_TR(it, 6);
             reg2d::line_fft<C::CA, C::CB>(y);
             pipe::group_sync(bar_id, GT);               // every column has been read
-            reg2d::store_cols<C>(y, buf + lcol, p);
+            if constexpr (IO16) {
+                typedef typename reg2d::Io16<IO>::v2 v2;
+                reg2d::store_cols16<IO, C>(y, reinterpret_cast<v2*>(reinterpret_cast<unsigned char*>(buf) + 8 * (int)(tile & 1)) + lcol, p);
+            } else {
+                reg2d::store_cols<C>(y, buf + lcol, p);
+            }
         } else {
             pipe::group_sync(bar_id, GT);
         }
@@ -459,6 +649,13 @@ __global__ void __launch_bounds__(C::THREADS, 1)
 {
     reg_rfft2_body<C, false>(in, out, nimg, 0, 0);
 }
+template <class C, class IO>
+__global__ void __launch_bounds__(C::THREADS, 1)
+    reg_rfft2_io16_kernel(const float* __restrict__ in, float* __restrict__ out, long long nimg, const float2* __restrict__ /*tables*/,
+                          float /*scale*/)
+{
+    reg_rfft2_body<C, false, IO>(in, out, nimg, 0, 0);
+}
 template <class C>
 __global__ void __launch_bounds__(C::THREADS, 1)
     reg_rfft2_trunc_kernel(const float* __restrict__ in, float* __restrict__ out, long long nimg, const float2* __restrict__ /*tables*/,
@@ -468,11 +665,13 @@ __global__ void __launch_bounds__(C::THREADS, 1)
 }
 
 // ---- inverse ---------------------------------------------------------------------------------
-template <class C, bool TR>
+template <class C, bool TR, class IO = float>
 __device__ __forceinline__ void reg_irfft2_body(const float* __restrict__ in, float* __restrict__ out, long long nimg, float scale,
                                                 const int kh, const int kw)
 {
+    constexpr bool IO16 = !std::is_same<IO, float>::value;
     static_assert(!TR || C::IOW, "the truncated kernels use the I/O-warp layout");
+    static_assert(!IO16 || (C::IOW && !TR), "the 16-bit kernels use the I/O-warp layout and move the full spectrum");
     constexpr int PPX = TR ? 0 : C::PP;
     constexpr int H = C::H, M = C::M, Mh = C::Mh, MO = C::MO, PI = C::PI, GT = C::GT, NG = C::NG, NS = C::NS, WPP = C::WPP;
     constexpr int NTW = C::NPAIR + 1;
@@ -495,10 +694,15 @@ __device__ __forceinline__ void reg_irfft2_body(const float* __restrict__ in, fl
 
     if constexpr (C::IOW) {
         if (tid >= NG * GT) {
-            if ((tid & 31) == 0)
-                reg2d::io_loop<C, C::STAGE_I>((tid - NG * GT) >> 5, reinterpret_cast<const unsigned char*>(in),
-                                              reinterpret_cast<unsigned char*>(out), nimg, stages, full0, done0,
-                                              TR ? 16 * kh * kw : C::TILE_I, C::TILE_F, TR ? (C::TAIL - 2 * kh * kw) * 8 : 0);
+            if ((tid & 31) == 0) {
+                if constexpr (IO16)
+                    reg2d::io_loop16<C, C::STAGE_I, false>((tid - NG * GT) >> 5, reinterpret_cast<const unsigned char*>(in),
+                                                           reinterpret_cast<unsigned char*>(out), nimg, stages, full0, done0);
+                else
+                    reg2d::io_loop<C, C::STAGE_I>((tid - NG * GT) >> 5, reinterpret_cast<const unsigned char*>(in),
+                                                  reinterpret_cast<unsigned char*>(out), nimg, stages, full0, done0,
+                                                  TR ? 16 * kh * kw : C::TILE_I, C::TILE_F, TR ? (C::TAIL - 2 * kh * kw) * 8 : 0);
+            }
             return;
         }
     }
@@ -595,7 +799,13 @@ __device__ __forceinline__ void reg_irfft2_body(const float* __restrict__ in, fl
             });
         } else {
             float2 y[C::Hh];
-            reg2d::load_fold_rev<C::Hh, MO>(y, buf + lcol, sgc);
+            if constexpr (IO16) {
+                reg2d::load_fold_rev16<IO, C::Hh, MO>(
+                    y, reinterpret_cast<const unsigned*>(reinterpret_cast<const unsigned char*>(buf) + 8 * (int)(tile & 1)) + lcol,
+                    pc ? reg2d::Io16<IO>::kMinusOne : reg2d::Io16<IO>::kOne);
+            } else {
+                reg2d::load_fold_rev<C::Hh, MO>(y, buf + lcol, sgc);
+            }
             refill();                                   // the previous image's store has long since drained
             pipe::group_sync(bar_id, GT);               // every column has been read
             reg2d::line_fft<C::CA, C::CB>(y);
@@ -638,8 +848,15 @@ __device__ __forceinline__ void reg_irfft2_body(const float* __restrict__ in, fl
                 const float ox = __shfl_xor_sync(0xffffffffu, z[n2].x, 16);
                 const float oy = __shfl_xor_sync(0xffffffffu, z[n2].y, 16);
                 const float2 r = float2{fmaf(sgr, z[n2].x, ox), fmaf(sgr, z[n2].y, oy)};
-                if constexpr (c0 < Mh) op[c0] = r;
-                else om[c0] = r;
+                if constexpr (IO16) {
+                    // (the same element of the dense image, four bytes wide instead of eight)
+                    typedef typename reg2d::Io16<IO>::v2 v2;
+                    if constexpr (c0 < Mh) reinterpret_cast<v2*>(buf)[(op - buf) + c0] = reg2d::Io16<IO>::down(r);
+                    else reinterpret_cast<v2*>(buf)[(om - buf) + c0] = reg2d::Io16<IO>::down(r);
+                } else {
+                    if constexpr (c0 < Mh) op[c0] = r;
+                    else om[c0] = r;
+                }
             });
             pipe::fence_async();
             if constexpr (C::IOW) {
@@ -669,6 +886,13 @@ __global__ void __launch_bounds__(C::THREADS, 1)
                       const float2* __restrict__ /*tables*/, float scale)
 {
     reg_irfft2_body<C, false>(in, out, nimg, scale, 0, 0);
+}
+template <class C, class IO>
+__global__ void __launch_bounds__(C::THREADS, 1)
+    reg_irfft2_io16_kernel(const float* __restrict__ in, float* __restrict__ out, long long nimg, const float2* __restrict__ /*tables*/,
+                           float scale)
+{
+    reg_irfft2_body<C, false, IO>(in, out, nimg, scale, 0, 0);
 }
 template <class C>
 __global__ void __launch_bounds__(C::THREADS, 1)

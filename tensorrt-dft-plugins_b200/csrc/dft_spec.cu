@@ -37,6 +37,10 @@ SpecEntry make_reg()
                 reg_rfft2_kernel<C>, reg_irfft2_kernel<C>, true};
     e.trunc_fwd = reg_rfft2_trunc_kernel<C>;
     e.trunc_inv = reg_irfft2_trunc_kernel<C>;
+    e.fwd16[0] = reg_rfft2_io16_kernel<C, __half>;
+    e.inv16[0] = reg_irfft2_io16_kernel<C, __half>;
+    e.fwd16[1] = reg_rfft2_io16_kernel<C, __nv_bfloat16>;
+    e.inv16[1] = reg_irfft2_io16_kernel<C, __nv_bfloat16>;
     return e;
 }
 

@@ -17,6 +17,10 @@ struct SpecEntry {
     int NT_inv = 0;      // threads of the inverse kernel when they differ from NT
     trunc_fn trunc_fwd = nullptr;   // same CTA size and shared memory as fwd / inv
     trunc_fn trunc_inv = nullptr;
+    // 16-bit tensors on both sides, fp32 arithmetic ([0] fp16, [1] bf16; the pointers are passed as float*): same CTA
+    // size and shared memory again
+    spec_fn fwd16[2] = {nullptr, nullptr};
+    spec_fn inv16[2] = {nullptr, nullptr};
 };
 
 // nullptr when (H, W) has no specialised kernel

@@ -23,6 +23,7 @@
 
 #include <stdint.h>
 #include <stdio.h>
+#include <stdlib.h>
 #include <string.h>
 
 #include <cuda_runtime_api.h>
@@ -72,9 +73,9 @@ bool split_dims(Dims const& d, int32_t signal_ndim, int64_t* batch, int64_t out[
 
 // Fixed-size key of one plan: no heap traffic on the enqueue path.
 struct PlanKey {
-    int32_t direction, signal_ndim, device;
+    int32_t direction, signal_ndim, device, io_type;
     int64_t batch, d0, d1, d2;
-    auto tie() const { return std::tie(direction, signal_ndim, device, batch, d0, d1, d2); }
+    auto tie() const { return std::tie(direction, signal_ndim, device, io_type, batch, d0, d1, d2); }
     bool operator<(PlanKey const& o) const { return tie() < o.tie(); }
     bool operator==(PlanKey const& o) const { return tie() == o.tie(); }
 };
@@ -100,7 +101,7 @@ public:
             if (!may_create) return nullptr;
             int64_t dims[3] = {k.d0, k.d1, k.d2};
             trt_dft_plan_t p = nullptr;
-            if (trt_dft_plan_create(&p, k.direction, k.signal_ndim, dims, k.batch) != TRT_DFT_OK) return nullptr;
+            if (trt_dft_plan_create_typed(&p, k.direction, k.signal_ndim, dims, k.batch, k.io_type) != TRT_DFT_OK) return nullptr;
             plans_[k] = p;
             return p;
         } catch (...) {
@@ -112,6 +113,23 @@ private:
     std::mutex mu_;
     std::map<PlanKey, trt_dft_plan_t> plans_;
 };
+
+// TensorRT data type -> TRT_DFT_IO_*, or -1.  The reference takes fp32 only (dft_plugins.cpp:93-105) and this plugin does
+// the same unless TRT_DFT_PLUGIN_16BIT_IO=1 is set when the engine is BUILT: with it, fp16 (and, from TensorRT 9, bf16)
+// tensors are offered as well -- same type on both sides, fp32 arithmetic inside -- which saves a half-precision engine
+// the two conversion layers around the plugin.  Opt-in because it changes numerics a model may rely on: the outputs are
+// rounded to 16 bits, and an unnormalised forward transform of a large image can exceed fp16's range (65504).
+static int io_type_of(DataType t)
+{
+    if (t == DataType::kFLOAT) return TRT_DFT_IO_F32;
+    char const* e = getenv("TRT_DFT_PLUGIN_16BIT_IO");        // (only ever read for non-fp32 tensors)
+    if (!e || e[0] != '1') return -1;
+    if (t == DataType::kHALF) return TRT_DFT_IO_F16;
+#if NV_TENSORRT_MAJOR >= 9
+    if (t == DataType::kBF16) return TRT_DFT_IO_BF16;
+#endif
+    return -1;
+}
 
 class DftPlugin final : public IPluginV2DynamicExt {
 public:
@@ -157,7 +175,8 @@ public:
                                    int32_t nbOutputs) noexcept override
     {
         if (nbInputs != 1 || nbOutputs != 1 || pos < 0 || pos >= 2 || !inOut) return false;
-        return inOut[pos].format == TensorFormat::kLINEAR && inOut[pos].type == DataType::kFLOAT;
+        if (inOut[pos].format != TensorFormat::kLINEAR || io_type_of(inOut[pos].type) < 0) return false;
+        return pos == 0 || inOut[1].type == inOut[0].type;          // one type on both sides
     }
 
     DataType getOutputDataType(int32_t, DataType const* inputTypes, int32_t nbInputs) const noexcept override
@@ -176,6 +195,7 @@ public:
         if (p) {
             p->ns_ = ns_;
             p->dynamic_ = dynamic_;
+            p->io_type_ = io_type_;
         }
         return p;
     }
@@ -185,7 +205,8 @@ public:
     {
         // Build the plan for the configured shape now, so that enqueue only launches.
         if (nbInputs != 1 || nbOutputs != 1 || !in || !out) return;
-        if (in[0].desc.type != DataType::kFLOAT || out[0].desc.type != DataType::kFLOAT) return;
+        if (io_type_of(in[0].desc.type) < 0 || out[0].desc.type != in[0].desc.type) return;
+        io_type_ = io_type_of(in[0].desc.type);
         // With a dynamic-shape profile (min != max) build the plans of the profile's corner shapes as well, so
         // that those shapes never allocate in enqueue; shapes in between are planned on first use.
         dynamic_ = false;
@@ -207,6 +228,7 @@ public:
         int64_t batch = 0, dims[3] = {1, 1, 1};
         if (!split_dims(signal_desc(inputs[0], outputs[0]).dims, attrs_.signal_ndim, &batch, dims)) return 0;
         size_t need = trt_dft_query_workspace_bytes(direction(), attrs_.signal_ndim, dims, batch);   // host-only arithmetic
+        const bool io16 = io_type_of(inputs[0].type) > TRT_DFT_IO_F32;
         if (dynamic_) {
             // TensorRT asks for the profile's largest shape only, but a smaller shape may pick another kind of
             // plan (fused kernels need nothing, un-fused inverses one complex tensor, lengths outside the radix
@@ -216,6 +238,16 @@ public:
             const size_t bound = 2 * (((size_t)cplx + 255) / 256 * 256);
             if (bound > need) need = bound;
         }
+        if (io16) {
+            // shapes without converting kernels run the fp32 plan between two conversion passes: fp32 copies of both
+            // tensors ahead of the plan's own workspace (an upper bound for the shapes that need none of it)
+            int64_t real = batch, cplx = batch * 2;
+            for (int32_t i = 0; i < attrs_.signal_ndim; ++i) {
+                real *= dims[i];
+                cplx *= (i == attrs_.signal_ndim - 1) ? dims[i] / 2 + 1 : dims[i];
+            }
+            need += ((size_t)real * 4 + 255) / 256 * 256 + ((size_t)cplx * 4 + 255) / 256 * 256;
+        }
         return need;
     }
 
@@ -224,6 +256,9 @@ public:
     {
         if (!inputDesc || !outputDesc || !inputs || !outputs) return 1;
         Dims const& sd = signal_desc(inputDesc[0], outputDesc[0]).dims;
+        const int io = io_type_of(inputDesc[0].type);
+        if (io < 0 || outputDesc[0].type != inputDesc[0].type) return 1;
+        io_type_ = io;
         trt_dft_plan_t plan = plan_for(sd, /*may_create=*/false);       // the normal case: a lookup, nothing else
         if (!plan) {
             // A shape no instance was configured for (dynamic shapes between the profile's corners).  Building a
@@ -267,7 +302,7 @@ private:
             cudaGetLastError();
             return nullptr;
         }
-        const PlanKey key{direction(), attrs_.signal_ndim, dev, batch, dims[0], dims[1], dims[2]};
+        const PlanKey key{direction(), attrs_.signal_ndim, dev, io_type_, batch, dims[0], dims[1], dims[2]};
         if (last_plan_ && key == last_key_) return last_plan_;
         trt_dft_plan_t p = PlanCache::get().find_or_create(key, may_create);
         if (p) {
@@ -281,6 +316,7 @@ private:
     Attributes attrs_;
     std::string ns_;
     bool dynamic_ = false;              // configured with a dynamic-shape profile (min != max)
+    int32_t io_type_ = TRT_DFT_IO_F32;  // of the tensors last configured / enqueued
     PlanKey last_key_{};
     trt_dft_plan_t last_plan_ = nullptr;
 };

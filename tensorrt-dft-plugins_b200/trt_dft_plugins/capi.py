@@ -16,6 +16,7 @@ SYMBOLS = [
     "trt_dft_plan_input_floats", "trt_dft_plan_output_floats", "trt_dft_plan_create_c2c", "trt_dft_plan_set_column_split",
     "trt_dft_query_workspace_bytes", "trt_dft_exec_static_ws", "trt_dft_plan_create_truncated",
     "trt_dft_plan_set_peer_column_split", "trt_dft_plan_set_peer_row_split", "trt_dft_plan_set_peer_column_gather",
+    "trt_dft_plan_create_typed", "trt_dft_plan_io_type",
 ]
 
 _bound = None
@@ -108,7 +109,8 @@ class Plan:
     def exec(self, x, out, workspace=None, stream=None):
         """x, out: contiguous CUDA float32 tensors; runs on `stream` (default: torch's current stream)."""
         import torch
-        assert x.is_cuda and out.is_cuda and x.dtype == torch.float32 and out.dtype == torch.float32
+        want = getattr(self, "torch_dtype", None) or torch.float32
+        assert x.is_cuda and out.is_cuda and x.dtype == want and out.dtype == want
         assert x.is_contiguous() and out.is_contiguous()
         assert x.numel() == self.input_floats and out.numel() == self.output_floats
         need = self.workspace_bytes
@@ -217,6 +219,37 @@ class TruncatedPlan(Plan):
         arr = (c_int64 * 2)(*self.dims)
         _check(L.trt_dft_plan_create_truncated(ctypes.byref(self._h), self.direction, arr, self.batch, self.keep_h, self.keep_w),
                "trt_dft_plan_create_truncated")
+
+
+IO_F32, IO_F16, IO_BF16 = 0, 1, 2
+
+
+class TypedPlan(Plan):
+    """rfftN / irfftN over 16-bit tensors with fp32 arithmetic (trt_dft_plan_create_typed).  `io` is IO_F16 or IO_BF16
+    (or a torch dtype); both the real and the complex tensor hold that type."""
+
+    def __init__(self, direction: int, dims, batch: int, io):
+        import torch
+        io = {torch.float32: IO_F32, torch.float16: IO_F16, torch.bfloat16: IO_BF16}.get(io, io)
+        L = lib()
+        L.trt_dft_plan_create_typed.restype = c_int
+        L.trt_dft_plan_create_typed.argtypes = [ctypes.POINTER(c_void_p), c_int, c_int, ctypes.POINTER(c_int64), c_int64, c_int]
+        L.trt_dft_plan_io_type.restype = c_int
+        L.trt_dft_plan_io_type.argtypes = [c_void_p]
+        self.direction = int(direction)
+        self.dims = tuple(int(d) for d in dims)
+        self.batch = int(batch)
+        self.io = int(io)
+        self.torch_dtype = {IO_F32: torch.float32, IO_F16: torch.float16, IO_BF16: torch.bfloat16}.get(self.io)
+        self._h = c_void_p()
+        self._ws = None
+        arr = (c_int64 * len(self.dims))(*self.dims)
+        _check(L.trt_dft_plan_create_typed(ctypes.byref(self._h), self.direction, len(self.dims), arr, self.batch, self.io),
+               "trt_dft_plan_create_typed")
+
+    @property
+    def io_type(self) -> int:
+        return int(lib().trt_dft_plan_io_type(self._h))
 
 
 def kept_rows(H: int, keep_h: int):

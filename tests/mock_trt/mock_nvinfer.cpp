@@ -190,6 +190,24 @@ int mock_output_dims(const char* op, int32_t nd, int32_t nb_in, const int32_t* i
     return r;
 }
 
+// data type of the tensors that mock_workspace_size and mock_lifecycle describe (default fp32)
+static DataType g_type = DataType::kFLOAT;
+void mock_set_tensor_type(int32_t type) { g_type = (DataType)type; }
+
+// both positions with the given types, as the builder asks once it has settled on a combination
+int mock_format_pair_ok(const char* op, int32_t type_in, int32_t type_out)
+{
+    IPluginV2DynamicExt* p = create(op, 0, 1, 2);
+    if (!p) return -1;
+    PluginTensorDesc d[2]{};
+    for (auto& x : d) { x.format = TensorFormat::kLINEAR; x.scale = 1.f; }
+    d[0].type = (DataType)type_in;
+    d[1].type = (DataType)type_out;
+    const int r = (p->supportsFormatCombination(0, d, 1, 1) && p->supportsFormatCombination(1, d, 1, 1)) ? 1 : 0;
+    p->destroy();
+    return r;
+}
+
 int mock_format_ok(const char* op, int32_t pos, int32_t type, int32_t format)
 {
     IPluginV2DynamicExt* p = create(op, 0, 1, 2);
@@ -238,7 +256,7 @@ size_t mock_workspace_size(const char* op, int32_t nd, int32_t nb_in, const int3
     if (!p) return (size_t)-1;
     Dims in = make_dims(nb_in, in_dims), out{};
     infer(p, in, &out);
-    PluginTensorDesc di{in, DataType::kFLOAT, TensorFormat::kLINEAR, 1.f}, dox{out, DataType::kFLOAT, TensorFormat::kLINEAR, 1.f};
+    PluginTensorDesc di{in, g_type, TensorFormat::kLINEAR, 1.f}, dox{out, g_type, TensorFormat::kLINEAR, 1.f};
     const size_t w = p->getWorkspaceSize(&di, 1, &dox, 1);
     p->destroy();
     return w;
@@ -255,7 +273,7 @@ int mock_lifecycle(const char* op, int32_t nd, int32_t nb_in, const int32_t* in_
     if (!infer(built, in, &out)) return 2;
     *nb_out = out.nbDims;
     memcpy(out_dims, out.d, sizeof(int32_t) * out.nbDims);
-    PluginTensorDesc io[2] = {{in, DataType::kFLOAT, TensorFormat::kLINEAR, 1.f}, {out, DataType::kFLOAT, TensorFormat::kLINEAR, 1.f}};
+    PluginTensorDesc io[2] = {{in, g_type, TensorFormat::kLINEAR, 1.f}, {out, g_type, TensorFormat::kLINEAR, 1.f}};
     if (!built->supportsFormatCombination(0, io, 1, 1) || !built->supportsFormatCombination(1, io, 1, 1)) return 3;
     // builder: clone, configure, workspace, (timing enqueue skipped), serialize
     IPluginV2DynamicExt* b2 = built->clone();

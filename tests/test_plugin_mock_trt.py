@@ -37,6 +37,9 @@ def mock():
     m.mock_try_create.argtypes = [c_char_p, c_int32, c_int32, c_int32]
     m.mock_output_dims.argtypes = [c_char_p, c_int32, c_int32, ctypes.POINTER(c_int32), ctypes.POINTER(c_int32)]
     m.mock_format_ok.argtypes = [c_char_p, c_int32, c_int32, c_int32]
+    m.mock_format_pair_ok.argtypes = [c_char_p, c_int32, c_int32]
+    m.mock_set_tensor_type.argtypes = [c_int32]
+    m.mock_set_tensor_type.restype = None
     m.mock_serialize_roundtrip.argtypes = [c_char_p, c_int32, ctypes.c_char_p, c_size_t]
     m.mock_workspace_size.argtypes = [c_char_p, c_int32, c_int32, ctypes.POINTER(c_int32)]
     m.mock_workspace_size.restype = c_size_t
@@ -139,6 +142,29 @@ def test_format_negotiation(mock, op):
 
 
 @pytest.mark.parametrize("op", [b"Rfft", b"Irfft"])
+def test_16_bit_tensors_are_offered_only_on_request(mock, op, monkeypatch):
+    """Like the reference (dft_plugins.cpp:93-105) the plugins take fp32 only -- unless TRT_DFT_PLUGIN_16BIT_IO=1 is set
+    while the engine is built; then fp16 on BOTH sides is a valid combination as well (mixed types never are)."""
+    FLOAT, HALF, INT8 = 0, 1, 2
+    monkeypatch.delenv("TRT_DFT_PLUGIN_16BIT_IO", raising=False)
+    assert mock.mock_format_pair_ok(op, FLOAT, FLOAT) == 1
+    assert mock.mock_format_pair_ok(op, HALF, HALF) == 0
+    monkeypatch.setenv("TRT_DFT_PLUGIN_16BIT_IO", "1")
+    assert mock.mock_format_pair_ok(op, FLOAT, FLOAT) == 1
+    assert mock.mock_format_pair_ok(op, HALF, HALF) == 1
+    assert mock.mock_format_pair_ok(op, HALF, FLOAT) == 0
+    assert mock.mock_format_pair_ok(op, FLOAT, HALF) == 0
+    assert mock.mock_format_pair_ok(op, INT8, INT8) == 0
+    # the conversion route's fp32 copies of both tensors are part of the workspace TensorRT is asked for
+    mock.mock_set_tensor_type(HALF)
+    try:
+        want = 4 * 128 * 128 * 4 + 4 * 128 * 65 * 2 * 4
+        assert mock.mock_workspace_size(b"Rfft", 2, 3, arr((4, 128, 128))) >= want
+    finally:
+        mock.mock_set_tensor_type(FLOAT)
+
+
+@pytest.mark.parametrize("op", [b"Rfft", b"Irfft"])
 @pytest.mark.parametrize("nd", [1, 2, 3])
 def test_serialisation_is_the_reference_wire_format(mock, op, nd):
     buf = ctypes.create_string_buffer(64)
@@ -160,9 +186,13 @@ def run_plugin(mock, op, nd, x, skip_configure=False):
     out_dims = (c_int32 * 8)()
     nb = c_int32(0)
     n = mock.mock_output_dims(op, nd, x.dim(), arr(tuple(x.shape)), out_dims)
-    y = torch.full(tuple(out_dims[:n]), float("nan"), device="cuda")
-    rc = mock.mock_lifecycle(op, nd, x.dim(), arr(tuple(x.shape)), xd.data_ptr(), y.data_ptr(),
-                             torch.cuda.current_stream().cuda_stream, int(skip_configure), out_dims, ctypes.byref(nb))
+    y = torch.full(tuple(out_dims[:n]), float("nan"), dtype=x.dtype, device="cuda")
+    mock.mock_set_tensor_type({torch.float32: 0, torch.float16: 1}[x.dtype])
+    try:
+        rc = mock.mock_lifecycle(op, nd, x.dim(), arr(tuple(x.shape)), xd.data_ptr(), y.data_ptr(),
+                                 torch.cuda.current_stream().cuda_stream, int(skip_configure), out_dims, ctypes.byref(nb))
+    finally:
+        mock.mock_set_tensor_type(0)
     assert rc == 0
     torch.cuda.synchronize()
     assert tuple(out_dims[:nb.value]) == tuple(y.shape)
@@ -214,6 +244,27 @@ def test_plugin_pair_at_baseline_shapes(mock, shape, nd, skip_configure):
     assert O.rel_l2(y.numpy(), want.numpy()) <= 1e-5
     xr = run_plugin(mock, b"Irfft", nd, y, skip_configure)
     assert O.rel_l2(xr.numpy(), x.numpy()) <= 1e-6
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("shape,nd", [((2, 9, 90, 180), 2), ((3, 64, 64), 2), ((4, 32, 64), 1)])
+def test_plugin_pair_with_fp16_tensors(mock, shape, nd, monkeypatch):
+    """The whole plugin lifecycle with kHALF on both sides (TRT_DFT_PLUGIN_16BIT_IO=1): fp32 arithmetic inside, so what
+    separates the result from the fp64 oracle on the same fp16 input is the rounding of the output (tolerance as in
+    tests/test_gpu_typed_io.py).  Without the switch the same descriptors are refused."""
+    torch.manual_seed(1)
+    x = torch.randn(*shape).to(torch.float16)
+    dim = tuple(range(-nd, 0))
+    monkeypatch.setenv("TRT_DFT_PLUGIN_16BIT_IO", "1")
+    y = run_plugin(mock, b"Rfft", nd, x)
+    want = torch.view_as_real(torch.fft.rfftn(x.double(), dim=dim))
+    assert float((y.double() - want).norm() / want.norm()) <= 3e-4
+    xr = run_plugin(mock, b"Irfft", nd, y)
+    want_x = torch.fft.irfftn(torch.view_as_complex(y.double().contiguous()), s=shape[-nd:], dim=dim)
+    assert float((xr.double() - want_x).norm() / want_x.norm()) <= 3e-4
+    monkeypatch.delenv("TRT_DFT_PLUGIN_16BIT_IO")
+    with pytest.raises(AssertionError):
+        run_plugin(mock, b"Rfft", nd, x)
 
 
 @pytest.mark.gpu
