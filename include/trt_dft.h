@@ -93,7 +93,7 @@ int trt_dft_plan_set_column_split(trt_dft_plan_t plan, int nparts, const int64_t
  *             == torch.fft.rfft2(x)[..., rows, :keep_w] with rows = cat(0..keep_h-1, H-keep_h..H-1)
  *   INVERSE : in  [batch][2*keep_h][keep_w] complex -> out [batch][H][W] real, scaled by 1/(H*W)
  *             == torch.fft.irfft2 of the spectrum that holds `in` at those modes and zeros elsewhere.
- * Shapes with fused register-resident kernels (90 x 180) run one kernel that bulk-copies only the kept block
+ * Shapes with fused kernels (90 x 180, 128 x 128, 64 x 64) run one kernel that moves only the kept block
  * (no workspace; in/out must be 16-byte aligned); every other shape runs the full transform through the workspace
  * plus a crop / zero-pad kernel (query trt_dft_workspace_bytes).  Executed with trt_dft_exec / trt_dft_exec_host.
  */
