@@ -243,8 +243,8 @@ def truncated_bench(capi, torch, peak, iters=200, nimg=SHAPE[0] * SHAPE[1], H=H,
     return out
 
 
-def half_io_bench(capi, torch, peak, iters=200, nimg=SHAPE[0] * SHAPE[1]):
-    """The headline shape with fp16 / bf16 tensors on both sides (trt_dft_plan_create_typed; fp32 arithmetic): half the
+def half_io_bench(capi, torch, peak, iters=200, nimg=SHAPE[0] * SHAPE[1], H=H, W=W):
+    """The headline shape (or the FNO shape) with fp16 / bf16 tensors on both sides (trt_dft_plan_create_typed; fp32 arithmetic): half the
     bytes per element cross HBM.  Its own algorithmic bytes; accuracy against fp64 torch.fft of the same 16-bit input
     on the first 64 images."""
     out = {}
@@ -677,6 +677,7 @@ def run_ours(args):
             extras["truncated_modes"] = {"error": repr(e)[:300]}
         try:
             extras["half_io_cfg3"] = half_io_bench(capi, torch, peak)
+            extras["half_io_cfg2"] = half_io_bench(capi, torch, peak, nimg=1024, H=128, W=128)
         except Exception as e:
             extras["half_io_cfg3"] = {"error": repr(e)[:300]}
         extras["cufft_sequence"] = cufft_sequence(torch, capi, ["cfg1", "cfg2", "cfg3", "cfg4", "cfg5"])

@@ -22,7 +22,10 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 
+#include <type_traits>
+
 #include "dft_butterflies.cuh"
+#include "dft_io16.cuh"
 
 namespace dft {
 
@@ -120,13 +123,19 @@ __device__ __forceinline__ int f2d_keep_arg(Keep... keep)
     return v[I];
 }
 
-template <class C, class... Keep>
+//
+// IO = float, or __half / __nv_bfloat16 for typed-I/O plans: both tensors hold 16-bit elements, which are widened as the
+// image is loaded into the (fp32) tile and rounded as the results are stored -- ordinary coalesced accesses in place of the
+// bulk copies, everything in between unchanged.
+template <class C, class IO, class... Keep>
 __global__ void __launch_bounds__(C::NT, C::MINB)
     fused_rfft2_kernel(const float* __restrict__ in, float* __restrict__ out, long long nimg,
                        const float2* __restrict__ tables, float /*scale: forward is unnormalised*/, Keep... keep)
 {
     constexpr bool TR = sizeof...(Keep) == 2;
+    constexpr bool IO16 = !std::is_same<IO, float>::value;
     static_assert(TR || sizeof...(Keep) == 0, "Keep is () or (keep_h, keep_w)");
+    static_assert(!(TR && IO16), "truncated-mode plans are fp32");
     const int kh = f2d_keep_arg<0>(keep...), kw = f2d_keep_arg<1>(keep...);
     constexpr int H = C::H, W = C::W, M = C::M, RA = C::RA, RB = C::RB, CA = C::CA, CB = C::CB, NT = C::NT;
     constexpr int KH = C::KH, MO = M + 1;
@@ -142,12 +151,17 @@ __global__ void __launch_bounds__(C::NT, C::MINB)
     if (tid == 0) f2d_mbar_init(bar);
     __syncthreads();
     unsigned phase = 0;
-    const bool bulk = C::BULK_REAL && (((uintptr_t)in & 15) == 0);
+    const bool bulk = !IO16 && C::BULK_REAL && (((uintptr_t)in & 15) == 0);
     const bool vec2 = (((uintptr_t)in & 7) == 0);
 
     for (long long img = blockIdx.x; img < nimg; img += gridDim.x) {
         const float* src = in + img * (long long)(H * W);
-        if (bulk) {
+        if constexpr (IO16) {
+            typedef typename Io16<IO>::v2 v2;
+            const v2* s16 = reinterpret_cast<const v2*>(in) + img * (long long)(H * M);      // (4-byte aligned: W is even)
+            for (int i = tid; i < H * M; i += NT) buf[i] = Io16<IO>::up(__ldg(s16 + i));
+            __syncthreads();
+        } else if (bulk) {
             if (tid == 0) f2d_bulk_load(buf, src, H * W * 4, bar);
             f2d_mbar_wait(bar, phase);
             phase ^= 1u;
@@ -258,7 +272,14 @@ __global__ void __launch_bounds__(C::NT, C::MINB)
                 const float ex = 0.5f * (z1.x + z2.x), ey = 0.5f * (z1.y - z2.y);
                 const float dx = z1.x - z2.x, dy = z1.y + z2.y;
                 const float tx = wh.x * dx - wh.y * dy, ty = wh.x * dy + wh.y * dx;
-                if constexpr (!TR) {
+                if constexpr (IO16) {
+                    typedef typename Io16<IO>::v2 v2;
+                    v2* o16 = reinterpret_cast<v2*>(out) + img * (long long)(H * MO);
+                    o16[(oa - oimg) + k2 * CA * MO] = Io16<IO>::down(float2{ex + ty, ey - tx});
+                    long long ib = (ob - oimg) - k2 * CA * MO;
+                    if (k2 == 0 && q1 == 0) ib -= H * MO;
+                    o16[ib] = Io16<IO>::down(float2{ex - ty, -ey - tx});
+                } else if constexpr (!TR) {
                     oa[k2 * CA * MO] = float2{ex + ty, ey - tx};
                     float2* pbk = ob - k2 * CA * MO;
                     if (k2 == 0 && q1 == 0) pbk -= H * MO;       // (H - 0) mod H = 0
@@ -279,13 +300,15 @@ __global__ void __launch_bounds__(C::NT, C::MINB)
 // ---- inverse ---------------------------------------------------------------------------------
 // TR: the input is the dense kept block [2*kh][kw]; it is expanded into the one-sided tile while it is loaded (zeros
 // everywhere else), the rest is the ordinary kernel.
-template <class C, class... Keep>
+template <class C, class IO, class... Keep>
 __global__ void __launch_bounds__(C::NT, C::MINB)
     fused_irfft2_kernel(const float* __restrict__ in, float* __restrict__ out, long long nimg,
                         const float2* __restrict__ tables, float scale /* 1/prod(signal dims) */, Keep... keep)
 {
     constexpr bool TR = sizeof...(Keep) == 2;
+    constexpr bool IO16 = !std::is_same<IO, float>::value;
     static_assert(TR || sizeof...(Keep) == 0, "Keep is () or (keep_h, keep_w)");
+    static_assert(!(TR && IO16), "truncated-mode plans are fp32");
     const int kh = f2d_keep_arg<0>(keep...), kw = f2d_keep_arg<1>(keep...);
     constexpr int H = C::H, W = C::W, M = C::M, RA = C::RA, RB = C::RB, CA = C::CA, CB = C::CB, NT = C::NT;
     constexpr int KH = C::KH, PI = C::PI;
@@ -301,8 +324,8 @@ __global__ void __launch_bounds__(C::NT, C::MINB)
     if (tid == 0) f2d_mbar_init(bar);
     __syncthreads();
     unsigned phase = 0;
-    const bool bulk_in = !TR && C::BULK_CPLX && (((uintptr_t)in & 15) == 0);
-    const bool bulk_out = C::BULK_REAL && (((uintptr_t)out & 15) == 0);
+    const bool bulk_in = !TR && !IO16 && C::BULK_CPLX && (((uintptr_t)in & 15) == 0);
+    const bool bulk_out = !IO16 && C::BULK_REAL && (((uintptr_t)out & 15) == 0);
 
     for (long long img = blockIdx.x; img < nimg; img += gridDim.x) {
         const float2* src = reinterpret_cast<const float2*>(in) + img * (long long)(TR ? 2 * kh * kw : H * PI);
@@ -317,6 +340,11 @@ __global__ void __launch_bounds__(C::NT, C::MINB)
                 const int qi = e / kw, k = e - qi * kw;
                 buf[(qi < kh ? qi : qi + (H - 2 * kh)) * PI + k] = __ldg(src + e);
             }
+            __syncthreads();
+        } else if constexpr (IO16) {
+            typedef typename Io16<IO>::v2 v2;
+            const v2* s16 = reinterpret_cast<const v2*>(in) + img * (long long)(H * PI);
+            for (int i = tid; i < H * PI; i += NT) buf[i] = Io16<IO>::up(__ldg(s16 + i));
             __syncthreads();
         } else if (bulk_in) {
             if (tid == 0) f2d_bulk_load(buf, src, H * PI * 8, bar);
@@ -447,7 +475,13 @@ __global__ void __launch_bounds__(C::NT, C::MINB)
             }
         }
         float* dst = out + img * (long long)(H * W);
-        if (bulk_out) {
+        if constexpr (IO16) {
+            typedef typename Io16<IO>::v2 v2;
+            v2* d16 = reinterpret_cast<v2*>(out) + img * (long long)(H * M);
+            __syncthreads();
+            for (int i = tid; i < H * M; i += NT) d16[i] = Io16<IO>::down(buf[i]);
+            __syncthreads();
+        } else if (bulk_out) {
             asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
             __syncthreads();
             if (tid == 0) f2d_bulk_store_and_wait(dst, buf, H * W * 4);

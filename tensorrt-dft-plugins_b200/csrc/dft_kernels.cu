@@ -328,8 +328,17 @@ int trt_dft_plan_create_typed(trt_dft_plan_t* plan_out, int direction, int rank,
         pl->t_scale = (float)(1.0 / ((double)dims[0] * (double)dims[1]));
         if (cudaFuncSetAttribute((const void*)fused, cudaFuncAttributeMaxDynamicSharedMemorySize, pl->t_smem) == cudaSuccess &&
             cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, (const void*)fused, pl->t_threads, pl->t_smem) == cudaSuccess && occ >= 1) {
-            pl->io_fn = fused;
-            pl->t_grid = (int)std::min<long long>(batch, (long long)num_sms * occ);
+            // the pass-per-radix fused kernels (128 x 128, 64 x 64) read their twiddles from a small device table
+            std::vector<float2> tab = spec_tables(*e, inv, (double)pl->t_scale);
+            if (cudaMalloc(&pl->pool, tab.size() * sizeof(float2)) == cudaSuccess &&
+                cudaMemcpy(pl->pool, tab.data(), tab.size() * sizeof(float2), cudaMemcpyHostToDevice) == cudaSuccess) {
+                pl->io_fn = fused;
+                pl->t_grid = (int)std::min<long long>(batch, (long long)num_sms * occ);
+            } else {
+                cudaGetLastError();
+                if (pl->pool) cudaFree(pl->pool);
+                pl->pool = nullptr;
+            }
         } else {
             cudaGetLastError();
         }
@@ -819,7 +828,7 @@ static int exec_typed(trt_dft_plan_t plan, const void* in, void* out, void* work
         // whole images move as bulk copies: 16-byte aligned tensors (any tensor of a framework allocator is)
         if ((((uintptr_t)in) | ((uintptr_t)out)) & 15) return TRT_DFT_ERR_INVALID_ARG;
         plan->io_fn<<<plan->t_grid, plan->t_threads, plan->t_smem, (cudaStream_t)stream>>>((const float*)in, (float*)out, plan->pd.batch,
-                                                                                           nullptr, plan->t_scale);
+                                                                                           (const float2*)plan->pool, plan->t_scale);
     } else {
         if (!workspace || ((uintptr_t)workspace & 15)) return TRT_DFT_ERR_WORKSPACE;
         if ((((uintptr_t)in) | ((uintptr_t)out)) & 1) return TRT_DFT_ERR_INVALID_ARG;

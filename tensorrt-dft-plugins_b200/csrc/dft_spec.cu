@@ -13,9 +13,13 @@ template <class C>
 SpecEntry make_spec()
 {
     SpecEntry e{C::H, C::W, C::RA, C::RB, C::CA, C::CB, C::NT, C::SMEM_F, C::SMEM_I,
-                fused_rfft2_kernel<C>, fused_irfft2_kernel<C>, false};
-    e.trunc_fwd = fused_rfft2_kernel<C, int, int>;
-    e.trunc_inv = fused_irfft2_kernel<C, int, int>;
+                fused_rfft2_kernel<C, float>, fused_irfft2_kernel<C, float>, false};
+    e.trunc_fwd = fused_rfft2_kernel<C, float, int, int>;
+    e.trunc_inv = fused_irfft2_kernel<C, float, int, int>;
+    e.fwd16[0] = fused_rfft2_kernel<C, __half>;
+    e.inv16[0] = fused_irfft2_kernel<C, __half>;
+    e.fwd16[1] = fused_rfft2_kernel<C, __nv_bfloat16>;
+    e.inv16[1] = fused_irfft2_kernel<C, __nv_bfloat16>;
     return e;
 }
 

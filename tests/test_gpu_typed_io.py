@@ -7,8 +7,8 @@ fp32 path on the widened input, rounded to 16 bits by torch: the typed plans run
 agree to the last bit almost everywhere (a different FMA contraction may flip a rounding once in a while: <= 1 ulp, <= 0.01 %
 of the elements).  That second check is what catches a misplaced element; it is exact where (1) is statistical.
 
-90 x 180 runs the kernels that convert as they load and store (odd and even image counts, more images than the grid holds
-at once, a single image); the other shapes run the fp32 plan between two conversion passes."""
+90 x 180, 128 x 128 and 64 x 64 run kernels that convert as they load and store (odd and even image counts, more images than
+the grid holds at once, a single image); the other shapes run the fp32 plan between two conversion passes."""
 import pytest
 import torch
 
@@ -19,7 +19,8 @@ TOL = {torch.float16: 3e-4, torch.bfloat16: 2.5e-3}
 CASES = [
     # (leading shape, signal dims)
     ((1,), (90, 180)), ((2,), (90, 180)), ((149,), (90, 180)), ((445,), (90, 180)), ((2, 500), (90, 180)), ((1333,), (90, 180)),
-    ((4, 32), (64,)), ((3,), (128, 128)), ((5,), (34, 74)), ((2,), (8, 12, 10)), ((3,), (720, 1440)), ((7,), (31,)),
+    ((3,), (128, 128)), ((1024,), (128, 128)), ((445,), (64, 64)), ((2000,), (64, 64)),
+    ((4, 32), (64,)), ((5,), (34, 74)), ((2,), (8, 12, 10)), ((3,), (720, 1440)), ((7,), (31,)), ((6,), (60, 120)),
 ]
 
 
@@ -88,11 +89,14 @@ def test_typed_plan_routes_and_argument_checks():
     p = capi.TypedPlan(capi.FORWARD, (90, 180), 64, capi.IO_F16)
     n, text = p.describe()
     assert n == 1 and "converts as it loads and stores" in text and p.workspace_bytes == 0, text
-    q = capi.TypedPlan(capi.INVERSE, (128, 128), 8, capi.IO_BF16)
+    for dims in ((128, 128), (64, 64)):
+        n, text = capi.TypedPlan(capi.INVERSE, dims, 8, capi.IO_BF16).describe()
+        assert n == 1 and "converts as it loads and stores" in text, text
+    q = capi.TypedPlan(capi.INVERSE, (60, 120), 8, capi.IO_BF16)
     n, text = q.describe()
     assert n == 3 and "bf16 -> fp32" in text and "fp32 -> bf16" in text, text
     # fp32 input + fp32 output + whatever the fp32 plan wants
-    inner = capi.Plan(capi.INVERSE, (128, 128), 8)
+    inner = capi.Plan(capi.INVERSE, (60, 120), 8)
     assert q.workspace_bytes >= (q.input_floats + q.output_floats) * 4 + inner.workspace_bytes
     # IO_F32 is the ordinary constructor
     r = capi.TypedPlan(capi.FORWARD, (90, 180), 4, capi.IO_F32)
@@ -106,8 +110,8 @@ def test_typed_plan_routes_and_argument_checks():
     assert e.describe()[0] == 0
     e.exec_ptr(0, 0, 0, 0)
     # the converting kernels move whole images with bulk copies: a tensor that is not 16-byte aligned is refused
-    x = torch.zeros(4 * 90 * 180 + 8, dtype=torch.float16, device="cuda")
-    y = torch.zeros(4 * 90 * 91 * 2, dtype=torch.float16, device="cuda")
+    x = torch.zeros(8 * 90 * 180 + 8, dtype=torch.float16, device="cuda")
+    y = torch.zeros(8 * 90 * 91 * 2, dtype=torch.float16, device="cuda")
     p4 = capi.TypedPlan(capi.FORWARD, (90, 180), 4, capi.IO_F16)
     with pytest.raises(capi.DftError):
         p4.exec_ptr(x.data_ptr() + 2, y.data_ptr(), 0, torch.cuda.current_stream().cuda_stream)
