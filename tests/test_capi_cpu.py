@@ -68,6 +68,26 @@ def test_argument_validation_without_a_device(lib):
     p.exec_ptr(0, 0)
 
 
+def test_typed_plan_argument_validation_without_a_device(lib):
+    """trt_dft_plan_create_typed: the element type is checked before anything touches CUDA, an empty batch needs no device,
+    and a 16-bit plan of a real size fails loudly without a GPU like every other plan."""
+    import torch
+    from trt_dft_plugins import capi
+    with pytest.raises(capi.DftError):
+        capi.TypedPlan(capi.FORWARD, (8, 8), 1, 3)
+    with pytest.raises(capi.DftError):
+        capi.TypedPlan(capi.FORWARD, (8, 8), 1, -1)
+    with pytest.raises(capi.DftError):
+        capi.TypedPlan(2, (8, 8), 1, capi.IO_F16)
+    e = capi.TypedPlan(capi.INVERSE, (90, 180), 0, capi.IO_BF16)
+    assert e.io_type == capi.IO_BF16 and e.num_launches == 0 and e.workspace_bytes == 0
+    e.exec_ptr(0, 0)
+    assert capi.TypedPlan(capi.FORWARD, (90, 180), 0, capi.IO_F32).io_type == capi.IO_F32
+    if not torch.cuda.is_available():
+        with pytest.raises(capi.DftError):
+            capi.TypedPlan(capi.FORWARD, (8, 8), 1, capi.IO_F16)
+
+
 def test_no_cpu_route_without_a_gpu(lib):
     """The product must fail loudly, not fall back, when there is no CUDA device."""
     import torch
