@@ -214,6 +214,38 @@ def test_c2c_strided_axis_plan(capi, outer, n, inner, direction):
     assert torch.equal(zd, out)
 
 
+@pytest.mark.parametrize("shape,nd", [((300, 90, 180), 2), ((2, 2048, 4100), 2), ((64, 128, 128), 2), ((3000, 60, 120), 2), ((40000, 64), 1)])
+def test_one_plan_on_two_streams_at_once(capi, shape, nd):
+    """include/trt_dft.h: a plan is immutable and may be used from several streams at once.  Two streams run the same
+    forward and inverse plans concurrently on different tensors (each with a workspace of its own), several rounds
+    without synchronising in between; both results must be what a lone call gives."""
+    batch = 1
+    for v in shape[:-nd]:
+        batch *= v
+    dims = shape[-nd:]
+    f = capi.Plan(capi.FORWARD, dims, batch)
+    i = capi.Plan(capi.INVERSE, dims, batch)
+    need = max(f.workspace_bytes, i.workspace_bytes, 16)
+    g = torch.Generator().manual_seed(11)
+    xs = [torch.randn(*shape, generator=g).cuda() for _ in range(2)]
+    ys = [torch.empty(shape[:-1] + (dims[-1] // 2 + 1, 2), device="cuda") for _ in range(2)]
+    xr = [torch.empty_like(xs[0]) for _ in range(2)]
+    ws = [torch.empty(need, dtype=torch.uint8, device="cuda") for _ in range(2)]
+    alone_y = capi.rfftn(xs[0], nd), capi.rfftn(xs[1], nd)
+    alone_x = capi.irfftn(alone_y[0], nd, last=dims[-1]), capi.irfftn(alone_y[1], nd, last=dims[-1])
+    torch.cuda.synchronize()
+    streams = [torch.cuda.Stream(), torch.cuda.Stream()]
+    for _ in range(4):
+        for k in range(2):
+            with torch.cuda.stream(streams[k]):
+                f.exec(xs[k], ys[k], workspace=ws[k])
+                i.exec(ys[k], xr[k], workspace=ws[k])
+    torch.cuda.synchronize()
+    for k in range(2):
+        assert torch.equal(ys[k], alone_y[k])
+        assert torch.equal(xr[k], alone_x[k])
+
+
 def test_exec_is_capturable_in_a_cuda_graph(capi):
     """trt_dft_exec only launches kernels on the given stream, so a whole rfft2 -> irfft2 pair can be
     captured once and replayed (what TensorRT does around enqueue)."""
