@@ -101,3 +101,33 @@ def test_truncated_plans_through_the_host_buffer_call(H, W, kh, kw):
     capi.TruncatedPlan(capi.INVERSE, (H, W), batch, kh, kw).exec_host(out, back)
     want_x = oracle_padded_inverse(out, H, W, kh, kw)
     assert O.rel_l2(back.numpy(), want_x.numpy()) <= 1e-5
+
+
+@pytest.mark.parametrize("B,C,H,W,kh,kw", [(4, 16, 128, 128, 12, 12), (2, 24, 90, 180, 16, 24), (3, 8, 64, 64, 8, 9), (2, 6, 60, 120, 10, 14)])
+def test_fno_spectral_layer_through_truncated_plans(B, C, H, W, kh, kw):
+    """The layer these plans exist for (FNO's SpectralConv2d, the reference's stated use, README.md:3):
+    rfft2 -> keep the low modes -> per-mode channel mixing -> zero-pad -> irfft2.  Ours: truncated forward plan, the
+    mixing as an einsum on the kept block, truncated inverse plan.  Checked against the same layer in fp64 torch on the
+    CPU with the full transforms."""
+    from trt_dft_plugins import capi
+    g = torch.Generator().manual_seed(B * 100 + C)
+    x = torch.randn(B, C, H, W, generator=g)
+    w = torch.randn(C, C, 2 * kh, kw, 2, generator=g) / C
+    rows = capi.kept_rows(H, kh)
+    # fp64 layer with full transforms
+    wc = torch.view_as_complex(w.double().contiguous())
+    X = torch.fft.rfft2(x.double())
+    Y = torch.zeros(B, C, H, W // 2 + 1, dtype=torch.complex128)
+    Y[:, :, rows, :kw] = torch.einsum("bixy,ioxy->boxy", X[:, :, rows, :kw], wc)
+    want = torch.fft.irfft2(Y, s=(H, W))
+    # the same layer on the GPU through the truncated plans
+    f = capi.TruncatedPlan(capi.FORWARD, (H, W), B * C, kh, kw)
+    i = capi.TruncatedPlan(capi.INVERSE, (H, W), B * C, kh, kw)
+    kept = torch.empty(B, C, 2 * kh, kw, 2, device="cuda")
+    f.exec(x.cuda(), kept)
+    mixed = torch.einsum("bixy,ioxy->boxy", torch.view_as_complex(kept), torch.view_as_complex(w.cuda().contiguous()))
+    out = torch.empty(B, C, H, W, device="cuda")
+    i.exec(torch.view_as_real(mixed).contiguous(), out)
+    torch.cuda.synchronize()
+    err = float((out.cpu().double() - want).norm() / want.norm())
+    assert err <= 1e-5, err
