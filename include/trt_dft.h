@@ -93,7 +93,7 @@ int trt_dft_plan_set_column_split(trt_dft_plan_t plan, int nparts, const int64_t
  *             == torch.fft.rfft2(x)[..., rows, :keep_w] with rows = cat(0..keep_h-1, H-keep_h..H-1)
  *   INVERSE : in  [batch][2*keep_h][keep_w] complex -> out [batch][H][W] real, scaled by 1/(H*W)
  *             == torch.fft.irfft2 of the spectrum that holds `in` at those modes and zeros elsewhere.
- * Shapes with fused kernels (90 x 180, 128 x 128, 64 x 64) run one kernel that moves only the kept block
+ * Shapes with fused kernels (90 x 180, 128 x 128, 64 x 64, 64 x 128, 128 x 64) run one kernel that moves only the kept block
  * (no workspace; in/out must be 16-byte aligned); every other shape runs the full transform through the workspace
  * plus a crop / zero-pad kernel (query trt_dft_workspace_bytes).  Executed with trt_dft_exec / trt_dft_exec_host.
  */
@@ -108,7 +108,7 @@ int trt_dft_plan_create_truncated(trt_dft_plan_t* plan, int direction, const int
  *             dim of 2) both hold 16-bit elements; same shapes, same scaling as trt_dft_plan_create.  Results are the
  *             fp32 transform of the 16-bit input, rounded to nearest even on the way out.  (fp16 overflows at 65504:
  *             an unnormalised forward transform of n points grows like sqrt(n) times the input's magnitude.)
- * 90 x 180, 128 x 128 and 64 x 64 run kernels that convert as they load and store, so only 16-bit data crosses HBM
+ * 90 x 180, 128 x 128, 64 x 64, 64 x 128 and 128 x 64 run kernels that convert as they load and store, so only 16-bit data crosses HBM
  * (no workspace; both tensors 16-byte aligned).  Every other shape runs the fp32 plan between two conversion passes through the workspace
  * (query trt_dft_workspace_bytes; tensors 2-byte aligned).  trt_dft_plan_input_floats / _output_floats count elements.
  * Executed with trt_dft_exec / trt_dft_exec_host / trt_dft_exec_static_ws.

@@ -66,6 +66,8 @@ const SpecEntry* find_spec(int H, int W)
         //                 H    W   RA  RB  CA  CB   NT  min CTAs/SM
         make_spec<FusedCfg<128, 128, 8, 8, 16, 8, 256, 3>>(),     // FNO (BASELINE cfg2)
         make_spec<FusedCfg<64, 64, 8, 4, 8, 8, 256, 4>>(),
+        make_spec<FusedCfg<64, 128, 8, 8, 8, 8, 256, 4>>(),       // rectangular FNO grids
+        make_spec<FusedCfg<128, 64, 8, 4, 16, 8, 256, 3>>(),
     };
     const bool no_pipe = getenv("TRT_DFT_NO_PIPE") != nullptr;   // benchmarking override
     for (const auto& e : table)

@@ -82,6 +82,7 @@ SHAPES = [
     # 2-D
     ((7, 8, 8), 2), ((3, 6, 10), 2), ((2, 5, 7), 2), ((2, 12, 18), 2), ((2, 17, 6), 2), ((2, 6, 38), 2),
     ((700, 4, 4), 2), ((1, 1, 16), 2), ((2, 16, 1), 2), ((2, 3, 3), 2), ((300, 32, 32), 2), ((5, 64, 64), 2),
+    ((7, 64, 128), 2), ((1030, 64, 128), 2), ((5, 128, 64), 2), ((1000, 128, 64), 2), ((2000, 64, 64), 2),   # fused rectangular FNO grids, looping and one-CTA-per-image grids
     ((3, 256, 256), 2), ((2, 180, 360), 2), ((2, 720, 1440), 2), ((4, 720, 1440), 2), ((1, 1024, 1024), 2), ((1, 2048, 4096), 2), ((2, 4096, 512), 2), ((1, 8192, 1024), 2), ((1, 5120, 320), 2),
     # 3-D
     ((2, 4, 6, 8), 3), ((2, 3, 5, 6), 3), ((1, 2, 3, 5, 7), 3), ((2, 1, 4, 4), 3), ((1, 17, 4, 6), 3),

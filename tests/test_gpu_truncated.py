@@ -11,7 +11,7 @@ pytestmark = pytest.mark.gpu
 CASES = [
     # (batch, H, W, keep_h, keep_w)
     (7, 90, 180, 12, 20), (300, 90, 180, 45, 91), (149, 90, 180, 1, 1), (5, 90, 180, 30, 33), (64, 90, 180, 20, 64),
-    (6, 128, 128, 16, 16), (3, 64, 64, 8, 12), (700, 128, 128, 12, 12), (5, 128, 128, 64, 65), (9, 128, 128, 1, 40), (4, 64, 64, 32, 33), (2, 720, 1440, 32, 48), (4, 34, 74, 5, 7), (3, 60, 120, 30, 61),
+    (6, 128, 128, 16, 16), (3, 64, 64, 8, 12), (700, 128, 128, 12, 12), (5, 128, 128, 64, 65), (9, 128, 128, 1, 40), (4, 64, 64, 32, 33), (900, 64, 128, 12, 20), (5, 128, 64, 64, 33), (2, 720, 1440, 32, 48), (4, 34, 74, 5, 7), (3, 60, 120, 30, 61),
 ]
 
 

@@ -19,7 +19,7 @@ TOL = {torch.float16: 3e-4, torch.bfloat16: 2.5e-3}
 CASES = [
     # (leading shape, signal dims)
     ((1,), (90, 180)), ((2,), (90, 180)), ((149,), (90, 180)), ((445,), (90, 180)), ((2, 500), (90, 180)), ((1333,), (90, 180)),
-    ((3,), (128, 128)), ((1024,), (128, 128)), ((445,), (64, 64)), ((2000,), (64, 64)),
+    ((3,), (128, 128)), ((1024,), (128, 128)), ((445,), (64, 64)), ((2000,), (64, 64)), ((1001,), (64, 128)), ((9,), (128, 64)),
     ((4, 32), (64,)), ((5,), (34, 74)), ((2,), (8, 12, 10)), ((3,), (720, 1440)), ((7,), (31,)), ((6,), (60, 120)),
 ]
 
